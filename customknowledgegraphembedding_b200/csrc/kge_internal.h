@@ -1,0 +1,64 @@
+// Internal launcher declarations (host side) shared by the translation units of libkge_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "kge_common.cuh"
+
+namespace kge {
+
+int sm_count();  // SMs of the current device (cached)
+
+// error plumbing + desc validation (kge_api.cu)
+int fail(int code, const char* fmt, ...);
+int fail_cuda(cudaError_t e, const char* where);
+int make_params(const kge_model_desc* d, Params* P);
+
+// true when every row of both tables can be read with 128-bit loads
+inline bool vec4_ok(const Params& P, const void* a, const void* b) {
+    return (P.H % 4 == 0) && (P.De % 4 == 0) && (P.Dr % 4 == 0) && ((reinterpret_cast<uintptr_t>(a) & 15) == 0) &&
+           ((reinterpret_cast<uintptr_t>(b) & 15) == 0);
+}
+
+// K1
+cudaError_t launch_score_forward(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
+                                 const int64_t* pos, const int64_t* neg, int64_t B, int64_t N, float* scores,
+                                 cudaStream_t st);
+
+// K3 (atomic variant): += into dense grad tables
+cudaError_t launch_score_backward_atomic(const Params& P, int mode, const float* ent, const float* rel,
+                                         const float* modulus, const int64_t* pos, const int64_t* neg, int64_t B,
+                                         int64_t N, const float* dscore, float* grad_ent, float* grad_rel,
+                                         float* grad_modulus, cudaStream_t st);
+
+// K3 (deterministic variant)
+size_t backward_det_workspace_bytes(const Params& P, int64_t B, int64_t N);
+cudaError_t launch_score_backward_det(const Params& P, int mode, const float* ent, const float* rel,
+                                      const float* modulus, const int64_t* pos, const int64_t* neg, int64_t B,
+                                      int64_t N, const float* dscore, float* grad_ent, float* grad_rel,
+                                      float* grad_modulus, void* ws, size_t ws_bytes, cudaStream_t st);
+
+// K2
+size_t loss_workspace_bytes(int64_t B);
+cudaError_t launch_loss(const float* neg_score, const float* pos_score, const float* w, int64_t B, int64_t N,
+                        const kge_loss_opts& o, float* loss3, float* dneg, float* dpos, float* ws, cudaStream_t st);
+cudaError_t launch_l3_sum_cubes(const float* x, int64_t n, float* out, float* ws, cudaStream_t st);
+
+// K4
+struct AdamScalars {
+    float beta1, beta2, step_size, inv_sqrt_bc2, eps;
+};
+AdamScalars adam_scalars(const kge_adam_opts& o);
+cudaError_t launch_adam(float* p, float* g, float* m, float* v, int64_t n, const AdamScalars& a, float l3_lambda,
+                        int zero_grad, cudaStream_t st);
+
+// K5
+size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter);
+cudaError_t launch_eval_rank(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
+                             const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                             const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
+                             int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes,
+                             cudaStream_t st);
+
+}  // namespace kge

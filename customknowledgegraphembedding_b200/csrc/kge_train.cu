@@ -1,0 +1,197 @@
+// Fused train step: both score passes, loss, backward and dense Adam enqueued by ONE C-ABI call on one
+// stream, nothing returning to the host in between.
+//
+// Replaces the body of KGEModel.train_step and of Trainer.train_step_fn
+// (/root/reference/tensorflow_codes/supervisor.py:15-28).
+//
+// Workspace carve (256-byte aligned regions):
+//   [host-batch only] positive i64[B,3] | negative i64[B,N] | weight f32[B]
+//   score_neg f32[B,N] | score_pos f32[B] | dneg f32[B,N] | dpos f32[B]
+//   loss scratch f32[2B+8] | l3 scratch f32[1024] | small f32[16] (loss3, reg sums, grad_modulus)
+//   grad_entity f32[E,De] | grad_relation f32[R,Dr]   (dense, as .grad in the reference)
+//   deterministic-backward scratch
+#include "kge_train.h"
+
+namespace kge {
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct TrainWs {
+    int64_t* pos;
+    int64_t* neg;
+    float* w;
+    float *score_neg, *score_pos, *dneg, *dpos, *loss_ws, *l3_ws, *small, *grad_ent, *grad_rel;
+    void* det_ws;
+    size_t det_bytes;
+    size_t total;
+};
+
+static TrainWs carve(const Params& P, int64_t B, int64_t N, bool host_batch, void* base) {
+    TrainWs w{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        void* p = base ? (void*)((char*)base + off) : nullptr;
+        off += align256(bytes);
+        return p;
+    };
+    if (host_batch) {
+        w.pos = (int64_t*)take((size_t)B * 3 * sizeof(int64_t));
+        w.neg = (int64_t*)take((size_t)B * N * sizeof(int64_t));
+        w.w = (float*)take((size_t)B * sizeof(float));
+    }
+    w.score_neg = (float*)take((size_t)B * N * sizeof(float));
+    w.score_pos = (float*)take((size_t)B * sizeof(float));
+    w.dneg = (float*)take((size_t)B * N * sizeof(float));
+    w.dpos = (float*)take((size_t)B * sizeof(float));
+    w.loss_ws = (float*)take(loss_workspace_bytes(B));
+    w.l3_ws = (float*)take(1024 * sizeof(float));
+    w.small = (float*)take(16 * sizeof(float));
+    w.grad_ent = (float*)take((size_t)P.E * P.De * sizeof(float));
+    w.grad_rel = (float*)take((size_t)P.R * P.Dr * sizeof(float));
+    w.det_bytes = backward_det_workspace_bytes(P, B, N);
+    w.det_ws = take(w.det_bytes);
+    w.total = off;
+    return w;
+}
+
+size_t train_step_workspace_bytes(const Params& P, int64_t B, int64_t N, bool host_batch) {
+    return carve(P, B, N, host_batch, nullptr).total;
+}
+
+// small[0..2] = loss3 ; small[3] = reg ; small[4] = sum|E|^3 ; small[5] = sum|R|^3 ; small[8] = grad_modulus
+__global__ void finalize_reg_kernel(float* small, float lambda) {
+    const float reg = lambda * (small[4] + small[5]);
+    small[3] = reg;
+    small[2] += reg;
+}
+
+static int train_step_device(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                             float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod, const int64_t* pos,
+                             const int64_t* neg, const float* w, int64_t B, int64_t N, const kge_loss_opts& lo,
+                             const kge_adam_opts& ao, int deterministic, const TrainWs& ws, cudaStream_t st) {
+    cudaError_t e;
+#define KGE_TRY(expr, what)                            \
+    do {                                               \
+        e = (expr);                                    \
+        if (e != cudaSuccess) return fail_cuda(e, what); \
+    } while (0)
+    KGE_TRY(cudaMemsetAsync(ws.grad_ent, 0, (size_t)P.E * P.De * sizeof(float), st), "memset grad_entity");
+    KGE_TRY(cudaMemsetAsync(ws.grad_rel, 0, (size_t)P.R * P.Dr * sizeof(float), st), "memset grad_relation");
+    KGE_TRY(cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st), "memset small");
+    KGE_TRY(launch_score_forward(P, mode, ent, rel, modulus, pos, neg, B, N, ws.score_neg, st), "forward(neg)");
+    KGE_TRY(launch_score_forward(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.score_pos, st),
+            "forward(pos)");
+    KGE_TRY(launch_loss(ws.score_neg, ws.score_pos, w, B, N, lo, ws.small, ws.dneg, ws.dpos, ws.loss_ws, st), "loss");
+    float* gmod = (P.model == KGE_PROTATE) ? ws.small + 8 : nullptr;
+    if (deterministic) {
+        KGE_TRY(launch_score_backward_det(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
+                                          ws.grad_rel, gmod, ws.det_ws, ws.det_bytes, st),
+                "backward_det(neg)");
+        KGE_TRY(launch_score_backward_det(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.dpos,
+                                          ws.grad_ent, ws.grad_rel, gmod, ws.det_ws, ws.det_bytes, st),
+                "backward_det(pos)");
+    } else {
+        KGE_TRY(launch_score_backward_atomic(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
+                                             ws.grad_rel, gmod, st),
+                "backward(neg)");
+        KGE_TRY(launch_score_backward_atomic(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.dpos,
+                                             ws.grad_ent, ws.grad_rel, gmod, st),
+                "backward(pos)");
+    }
+    float l3 = 0.f;
+    if (lo.regularization != 0.f) {
+        l3 = lo.regularization;
+        KGE_TRY(launch_l3_sum_cubes(ent, (int64_t)P.E * P.De, ws.small + 4, ws.l3_ws, st), "l3(entity)");
+        KGE_TRY(launch_l3_sum_cubes(rel, (int64_t)P.R * P.Dr, ws.small + 5, ws.l3_ws, st), "l3(relation)");
+        finalize_reg_kernel<<<1, 1, 0, st>>>(ws.small, l3);
+        KGE_TRY(cudaGetLastError(), "finalize_reg");
+    }
+    const AdamScalars a = adam_scalars(ao);
+    KGE_TRY(launch_adam(ent, ws.grad_ent, m_ent, v_ent, (int64_t)P.E * P.De, a, l3, 0, st), "adam(entity)");
+    KGE_TRY(launch_adam(rel, ws.grad_rel, m_rel, v_rel, (int64_t)P.R * P.Dr, a, l3, 0, st), "adam(relation)");
+    if (P.model == KGE_PROTATE) KGE_TRY(launch_adam(modulus, gmod, m_mod, v_mod, 1, a, 0.f, 0, st), "adam(modulus)");
+#undef KGE_TRY
+    return KGE_OK;
+}
+
+static int check_train_args(const kge_model_desc* desc, Params* P, int mode, const void* ent, const void* rel,
+                            const void* modulus, const void* m_ent, const void* v_ent, const void* m_rel,
+                            const void* v_rel, const void* m_mod, const void* v_mod, const void* pos, const void* neg, const void* w,
+                            int64_t B, int64_t N, const kge_loss_opts* lo, const kge_adam_opts* ao) {
+    int rc = make_params(desc, P);
+    if (rc) return rc;
+    if (mode != KGE_MODE_HEAD_BATCH && mode != KGE_MODE_TAIL_BATCH)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "negative batch mode %d not supported", mode);
+    if (B <= 0 || N <= 0) return fail(KGE_ERR_INVALID_ARGUMENT, "B and N must be positive");
+    if (!ent || !rel || !m_ent || !v_ent || !m_rel || !v_rel || !pos || !neg || !lo || !ao)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if (!lo->uni_weight && !w) return fail(KGE_ERR_INVALID_ARGUMENT, "subsampling_weight is NULL without uni_weight");
+    if (P->model == KGE_PROTATE && (!modulus || !m_mod || !v_mod))
+        return fail(KGE_ERR_INVALID_ARGUMENT, "pRotatE needs modulus and its Adam state");
+    if (ao->step < 1) return fail(KGE_ERR_INVALID_ARGUMENT, "adam step must be >= 1");
+    return KGE_OK;
+}
+
+}  // namespace kge
+
+using namespace kge;
+
+extern "C" {
+
+int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
+                   float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
+                   float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive, const int64_t* negative,
+                   const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
+                   const kge_adam_opts* adam_opts, int deterministic, float* loss3, float* reg1, void* ws,
+                   size_t ws_bytes, void* stream) {
+    Params P;
+    int rc = check_train_args(desc, &P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity,
+                              adam_m_relation, adam_v_relation, adam_m_modulus, adam_v_modulus, positive, negative,
+                              subsampling_weight, B, N, loss_opts, adam_opts);
+    if (rc) return rc;
+    if (!loss3) return fail(KGE_ERR_INVALID_ARGUMENT, "loss3 is NULL");
+    const size_t need = train_step_workspace_bytes(P, B, N, false);
+    if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "train step needs %zu workspace bytes, got %zu", need, ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    const TrainWs w = carve(P, B, N, false, ws);
+    rc = train_step_device(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                           adam_v_relation, adam_m_modulus, adam_v_modulus, positive, negative, subsampling_weight, B, N, *loss_opts,
+                           *adam_opts, deterministic, w, st);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpyAsync(loss3, w.small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, w.small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step(copy loss)");
+}
+
+int kge_train_step_host(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
+                        float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
+                        float* adam_m_modulus, float* adam_v_modulus, const int64_t* host_positive, const int64_t* host_negative,
+                        const float* host_subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
+                        const kge_adam_opts* adam_opts, int deterministic, float* host_loss4, void* ws,
+                        size_t ws_bytes, void* stream) {
+    Params P;
+    int rc = check_train_args(desc, &P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity,
+                              adam_m_relation, adam_v_relation, adam_m_modulus, adam_v_modulus, host_positive, host_negative,
+                              host_subsampling_weight, B, N, loss_opts, adam_opts);
+    if (rc) return rc;
+    if (!host_loss4) return fail(KGE_ERR_INVALID_ARGUMENT, "host_loss4 is NULL");
+    const size_t need = train_step_workspace_bytes(P, B, N, true);
+    if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "train step needs %zu workspace bytes, got %zu", need, ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    const TrainWs w = carve(P, B, N, true, ws);
+    cudaError_t e = cudaMemcpyAsync(w.pos, host_positive, (size_t)B * 3 * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(w.neg, host_negative, (size_t)B * N * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && host_subsampling_weight)
+        e = cudaMemcpyAsync(w.w, host_subsampling_weight, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return fail_cuda(e, "kge_train_step_host(H2D)");
+    rc = train_step_device(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                           adam_v_relation, adam_m_modulus, adam_v_modulus, w.pos, w.neg, host_subsampling_weight ? w.w : nullptr, B,
+                           N, *loss_opts, *adam_opts, deterministic, w, st);
+    if (rc) return rc;
+    e = cudaMemcpyAsync(host_loss4, w.small, 4 * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step_host(D2H)");
+}
+
+}  // extern "C"

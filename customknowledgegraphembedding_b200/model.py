@@ -1,0 +1,342 @@
+"""``KGEModel`` -- drop-in for the PyTorch ``codes/model.py::KGEModel`` of the KnowledgeGraphEmbedding
+codes the reference wraps (absent submodule @2e440e0f), extended with the
+reference's own InterHT score function and ``-tr`` flag (/root/reference/tensorflow_codes/model.py:49-112,
+207-224).  Same constructor, ``forward(sample, mode)``, static ``train_step`` / ``test_step`` and
+parameter names (``entity_embedding``, ``relation_embedding``, ``gamma``, ``embedding_range``,
+``modulus`` -- the naming contract of /root/reference/Checker/copy_weights.py:9-10).
+
+All arithmetic runs in the hand-written sm_100a kernels of ``libkge_b200.so``; torch provides device
+memory, streams and the autograd graph edge.  There is no CPU path: a model left on the CPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib, ops
+from ._lib import AdamOpts, LossOpts
+
+MODEL_NAMES = ("TransE", "DistMult", "ComplEx", "RotatE", "pRotatE", "InterHT")
+
+
+class _ScoreFunction(torch.autograd.Function):
+    """scores = K1(entity, relation, modulus; sample, mode);  backward = K3 into dense gradients."""
+
+    @staticmethod
+    def forward(ctx, entity, relation, modulus, positive, negative, desc, mode, deterministic):
+        mod = modulus if modulus is not None and modulus.numel() else None
+        scores = ops.score_forward(desc, mode, entity.detach(), relation.detach(),
+                                   None if mod is None else mod.detach(), positive, negative)
+        ctx.save_for_backward(entity, relation, modulus, positive, negative)
+        ctx.desc, ctx.mode, ctx.deterministic, ctx.has_mod = desc, mode, deterministic, mod is not None
+        return scores
+
+    @staticmethod
+    def backward(ctx, dscore):
+        entity, relation, modulus, positive, negative = ctx.saved_tensors
+        g_ent = torch.zeros_like(entity)
+        g_rel = torch.zeros_like(relation)
+        g_mod = torch.zeros_like(modulus) if ctx.has_mod else None
+        ops.score_backward(ctx.desc, ctx.mode, entity.detach(), relation.detach(),
+                           modulus.detach() if ctx.has_mod else None, positive, negative,
+                           dscore.contiguous(), g_ent, g_rel, g_mod, deterministic=ctx.deterministic)
+        return g_ent, g_rel, g_mod, None, None, None, None, None
+
+
+class KGEModel(nn.Module):
+    def __init__(self, model_name, nentity, nrelation, hidden_dim, gamma,
+                 double_entity_embedding=False, double_relation_embedding=False,
+                 triple_relation_embedding=False):
+        super().__init__()
+        self.model_name = model_name
+        self.nentity = nentity
+        self.nrelation = nrelation
+        self.hidden_dim = hidden_dim
+        self.epsilon = 2.0
+
+        self.gamma = nn.Parameter(torch.Tensor([gamma]), requires_grad=False)
+        self.embedding_range = nn.Parameter(
+            torch.Tensor([(self.gamma.item() + self.epsilon) / hidden_dim]), requires_grad=False)
+
+        self.entity_dim = hidden_dim * 2 if double_entity_embedding else hidden_dim
+        self.relation_dim = hidden_dim * 2 if double_relation_embedding else hidden_dim
+        if triple_relation_embedding:  # tensorflow_codes/model.py:75-78
+            self.relation_dim = hidden_dim * 3
+
+        self.entity_embedding = nn.Parameter(torch.zeros(nentity, self.entity_dim))
+        nn.init.uniform_(tensor=self.entity_embedding, a=-self.embedding_range.item(), b=self.embedding_range.item())
+        self.relation_embedding = nn.Parameter(torch.zeros(nrelation, self.relation_dim))
+        nn.init.uniform_(tensor=self.relation_embedding, a=-self.embedding_range.item(), b=self.embedding_range.item())
+
+        if model_name == "pRotatE":
+            self.modulus = nn.Parameter(torch.Tensor([[0.5 * self.embedding_range.item()]]))
+
+        # Do not forget to modify this line when you add a new model in the "forward" function
+        if model_name not in MODEL_NAMES:
+            raise ValueError("model %s not supported" % model_name)
+        if model_name == "RotatE" and (not double_entity_embedding or double_relation_embedding):
+            raise ValueError("RotatE should use --double_entity_embedding")
+        if model_name == "ComplEx" and (not double_entity_embedding or not double_relation_embedding):
+            raise ValueError("ComplEx should use --double_entity_embedding and --double_relation_embedding")
+        if model_name == "InterHT" and (not double_entity_embedding or not triple_relation_embedding):
+            raise ValueError("InterHT should use --double_entity_embedding and --triple_relation_embedding")
+
+        # B200 knobs (not in the reference API)
+        self.deterministic = False  # fixed-order backward (exact-check runs)
+        self.interht_eps = 0.0      # 0: tf.linalg.normalize; 1e-12: F.normalize
+        self._ws: Dict[tuple, torch.Tensor] = {}
+        self._filter_cache = None
+        self.last_eval = {}
+
+    # ------------------------------------------------------------------------------------
+    def _desc(self):
+        return ops.make_desc(self.model_name, self.nentity, self.nrelation, self.hidden_dim, self.entity_dim,
+                             self.relation_dim, self.gamma.item(), self.embedding_range.item(), self.interht_eps)
+
+    def _modulus(self) -> Optional[torch.Tensor]:
+        return self.modulus if self.model_name == "pRotatE" else None
+
+    def _workspace(self, kind: int, B: int, N: int) -> torch.Tensor:
+        dev = self.entity_embedding.device
+        need = ops.workspace_bytes(kind, self._desc(), B, N)
+        key = (kind, dev)
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < need:
+            ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            self._ws[key] = ws
+        return ws
+
+    def forward(self, sample, mode="single"):
+        """Raw scores ``[B,1]`` ('single') or ``[B,N]`` ('head-batch' / 'tail-batch') -- U2."""
+        if mode == "single":
+            positive, negative = sample, None
+        elif mode in ("head-batch", "tail-batch"):
+            positive, negative = sample
+        else:
+            raise ValueError("mode %s not supported" % mode)
+        dev = self.entity_embedding.device
+        if dev.type != "cuda":
+            raise RuntimeError("KGEModel is on %s: the B200 kernels need the model on a CUDA device "
+                               "(no CPU fallback)" % dev)
+        positive = positive.to(dev, non_blocking=True)
+        if negative is not None:
+            negative = negative.to(dev, non_blocking=True)
+        mod = self._modulus()
+        return _ScoreFunction.apply(self.entity_embedding, self.relation_embedding,
+                                    mod if mod is not None else torch.empty(0, device=dev),
+                                    positive.contiguous(), None if negative is None else negative.contiguous(),
+                                    self._desc(), mode, self.deterministic)
+
+    # ------------------------------------------------------------------------------------
+    # train_step (U9; loss body restated by the reference at tensorflow_codes/model.py:4-44)
+    # ------------------------------------------------------------------------------------
+    def _fused_adam_plan(self, optimizer):
+        """The fused K1-K4 step applies when `optimizer` is plain Adam over exactly this model's trainable
+        parameters (what the upstream run.py builds).  Returns the param group or None."""
+        from .optim import FusedAdam
+        if not isinstance(optimizer, (torch.optim.Adam, FusedAdam)) or len(optimizer.param_groups) != 1:
+            return None
+        g = optimizer.param_groups[0]
+        if g.get("amsgrad") or g.get("weight_decay", 0) != 0 or g.get("maximize") or g.get("differentiable"):
+            return None
+        mine = [p for p in self.parameters() if p.requires_grad]
+        if len(g["params"]) != len(mine) or any(a is not b for a, b in zip(sorted(g["params"], key=id), sorted(mine, key=id))):
+            return None
+        return g
+
+    @staticmethod
+    def _adam_state(optimizer, p):
+        st = optimizer.state[p]
+        if len(st) == 0:  # same layout torch.optim.Adam creates lazily
+            st["step"] = torch.tensor(0.0, dtype=torch.float32)
+            st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        return st
+
+    @staticmethod
+    def train_step(model, optimizer, train_iterator, args):
+        """A single train step: apply back-propagation and return the loss log (same keys as upstream)."""
+        model.train()
+        positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
+        if mode not in ("head-batch", "tail-batch"):
+            raise ValueError("mode %s not supported" % mode)
+        adv = bool(getattr(args, "negative_adversarial_sampling", False))
+        alpha = float(getattr(args, "adversarial_temperature", 1.0))
+        uni = bool(getattr(args, "uni_weight", False))
+        reg = float(getattr(args, "regularization", 0.0))
+        dev = model.entity_embedding.device
+        if dev.type != "cuda":
+            raise RuntimeError("KGEModel.train_step: model is on %s; move it to a CUDA device (no CPU fallback)" % dev)
+
+        group = model._fused_adam_plan(optimizer)
+        if group is None:
+            return model._train_step_generic(optimizer, positive_sample, negative_sample, subsampling_weight, mode,
+                                             adv, alpha, uni, reg)
+
+        lib = _lib.load()
+        B, N = negative_sample.shape
+        ent, rel, mod = model.entity_embedding, model.relation_embedding, model._modulus()
+        st_e, st_r = model._adam_state(optimizer, ent), model._adam_state(optimizer, rel)
+        st_m = model._adam_state(optimizer, mod) if mod is not None else None
+        states = [s for s in (st_e, st_r, st_m) if s is not None]
+        for s in states:
+            s["step"] += 1
+        step = int(st_e["step"])
+        beta1, beta2 = group["betas"]
+        adam = AdamOpts(float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), step, 0)
+        loss_opts = LossOpts(int(adv), int(uni), 1, 0, alpha, reg)
+        desc = model._desc()
+        host_batch = not positive_sample.is_cuda
+        P = ops._ptr
+        common_state = (P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]), P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]),
+                        P(st_m["exp_avg"]) if st_m else None, P(st_m["exp_avg_sq"]) if st_m else None)
+        with torch.cuda.device(dev):
+            stream = ops._stream()
+            if host_batch:
+                pos = positive_sample.contiguous()
+                neg = negative_sample.contiguous()
+                w = None if uni else subsampling_weight.to(torch.float32).contiguous()
+                if pos.dtype != torch.int64 or neg.dtype != torch.int64:
+                    raise TypeError("positive_sample / negative_sample must be int64")
+                ws = model._workspace(_lib.WS_TRAIN_STEP_HOST, B, N)
+                out = np.empty(4, dtype=np.float32)
+                _lib.check(lib.kge_train_step_host(
+                    C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state,
+                    C.c_void_p(pos.data_ptr()), C.c_void_p(neg.data_ptr()),
+                    None if w is None else C.c_void_p(w.data_ptr()), B, N, C.byref(loss_opts), C.byref(adam),
+                    int(model.deterministic), out.ctypes.data_as(C.c_void_p), P(ws), ws.numel(), stream),
+                    "kge_train_step_host")
+                pos_l, neg_l, loss, regv = (float(x) for x in out)
+            else:
+                pos = ops._need_cuda("positive_sample", positive_sample, torch.int64)
+                neg = ops._need_cuda("negative_sample", negative_sample, torch.int64)
+                w = None if uni else ops._need_cuda("subsampling_weight", subsampling_weight.to(dev), torch.float32)
+                ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
+                out = torch.empty(4, dtype=torch.float32, device=dev)
+                _lib.check(lib.kge_train_step(
+                    C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(pos), P(neg), P(w),
+                    B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out),
+                    C.c_void_p(out.data_ptr() + 12), P(ws), ws.numel(), stream), "kge_train_step")
+                pos_l, neg_l, loss, regv = out.tolist()
+        log = {"regularization": regv} if reg != 0.0 else {}
+        log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
+        return log
+
+    def _train_step_generic(self, optimizer, positive_sample, negative_sample, subsampling_weight, mode,
+                            adv, alpha, uni, reg):
+        """Any other optimizer: K1 forward, K2 loss, K3 backward into .grad, then optimizer.step()."""
+        dev = self.entity_embedding.device
+        optimizer.zero_grad()
+        positive_sample = positive_sample.to(dev)
+        negative_sample = negative_sample.to(dev)
+        subsampling_weight = subsampling_weight.to(dev)
+        negative_score = self((positive_sample, negative_sample), mode=mode)
+        positive_score = self(positive_sample)
+        loss3, dneg, dpos = ops.loss_forward_backward(
+            negative_score.detach(), positive_score.detach(), subsampling_weight,
+            negative_adversarial_sampling=adv, adversarial_temperature=alpha, uni_weight=uni)
+        torch.autograd.backward([negative_score, positive_score], [dneg, dpos.view(-1, 1)])
+        pos_l, neg_l, loss = loss3.tolist()
+        log = {}
+        if reg != 0.0:
+            regv = reg * (ops.l3_sum_cubes(self.entity_embedding.detach())
+                          + ops.l3_sum_cubes(self.relation_embedding.detach())).item()
+            with torch.no_grad():
+                for p in (self.entity_embedding, self.relation_embedding):
+                    p.grad.add_(3.0 * reg * p * p.abs())
+            loss += regv
+            log["regularization"] = regv
+        optimizer.step()
+        log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
+        return log
+
+    # ------------------------------------------------------------------------------------
+    # test_step (U10): filtered full-entity ranking, rank by counting instead of argsort
+    # ------------------------------------------------------------------------------------
+    def _filter_maps(self, all_true_triples):
+        """Sorted (r,t)->heads and (h,r)->tails tables over the unique true triples, built once per list."""
+        key = (id(all_true_triples), len(all_true_triples))
+        if self._filter_cache is not None and self._filter_cache[0] == key:
+            return self._filter_cache[1]
+        A = np.unique(np.asarray(all_true_triples, dtype=np.int64).reshape(-1, 3), axis=0)
+        E = np.int64(self.nentity)
+        maps = {}
+        for mode, kcols, vcol in (("head-batch", (1, 2), 0), ("tail-batch", (1, 0), 2)):
+            k = A[:, kcols[0]] * E + A[:, kcols[1]]
+            order = np.argsort(k, kind="stable")
+            maps[mode] = (k[order], A[order, vcol])
+        self._filter_cache = (key, maps)
+        return maps
+
+    @staticmethod
+    def build_filter_csr(maps, queries: np.ndarray, mode: str, nentity: int):
+        """CSR (indptr [Q+1], idx) of the candidate ids upstream's TestDataset gives bias -1 for each query."""
+        keys, vals = maps[mode]
+        E = np.int64(nentity)
+        other = queries[:, 2] if mode == "head-batch" else queries[:, 0]
+        qk = queries[:, 1] * E + other
+        lo = np.searchsorted(keys, qk, side="left")
+        hi = np.searchsorted(keys, qk, side="right")
+        lens = hi - lo
+        indptr = np.zeros(len(queries) + 1, dtype=np.int64)
+        np.cumsum(lens, out=indptr[1:])
+        total = int(indptr[-1])
+        if total == 0:
+            return indptr, np.zeros(0, dtype=np.int64)
+        pos_in = np.arange(total, dtype=np.int64) - np.repeat(indptr[:-1], lens)
+        idx = vals[np.repeat(lo, lens) + pos_in]
+        return indptr, idx.astype(np.int64, copy=False)
+
+    @torch.no_grad()
+    def rank_queries(self, queries: torch.Tensor, mode: str, filter_indptr=None, filter_idx=None,
+                     entity_lo: int = 0, entity_hi: Optional[int] = None):
+        """(true_score, n_greater, n_equal) for a [Q,3] int64 query tensor (any device) -- thin K5 call."""
+        dev = self.entity_embedding.device
+        entity_hi = self.nentity if entity_hi is None else entity_hi
+        to = lambda t: None if t is None else t.to(dev, non_blocking=True)
+        return ops.eval_rank(self._desc(), mode, self.entity_embedding.detach(), self.relation_embedding.detach(),
+                             None if self._modulus() is None else self._modulus().detach(), to(queries),
+                             entity_lo, entity_hi, to(filter_indptr), to(filter_idx))
+
+    @staticmethod
+    def test_step(model, test_triples, all_true_triples, args):
+        """Evaluate the model on test or valid datasets: filtered MRR / MR / HITS@1,3,10 over
+        head-batch then tail-batch queries (same query order and metric arithmetic as upstream)."""
+        model.eval()
+        if getattr(args, "countries", False):
+            raise NotImplementedError("--countries AUC-PR evaluation is outside the B200 hot path (SURVEY 8(f) N4)")
+        dev = model.entity_embedding.device
+        if dev.type != "cuda":
+            raise RuntimeError("KGEModel.test_step: model is on %s; move it to a CUDA device (no CPU fallback)" % dev)
+        nentity = getattr(args, "nentity", None) or model.nentity
+        T = np.asarray(test_triples, dtype=np.int64).reshape(-1, 3)
+        maps = model._filter_maps(all_true_triples)
+        chunk = int(getattr(model, "eval_chunk", 4096))
+        ranks, ties = [], 0
+        for mode in ("head-batch", "tail-batch"):
+            for lo in range(0, len(T), chunk):
+                q = T[lo:lo + chunk]
+                indptr, idx = KGEModel.build_filter_csr(maps, q, mode, nentity)
+                _, n_greater, n_equal = model.rank_queries(torch.from_numpy(q), mode, torch.from_numpy(indptr),
+                                                           torch.from_numpy(idx))
+                ranks.append((1 + n_greater).cpu().numpy())
+                ties += int(n_equal.sum().item())
+        ranks = np.concatenate(ranks) if ranks else np.zeros(0, dtype=np.int64)
+        model.last_eval = {"ranks": ranks, "n_tied_candidates": ties}
+        if ties:
+            logging.warning("test_step: %d candidates tie exactly with a true score; ranks are 1 + #greater", ties)
+        # upstream: per-query logs, then sum(...) / len(...) in query order with Python floats
+        sums = {"MRR": 0.0, "MR": 0.0, "HITS@1": 0.0, "HITS@3": 0.0, "HITS@10": 0.0}
+        for ranking in ranks.tolist():
+            sums["MRR"] += 1.0 / ranking
+            sums["MR"] += float(ranking)
+            sums["HITS@1"] += 1.0 if ranking <= 1 else 0.0
+            sums["HITS@3"] += 1.0 if ranking <= 3 else 0.0
+            sums["HITS@10"] += 1.0 if ranking <= 10 else 0.0
+        n = max(len(ranks), 1)
+        return {k: v / n for k, v in sums.items()}

@@ -1,0 +1,219 @@
+/*
+ * kge_b200.h -- C-ABI of the B200-native KGE hot path (libkge_b200.so, sm_100a).
+ *
+ * Drop-in boundary for the data-parallel hot path of
+ * NguyenThaiHoc1/CustomKnowledgeGraphEmbedding.  The reference has no native code and
+ * therefore no FFI of its own; each entry point below names the reference *Python*
+ * interface whose body it replaces (paths relative to /root/reference; "U<n>" rows are
+ * the absent PyTorch submodule KnowledgeGraphEmbedding@2e440e0f).
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - plain C: pointers + sizes; no torch / C++ types.  `stream` is a cudaStream_t passed
+ *     as void* (NULL = legacy default stream).
+ *   - all table / score pointers are DEVICE pointers to contiguous row-major fp32;
+ *     indices are int64 at the boundary (as torch.LongTensor / tf.int64).  Entry points
+ *     whose name ends in `_host` take HOST pointers for the per-step batch and do the
+ *     H2D / D2H copies themselves.
+ *   - the caller owns every buffer; nothing here allocates except through the caller's
+ *     workspace (`ws`, `ws_bytes`; size it with kge_workspace_bytes()).
+ *   - return value: 0 = ok, negative = kge_status; kge_last_error() gives the message
+ *     (thread-local).  Kernels are enqueued asynchronously; CUDA launch errors are
+ *     reported by the call that made them.
+ *   - indices are not range-checked on the device (as tf.gather on GPU); the Python host
+ *     layer checks them where the reference's index_select would raise.
+ */
+#ifndef KGE_B200_H
+#define KGE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGE_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define KGE_API __attribute__((visibility("default")))
+#else
+#define KGE_API
+#endif
+
+typedef enum {
+    KGE_OK = 0,
+    KGE_ERR_INVALID_ARGUMENT = -1, /* bad enum / size / NULL pointer / dims the model forbids */
+    KGE_ERR_WORKSPACE = -2,        /* workspace missing or too small */
+    KGE_ERR_CUDA = -3,             /* a CUDA runtime call or launch failed */
+    KGE_ERR_UNSUPPORTED = -4
+} kge_status;
+
+/* score functions: U3-U7 (TransE..pRotatE) and tensorflow_codes/model.py:207-224 (InterHT) */
+typedef enum {
+    KGE_TRANSE = 0,
+    KGE_DISTMULT = 1,
+    KGE_COMPLEX = 2,
+    KGE_ROTATE = 3,
+    KGE_PROTATE = 4,
+    KGE_INTERHT = 5
+} kge_model_id;
+
+/* KGEModel.forward modes (U2).  The TF wire ints 0 = head-batch, 1 = tail-batch, 3 = single
+ * (compress_data/main.py:65,69; supervisor.py:18) are mapped by the host layer. */
+typedef enum {
+    KGE_MODE_SINGLE = 0,
+    KGE_MODE_HEAD_BATCH = 1,
+    KGE_MODE_TAIL_BATCH = 2
+} kge_mode;
+
+/* What KGEModel.__init__ fixes (U1; tensorflow_codes/model.py:49-112). */
+typedef struct {
+    int32_t model;         /* kge_model_id */
+    int32_t hidden_dim;    /* H */
+    int32_t entity_dim;    /* De = H or 2H (-de) */
+    int32_t relation_dim;  /* Dr = H, 2H (-dr) or 3H (-tr) */
+    int64_t nentity;       /* E: rows of the entity table this pointer addresses */
+    int64_t nrelation;     /* R */
+    float gamma;           /* margin */
+    float embedding_range; /* (gamma + 2) / H, as fp32 */
+    float interht_eps;     /* 0 = tf.linalg.normalize (model.py:215-218); 1e-12 = F.normalize */
+    int32_t reserved;
+} kge_model_desc;
+
+/* Loss options of train_step (U9; tensorflow_codes/model.py:4-44; supervisor.py:19-23). */
+typedef struct {
+    int32_t negative_adversarial_sampling; /* -adv */
+    int32_t uni_weight;                    /* --uni_weight */
+    int32_t detach_weights;                /* 1 = PyTorch (.detach()), 0 = TF graph model (model.py:168-171) */
+    int32_t reserved;
+    float adversarial_temperature;         /* -a */
+    float regularization;                  /* -r (L3), 0 = off */
+} kge_loss_opts;
+
+/* torch.optim.Adam defaults: lr, betas (.9,.999), eps 1e-8, eps inside the bias-corrected
+ * denominator.  keras_epsilon_mode = 1 gives tf.keras.optimizers.Adam (run.py:111):
+ * p -= lr*sqrt(1-b2^t)/(1-b1^t) * m / (sqrt(v) + eps). */
+typedef struct {
+    float lr;
+    float beta1;
+    float beta2;
+    float eps;
+    int32_t step; /* t >= 1: the step being applied */
+    int32_t keras_epsilon_mode;
+} kge_adam_opts;
+
+KGE_API const char *kge_last_error(void);
+KGE_API int kge_abi_version(void);
+
+/* Number of SMs / device name of the current device (diagnostics; bench.py). */
+KGE_API int kge_device_info(int *sm_count, int *cc_major, int *cc_minor, char *name, size_t name_len);
+
+/*
+ * K1  fused gather-and-score.  Replaces KGEModel.forward (U2-U8) and the gather + score part of
+ * TFKGEModel.call (tensorflow_codes/model.py:127-199).
+ *   mode SINGLE:      positive [B,3]                -> scores [B,1]   (negative ignored, N := 1)
+ *   mode HEAD_BATCH:  positive [B,3], negative [B,N] heads  -> scores [B,N]
+ *   mode TAIL_BATCH:  positive [B,3], negative [B,N] tails  -> scores [B,N]
+ * modulus: device pointer to the pRotatE modulus scalar (U7), NULL otherwise.
+ */
+KGE_API int kge_score_forward(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
+                      const float *modulus, const int64_t *positive, const int64_t *negative, int64_t B,
+                      int64_t N, float *scores, void *stream);
+
+/*
+ * K3  backward of K1: given dL/dscore [B,N] accumulate (+=) dL/dtable into dense grad tables
+ * (what loss.backward() leaves in .grad, U9; tape.gradient, supervisor.py:25).
+ *   deterministic = 0: warp-aggregated red.global.add (order of float adds not fixed)
+ *   deterministic = 1: occurrences of every row are reduced in a fixed order (needs workspace)
+ * grad_modulus: device scalar accumulated for pRotatE, NULL otherwise.
+ */
+KGE_API int kge_score_backward(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
+                       const float *modulus, const int64_t *positive, const int64_t *negative, int64_t B,
+                       int64_t N, const float *dscore, float *grad_entity, float *grad_relation,
+                       float *grad_modulus, int deterministic, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * K2  fused loss (U9 body; tensorflow_codes/model.py:12-31).  negative_score [B,N], positive_score [B]
+ * raw scores, subsampling_weight [B] (may be NULL iff uni_weight).  Writes
+ *   loss3 = {positive_sample_loss, negative_sample_loss, (pos+neg)/2}   (device, 3 floats)
+ * and, when non-NULL, dL/dscore into dneg [B,N], dpos [B] for loss = loss3[2].
+ * ws: B*2+8 floats of scratch.
+ */
+KGE_API int kge_loss_forward_backward(const float *negative_score, const float *positive_score,
+                              const float *subsampling_weight, int64_t B, int64_t N, const kge_loss_opts *opts,
+                              float *loss3, float *dneg, float *dpos, void *ws, size_t ws_bytes, void *stream);
+
+/* L3 regulariser value (tensorflow_codes/model.py:33-39): out[0] = sum |x|^3 over n elements (device
+ * scalar, overwritten).  ws: 1024 floats. */
+KGE_API int kge_l3_sum_cubes(const float *x, int64_t n, float *out, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * K4  fused dense Adam over one table (optimizer.step(), U9; apply_gradients, supervisor.py:26).
+ * g may be NULL (all-zero gradient).  l3_lambda != 0 adds d/dp lambda*|p|^3 = 3*lambda*p*|p| to g.
+ * zero_grad != 0 writes zeros back to g (optimizer.zero_grad() folded in).
+ */
+KGE_API int kge_adam_dense(float *p, float *g, float *m, float *v, int64_t n, const kge_adam_opts *opts, float l3_lambda,
+                   int zero_grad, void *stream);
+
+/*
+ * K5  filtered full-entity ranking.  Replaces the body of KGEModel.test_step (U10): for every query
+ * (triple, mode) score the candidates e in [entity_lo, entity_hi) of the table, skip the filtered
+ * candidates, and count  n_greater[q] = #{e != true : score_e >  score_true}
+ *                        n_equal[q]   = #{e != true : score_e == score_true}
+ * so that the reference's rank is 1 + n_greater (+ ties in [0, n_equal]).
+ *   queries [Q,3] int64; mode HEAD_BATCH or TAIL_BATCH for all Q
+ *   filter_indptr [Q+1], filter_idx: CSR of candidate ids to skip per query (global ids;
+ *     the true entity itself need not be listed).  NULL/NULL = raw (unfiltered) ranking.
+ *   entity points at row 0 of the FULL id space; rows outside [entity_lo, entity_hi) are not
+ *     read except the rows the queries name (h, t) unless `query_rows` is given.
+ *   true_score [Q]: written (accumulate = 0); counts are overwritten (accumulate = 0) or
+ *     added to (accumulate = 1, used when a shard is visited in several calls).
+ * ws: see kge_workspace_bytes(KGE_WS_EVAL, ...).
+ */
+KGE_API int kge_eval_rank(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
+                  const float *modulus, const int64_t *queries, int64_t Q, int64_t entity_lo, int64_t entity_hi,
+                  const int64_t *filter_indptr, const int64_t *filter_idx, float *true_score, int64_t *n_greater,
+                  int64_t *n_equal, int accumulate, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * Fused train step, tables and batch resident in HBM.  Replaces the body of KGEModel.train_step (U9) /
+ * Trainer.train_step_fn (supervisor.py:15-28): both score passes, the loss, the backward and dense Adam
+ * on both tables (+ the pRotatE modulus) in one call.  `mode` HEAD_BATCH or TAIL_BATCH.
+ *   adam_m_*, adam_v_*: optimizer state, same shapes as the parameters (modulus: 1 float each; NULL unless pRotatE).
+ *   loss3 (device, 3 floats): positive_sample_loss, negative_sample_loss, loss (+ reg4[0] when -r).
+ *   reg1 (device, 1 float, may be NULL when regularization == 0): the regularisation term.
+ */
+KGE_API int kge_train_step(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
+                   float *adam_m_entity, float *adam_v_entity, float *adam_m_relation, float *adam_v_relation,
+                   float *adam_m_modulus, float *adam_v_modulus, const int64_t *positive, const int64_t *negative,
+                   const float *subsampling_weight, int64_t B, int64_t N, const kge_loss_opts *loss_opts,
+                   const kge_adam_opts *adam_opts, int deterministic, float *loss3, float *reg1, void *ws,
+                   size_t ws_bytes, void *stream);
+
+/* Same step with the batch in HOST memory (pinned for async copies): copies positive / negative /
+ * weights H2D into the workspace, runs kge_train_step, copies loss3 (+reg) back to host_loss4 and
+ * synchronises the stream.  This is the end-to-end call bench.py times as `e2e`. */
+KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
+                        float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
+                        float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus, const int64_t *host_positive,
+                        const int64_t *host_negative, const float *host_subsampling_weight, int64_t B, int64_t N,
+                        const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts, int deterministic,
+                        float *host_loss4, void *ws, size_t ws_bytes, void *stream);
+
+typedef enum {
+    KGE_WS_BACKWARD = 0, /* kge_score_backward (deterministic) */
+    KGE_WS_LOSS = 1,
+    KGE_WS_EVAL = 2,
+    KGE_WS_TRAIN_STEP = 3,
+    KGE_WS_TRAIN_STEP_HOST = 4
+} kge_ws_kind;
+
+/* Bytes of workspace the call of that kind needs for (desc, B, N) -- for KGE_WS_EVAL pass Q as B and the
+ * total filter length as N. */
+KGE_API size_t kge_workspace_bytes(int kind, const kge_model_desc *desc, int64_t B, int64_t N);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGE_B200_H */

@@ -1,0 +1,61 @@
+"""CPU: the C-ABI library loads and exports every symbol include/kge_b200.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(REPO, "include", "kge_b200.h")).read()
+    return sorted(set(re.findall(r"KGE_API\s+[\w\s\*]+?\b(kge_\w+)\s*\(", text)))
+
+
+def test_header_declares_entry_points():
+    names = _declared()
+    for must in ("kge_score_forward", "kge_score_backward", "kge_loss_forward_backward", "kge_adam_dense",
+                 "kge_eval_rank", "kge_train_step", "kge_train_step_host", "kge_last_error"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    from customknowledgegraphembedding_b200 import _lib, build
+    if not os.path.exists(_lib.LIB_PATH):
+        build.build()
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in _declared():
+        assert hasattr(lib, name), "libkge_b200.so does not export %s" % name
+        assert name in _lib.PROTOTYPES, "ctypes binding lacks %s" % name
+    assert set(_lib.PROTOTYPES) == set(_declared())
+
+
+def test_binding_loads_and_reports_abi():
+    from customknowledgegraphembedding_b200 import _lib
+    assert _lib.load().kge_abi_version() == _lib.ABI_VERSION
+
+
+def test_invalid_desc_is_value_error_without_gpu():
+    """Argument validation happens before any CUDA call, so it is checkable on the CPU box."""
+    from customknowledgegraphembedding_b200 import _lib, ops
+    lib = _lib.load()
+    desc = ops.make_desc("RotatE", 10, 2, 8, 8, 8, 9.0, 1.0)  # RotatE needs entity_dim = 2H
+    rc = lib.kge_score_forward(ctypes.byref(desc), 0, None, None, None, None, None, 1, 1, None, None)
+    assert rc == _lib.KGE_ERR_INVALID_ARGUMENT
+    with pytest.raises(ValueError):
+        _lib.check(rc)
+    assert ops.workspace_bytes(_lib.WS_TRAIN_STEP, ops.make_desc("TransE", 100, 3, 8, 8, 8, 12.0, 1.75), 4, 8) > 0
+
+
+def test_no_cpu_fallback():
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    m = kb.KGEModel("TransE", 10, 2, 8, 12.0)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError):
+            m(torch.zeros(2, 3, dtype=torch.int64))
+    # the product never imports the oracle
+    import sys
+    src = open(os.path.join(REPO, "customknowledgegraphembedding_b200", "model.py")).read()
+    assert "oracle" not in src and "oracle" not in open(os.path.join(REPO, "customknowledgegraphembedding_b200", "ops.py")).read()
