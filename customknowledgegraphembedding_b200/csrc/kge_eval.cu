@@ -1,10 +1,441 @@
-// K5 placeholder while the tiled ranking kernel is written (replaced in the next commit).
+// K5: filtered full-entity ranking by counting (sm_100a).
+//
+// Replaces the body of KGEModel.test_step: instead of materialising the [Q,E]
+// score matrix and arg-sorting it, every (query, candidate) score is produced inside a register
+// tile and immediately compared with the query's true score; only two integer counters per query
+// leave the SM.
+//
+//   1 stage      per query: the candidate-independent planes q (same maths as K1) -> workspace
+//   2 norms      InterHT only: 1/|a_e|, 1/|b_e| per entity
+//   3 true       per query: score of the true entity, accumulated k = 0..H-1 in order
+//   4 tile       128 queries x 128 entities per CTA, 8x8 scores per thread, coordinates streamed
+//                through shared memory in chunks of 16 (k-major, register-staged double buffer);
+//                epilogue counts score > true / score == true, skipping the true entity itself
+//   5 filter     per filtered (query, entity) pair: undo its contribution to the counters
+//
+// Bit-consistency: 3, 4 and 5 evaluate a pair with the SAME instruction sequence (explicit
+// round-to-nearest intrinsics, no contraction freedom) in the SAME order, so the true entity
+// scores exactly its true score inside the tile and a filtered entity is subtracted iff it was
+// counted.  This is what makes "rank = 1 + #greater" reproduce the reference's tie handling.
 #include "kge_internal.h"
+#include "kge_score.cuh"
+
 namespace kge {
-size_t eval_workspace_bytes(const Params&, int64_t, int64_t) { return 256; }
-cudaError_t launch_eval_rank(const Params&, int, const float*, const float*, const float*, const int64_t*, int64_t,
-                             int64_t, int64_t, const int64_t*, const int64_t*, float*, int64_t*, int64_t*, int, void*,
-                             size_t, cudaStream_t) {
-    return cudaErrorNotSupported;
+
+__host__ __device__ constexpr int cand_planes(int model) {
+    return (model == KGE_COMPLEX || model == KGE_ROTATE || model == KGE_INTERHT) ? 2 : 1;
 }
+
+struct EvalConsts {
+    float gamma, inv_phase_div, modulus;
+};
+
+// raw table values -> what the inner loop consumes
+template <int MODEL>
+__device__ __forceinline__ void prep_candidate(float& c0, float& c1, float x0, float x1, float inv_div, float ina,
+                                               float inb) {
+    if constexpr (MODEL == KGE_PROTATE) {
+        c0 = __fmul_rn(x0, inv_div);
+        c1 = 0.f;
+    } else if constexpr (MODEL == KGE_INTERHT) {
+        c0 = __fmul_rn(x0, ina);
+        c1 = __fadd_rn(__fmul_rn(x1, inb), 1.0f);
+    } else {
+        c0 = x0;
+        c1 = x1;
+    }
+}
+
+template <int MODEL, bool HEAD>
+__device__ __forceinline__ float accum(float acc, float q0, float q1, float q2, float c0, float c1) {
+    if constexpr (MODEL == KGE_TRANSE) {
+        return __fadd_rn(acc, fabsf(HEAD ? __fadd_rn(c0, q0) : __fsub_rn(q0, c0)));
+    } else if constexpr (MODEL == KGE_DISTMULT) {
+        return __fmaf_rn(q0, c0, acc);
+    } else if constexpr (MODEL == KGE_COMPLEX) {
+        return __fmaf_rn(q1, c1, __fmaf_rn(q0, c0, acc));
+    } else if constexpr (MODEL == KGE_ROTATE) {
+        const float vr = __fsub_rn(q0, c0), vi = __fsub_rn(q1, c1);
+        return __fadd_rn(acc, fast_sqrt(__fmaf_rn(vr, vr, __fmul_rn(vi, vi))));
+    } else if constexpr (MODEL == KGE_PROTATE) {
+        const float v = HEAD ? __fadd_rn(c0, q0) : __fsub_rn(q0, c0);
+        return __fadd_rn(acc, fabsf(sinf(v)));
+    } else {  // InterHT: q = (A, B+1, mid), c = (a_hat, b_hat + 1)
+        const float v = HEAD ? __fmaf_rn(c0, q1, __fmaf_rn(-q0, c1, q2)) : __fmaf_rn(q0, c1, __fmaf_rn(-c0, q1, q2));
+        return __fadd_rn(acc, fabsf(v));
+    }
+}
+
+template <int MODEL>
+__device__ __forceinline__ float finalize(float acc, const EvalConsts& c) {
+    if constexpr (MODEL == KGE_DISTMULT || MODEL == KGE_COMPLEX) return acc;
+    else if constexpr (MODEL == KGE_PROTATE) return __fsub_rn(c.gamma, __fmul_rn(acc, c.modulus));
+    else return __fsub_rn(c.gamma, acc);
+}
+
+// One thread, one (query, entity) pair, coordinates in ascending order: the reference order of K5.
+template <int MODEL, bool HEAD>
+__device__ __forceinline__ float pair_score_seq(const float* __restrict__ qrow, const float* __restrict__ erow, int H,
+                                                const EvalConsts& c, float ina, float inb) {
+    constexpr int QP = model_planes(MODEL), CP = cand_planes(MODEL);
+    float acc = 0.f;
+    for (int k = 0; k < H; ++k) {
+        const float q0 = qrow[k];
+        const float q1 = (QP > 1) ? qrow[H + k] : 0.f;
+        const float q2 = (QP > 2) ? qrow[2 * H + k] : 0.f;
+        const float x0 = __ldg(erow + k);
+        const float x1 = (CP > 1) ? __ldg(erow + H + k) : 0.f;
+        float c0, c1;
+        prep_candidate<MODEL>(c0, c1, x0, x1, c.inv_phase_div, ina, inb);
+        acc = accum<MODEL, HEAD>(acc, q0, q1, q2, c0, c1);
+    }
+    return finalize<MODEL>(acc, c);
+}
+
+// ---- 1 stage ---------------------------------------------------------------------------------
+template <int MODEL>
+__global__ void __launch_bounds__(128)
+eval_stage_kernel(Params P, int head, const float* __restrict__ ent, const float* __restrict__ rel,
+                  const int64_t* __restrict__ queries, float* __restrict__ Qs) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int planes = model_planes(MODEL);
+    const int qdim = planes * P.H;
+    float* q = smem;
+    float* aux = q + qdim;
+    float* red = aux + 4;
+    const long long b = blockIdx.x;
+    stage_positive<MODEL>(q, aux, red, P, ent, rel, queries[3 * b], queries[3 * b + 1], queries[3 * b + 2], head != 0);
+    for (int k = threadIdx.x; k < qdim; k += blockDim.x) Qs[b * qdim + k] = q[k];
+}
+
+// ---- 2 norms (InterHT) -----------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+eval_inv_norm_kernel(Params P, const float* __restrict__ ent, float* __restrict__ ina, float* __restrict__ inb) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long e = warp; e < P.E; e += nw) {
+        const float* row = ent + e * (long long)P.De;
+        float sa = 0.f, sb = 0.f;
+        for (int k = lane; k < P.H; k += 32) {
+            const float a = __ldg(row + k), b = __ldg(row + P.H + k);
+            sa = fmaf(a, a, sa);
+            sb = fmaf(b, b, sb);
+        }
+        float na = sqrtf(warp_sum(sa)), nb = sqrtf(warp_sum(sb));
+        if (P.interht_eps > 0.f) {
+            na = fmaxf(na, P.interht_eps);
+            nb = fmaxf(nb, P.interht_eps);
+        }
+        if (lane == 0) {
+            ina[e] = 1.0f / na;
+            inb[e] = 1.0f / nb;
+        }
+    }
+}
+
+// ---- 3 true ----------------------------------------------------------------------------------
+template <int MODEL, bool HEAD>
+__global__ void __launch_bounds__(128)
+eval_true_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
+                 const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
+                 const int64_t* __restrict__ queries, long long Q, float* __restrict__ true_score) {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Q) return;
+    if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
+    const long long e = HEAD ? queries[3 * q] : queries[3 * q + 2];
+    const int qdim = model_planes(MODEL) * P.H;
+    const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
+    true_score[q] = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b);
+}
+
+// ---- 5 filter --------------------------------------------------------------------------------
+template <int MODEL, bool HEAD>
+__device__ __forceinline__ void filter_one(long long f, const Params& P, const EvalConsts& c, const float* __restrict__ ent,
+                   const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
+                   const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
+                   const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
+                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal);
+
+template <int MODEL, bool HEAD>
+__global__ void __launch_bounds__(128)
+eval_filter_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
+                   const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
+                   const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
+                   const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
+                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+    const long long total = indptr[Q];
+    if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
+    for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x)
+        filter_one<MODEL, HEAD>(f, P, c, ent, Qs, ina, inb, queries, Q, indptr, idx, e_lo, e_hi, true_score, n_greater, n_equal);
+}
+
+template <int MODEL, bool HEAD>
+__device__ __forceinline__ void filter_one(long long f, const Params& P, const EvalConsts& c, const float* __restrict__ ent,
+                   const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
+                   const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
+                   const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
+                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+    // query owning entry f: last q with indptr[q] <= f
+    long long lo = 0, hi = Q;
+    while (hi - lo > 1) {
+        const long long mid = (lo + hi) >> 1;
+        if (indptr[mid] <= f) lo = mid;
+        else hi = mid;
+    }
+    const long long q = lo;
+    const long long e = idx[f];
+    const long long te = HEAD ? queries[3 * q] : queries[3 * q + 2];
+    if (e == te || e < e_lo || e >= e_hi) return;
+    // a candidate listed twice must be undone once: only its first occurrence in the row acts
+    for (long long j = indptr[q]; j < f; ++j)
+        if (idx[j] == e) return;
+    const int qdim = model_planes(MODEL) * P.H;
+    const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
+    const float s = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b);
+    const float t = true_score[q];
+    if (s > t) atomicAdd(n_greater + q, ~0ULL);      // -1
+    else if (s == t) atomicAdd(n_equal + q, ~0ULL);  // -1
+}
+
+// ---- 4 tile ----------------------------------------------------------------------------------
+constexpr int kTQ = 128, kTE = 128, kKC = 16, kEvalThreads = 256;
+
+template <int MODEL>
+constexpr size_t eval_tile_smem() {
+    return (size_t)2 * (model_planes(MODEL) + cand_planes(MODEL)) * kKC * kTQ * sizeof(float);
+}
+
+template <int MODEL, bool HEAD>
+__global__ void __launch_bounds__(kEvalThreads)
+eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
+                 const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
+                 const int64_t* __restrict__ queries, long long Q, long long e_lo, long long e_hi,
+                 const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+    constexpr int QP = model_planes(MODEL), CP = cand_planes(MODEL);
+    extern __shared__ __align__(16) float smem[];
+    // [buf][plane][k][row]
+    float* Qt = smem;
+    float* Et = smem + 2 * QP * kKC * kTQ;
+    const int H = P.H, qdim = QP * H;
+    const int tid = threadIdx.x;
+    if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
+
+    const long long e0 = e_lo + (long long)blockIdx.x * kTE;
+    const long long q0 = (long long)blockIdx.y * kTQ;
+
+    // loader role: one row of each tile, 8 consecutive coordinates per chunk
+    const int lrow = tid & 127, lk = (tid >> 7) * 8;
+    const long long lq = min(q0 + lrow, Q - 1);
+    const long long le = min(e0 + lrow, e_hi - 1);
+    const float* qsrc = Qs + lq * qdim;
+    const float* esrc = ent + le * (long long)P.De;
+    const float l_ina = (MODEL == KGE_INTERHT) ? ina[le] : 0.f, l_inb = (MODEL == KGE_INTERHT) ? inb[le] : 0.f;
+    const bool vec = (H % 4 == 0);
+
+    float qreg[QP][8], ereg[CP][8];
+    auto fetch = [&](int kbase) {
+#pragma unroll
+        for (int p = 0; p < QP; ++p) {
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int k = kbase + lk + 4 * v;
+                if (vec && k + 3 < H) {
+                    const float4 x = *reinterpret_cast<const float4*>(qsrc + p * H + k);
+                    qreg[p][4 * v] = x.x; qreg[p][4 * v + 1] = x.y; qreg[p][4 * v + 2] = x.z; qreg[p][4 * v + 3] = x.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) qreg[p][4 * v + i] = (k + i < H) ? qsrc[p * H + k + i] : 0.f;
+                }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < CP; ++p) {
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int k = kbase + lk + 4 * v;
+                if (vec && k + 3 < H) {
+                    const float4 x = __ldg(reinterpret_cast<const float4*>(esrc + p * H + k));
+                    ereg[p][4 * v] = x.x; ereg[p][4 * v + 1] = x.y; ereg[p][4 * v + 2] = x.z; ereg[p][4 * v + 3] = x.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) ereg[p][4 * v + i] = (k + i < H) ? __ldg(esrc + p * H + k + i) : 0.f;
+                }
+            }
+        }
+    };
+    auto stash = [&](int buf, int kbase) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const bool live = (kbase + lk + i) < H;  // padding coordinates contribute exactly +0
+#pragma unroll
+            for (int p = 0; p < QP; ++p) Qt[((buf * QP + p) * kKC + lk + i) * kTQ + lrow] = qreg[p][i];
+            float c0, c1;
+            prep_candidate<MODEL>(c0, c1, ereg[0][i], (CP > 1) ? ereg[CP - 1][i] : 0.f, c.inv_phase_div, l_ina, l_inb);
+            if (!live) { c0 = 0.f; c1 = 0.f; }
+            Et[((buf * CP + 0) * kKC + lk + i) * kTE + lrow] = c0;
+            if (CP > 1) Et[((buf * CP + 1) * kKC + lk + i) * kTE + lrow] = c1;
+        }
+    };
+
+    // compute role: 8 queries x 8 entities, split 4 + 4 so that LDS.128 is conflict-free
+    const int ty = tid >> 4, tx = tid & 15;
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    const int nchunks = (H + kKC - 1) / kKC;
+    fetch(0);
+    stash(0, 0);
+    __syncthreads();
+    for (int ch = 0; ch < nchunks; ++ch) {
+        const int buf = ch & 1;
+        if (ch + 1 < nchunks) fetch((ch + 1) * kKC);
+#pragma unroll 4
+        for (int k = 0; k < kKC; ++k) {
+            float qv[QP][8], ev[CP][8];
+#pragma unroll
+            for (int p = 0; p < QP; ++p) {
+                const float* src = Qt + ((buf * QP + p) * kKC + k) * kTQ;
+                const float4 a = *reinterpret_cast<const float4*>(src + ty * 4);
+                const float4 b = *reinterpret_cast<const float4*>(src + 64 + ty * 4);
+                qv[p][0] = a.x; qv[p][1] = a.y; qv[p][2] = a.z; qv[p][3] = a.w;
+                qv[p][4] = b.x; qv[p][5] = b.y; qv[p][6] = b.z; qv[p][7] = b.w;
+            }
+#pragma unroll
+            for (int p = 0; p < CP; ++p) {
+                const float* src = Et + ((buf * CP + p) * kKC + k) * kTE;
+                const float4 a = *reinterpret_cast<const float4*>(src + tx * 4);
+                const float4 b = *reinterpret_cast<const float4*>(src + 64 + tx * 4);
+                ev[p][0] = a.x; ev[p][1] = a.y; ev[p][2] = a.z; ev[p][3] = a.w;
+                ev[p][4] = b.x; ev[p][5] = b.y; ev[p][6] = b.z; ev[p][7] = b.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    acc[i][j] = accum<MODEL, HEAD>(acc[i][j], qv[0][i], (QP > 1) ? qv[QP > 1 ? 1 : 0][i] : 0.f,
+                                                   (QP > 2) ? qv[QP > 2 ? 2 : 0][i] : 0.f, ev[0][j],
+                                                   (CP > 1) ? ev[CP - 1][j] : 0.f);
+        }
+        if (ch + 1 < nchunks) {
+            stash(buf ^ 1, (ch + 1) * kKC);  // the other buffer was last read in iteration ch-1
+            __syncthreads();
+        }
+    }
+
+    // epilogue: compare with the true score, reduce over the 16 threads that share the query rows
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const long long q = q0 + ((i < 4) ? (ty * 4 + i) : (64 + ty * 4 + i - 4));
+        const bool qok = q < Q;
+        const float t = qok ? true_score[q] : 0.f;
+        const long long te = qok ? (HEAD ? queries[3 * q] : queries[3 * q + 2]) : -1;
+        int gt = 0, eq = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const long long e = e0 + ((j < 4) ? (tx * 4 + j) : (64 + tx * 4 + j - 4));
+            const float s = finalize<MODEL>(acc[i][j], c);
+            const bool ok = qok && e < e_hi && e != te;
+            gt += (ok && s > t) ? 1 : 0;
+            eq += (ok && s == t) ? 1 : 0;
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            gt += __shfl_xor_sync(0xffffffffu, gt, o);
+            eq += __shfl_xor_sync(0xffffffffu, eq, o);
+        }
+        if (tx == 0 && qok) {
+            if (gt) atomicAdd(n_greater + q, (unsigned long long)gt);
+            if (eq) atomicAdd(n_equal + q, (unsigned long long)eq);
+        }
+    }
+}
+
+// ---- launcher --------------------------------------------------------------------------------
+static inline size_t ev_align(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t /*nfilter*/) {
+    size_t total = ev_align((size_t)Q * model_planes(P.model) * P.H * sizeof(float));
+    if (P.model == KGE_INTERHT) total += 2 * ev_align((size_t)P.E * sizeof(float));
+    return total + 256;
+}
+
+template <int MODEL, bool HEAD>
+static cudaError_t launch_eval_model(const Params& P, const float* ent, const float* rel, const float* modulus,
+                                     const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                                     const int64_t* indptr, const int64_t* idx, float* true_score,
+                                     unsigned long long* n_greater, unsigned long long* n_equal, int accumulate,
+                                     void* ws, cudaStream_t st) {
+    const int qdim = model_planes(MODEL) * P.H;
+    float* Qs = (float*)ws;
+    float* ina = nullptr;
+    float* inb = nullptr;
+    if (MODEL == KGE_INTERHT) {
+        ina = (float*)((char*)ws + ev_align((size_t)Q * qdim * sizeof(float)));
+        inb = (float*)((char*)ina + ev_align((size_t)P.E * sizeof(float)));
+    }
+    EvalConsts c{P.gamma, P.inv_phase_div, 0.f};
+    cudaError_t e;
+    if (!accumulate) {
+        if ((e = cudaMemsetAsync(n_greater, 0, (size_t)Q * sizeof(unsigned long long), st)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(n_equal, 0, (size_t)Q * sizeof(unsigned long long), st)) != cudaSuccess) return e;
+    }
+    const size_t smem_stage = (size_t)(qdim + 4 + 32) * sizeof(float);
+    if (smem_stage > 48 * 1024)
+        cudaFuncSetAttribute(eval_stage_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_stage);
+    eval_stage_kernel<MODEL><<<(unsigned)Q, 128, smem_stage, st>>>(P, HEAD ? 1 : 0, ent, rel, queries, Qs);
+    if (MODEL == KGE_INTERHT) {
+        const int blocks = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
+        eval_inv_norm_kernel<<<blocks, 256, 0, st>>>(P, ent, ina, inb);
+    }
+    eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + 127) / 128), 128, 0, st>>>(P, c, modulus, ent, Qs, ina, inb, queries,
+                                                                             Q, true_score);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (e_hi > e_lo) {
+        constexpr size_t smem = eval_tile_smem<MODEL>();
+        cudaFuncSetAttribute(eval_tile_kernel<MODEL, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        dim3 grid((unsigned)((e_hi - e_lo + kTE - 1) / kTE), (unsigned)((Q + kTQ - 1) / kTQ));
+        eval_tile_kernel<MODEL, HEAD><<<grid, kEvalThreads, smem, st>>>(P, c, modulus, ent, Qs, ina, inb, queries, Q, e_lo,
+                                                                         e_hi, true_score, n_greater, n_equal);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    if (indptr != nullptr && idx != nullptr) {
+        // the number of filter entries lives on the device (indptr[Q]): grid-stride over it, no host sync
+        eval_filter_kernel<MODEL, HEAD><<<4 * sm_count(), 128, 0, st>>>(P, c, modulus, ent, Qs, ina, inb, queries, Q, indptr,
+                                                                      idx, e_lo, e_hi, true_score, n_greater, n_equal);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_eval_rank(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
+                             const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                             const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
+                             int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes,
+                             cudaStream_t st) {
+    if (ws_bytes < eval_workspace_bytes(P, Q, 0)) return cudaErrorInvalidValue;
+    auto* ng = reinterpret_cast<unsigned long long*>(n_greater);
+    auto* ne = reinterpret_cast<unsigned long long*>(n_equal);
+    const bool head = (mode == KGE_MODE_HEAD_BATCH);
+#define KGE_CASE(M)                                                                                                  \
+    case M:                                                                                                          \
+        return head ? launch_eval_model<M, true>(P, ent, rel, modulus, queries, Q, e_lo, e_hi, filter_indptr,        \
+                                                 filter_idx, true_score, ng, ne, accumulate, ws, st)                 \
+                    : launch_eval_model<M, false>(P, ent, rel, modulus, queries, Q, e_lo, e_hi, filter_indptr,       \
+                                                  filter_idx, true_score, ng, ne, accumulate, ws, st)
+    switch (P.model) {
+        KGE_CASE(KGE_TRANSE);
+        KGE_CASE(KGE_DISTMULT);
+        KGE_CASE(KGE_COMPLEX);
+        KGE_CASE(KGE_ROTATE);
+        KGE_CASE(KGE_PROTATE);
+        KGE_CASE(KGE_INTERHT);
+    }
+#undef KGE_CASE
+    return cudaErrorInvalidValue;
+}
+
 }  // namespace kge

@@ -330,13 +330,19 @@ class KGEModel(nn.Module):
         model.last_eval = {"ranks": ranks, "n_tied_candidates": ties}
         if ties:
             logging.warning("test_step: %d candidates tie exactly with a true score; ranks are 1 + #greater", ties)
-        # upstream: per-query logs, then sum(...) / len(...) in query order with Python floats
-        sums = {"MRR": 0.0, "MR": 0.0, "HITS@1": 0.0, "HITS@3": 0.0, "HITS@10": 0.0}
+        # upstream: per-query logs, then `sum([log[metric] for log in logs]) / len(logs)` -- the same builtin
+        # sum over Python floats in query order, so equal ranks give bit-equal metrics
+        logs = []
         for ranking in ranks.tolist():
-            sums["MRR"] += 1.0 / ranking
-            sums["MR"] += float(ranking)
-            sums["HITS@1"] += 1.0 if ranking <= 1 else 0.0
-            sums["HITS@3"] += 1.0 if ranking <= 3 else 0.0
-            sums["HITS@10"] += 1.0 if ranking <= 10 else 0.0
-        n = max(len(ranks), 1)
-        return {k: v / n for k, v in sums.items()}
+            logs.append({
+                "MRR": 1.0 / ranking,
+                "MR": float(ranking),
+                "HITS@1": 1.0 if ranking <= 1 else 0.0,
+                "HITS@3": 1.0 if ranking <= 3 else 0.0,
+                "HITS@10": 1.0 if ranking <= 10 else 0.0,
+            })
+        metrics = {}
+        if logs:
+            for metric in logs[0].keys():
+                metrics[metric] = sum([log[metric] for log in logs]) / len(logs)
+        return metrics
