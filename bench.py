@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""bench.py -- the BASELINE.json metric on the BASELINE.json config, one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+metric  : train triples*neg/sec  (B*N negatives scored, back-propagated and Adam-applied per step)
+workload: BASELINE.json configs[1] -- RotatE, FB15k-237 sizes (14541 entities, 237 relations),
+          hidden_dim 1000, gamma 9, batch 1024, 256 negatives, -adv; synthetic triples of that shape
+          (the dataset's train.txt is a missing blob in the reference), random-init tables.
+step    : forward (negative + positive scores), loss, backward, dense Adam on both tables.
+
+value   : device-resident batches, CUDA events around exactly K steps, max over ranks.
+e2e     : the same K steps through KGEModel.train_step(model, optimizer, iterator, args) with the batch
+          in pinned HOST memory: per step H2D of (positive, negative, weights) and D2H of the loss log.
+roofline: dominant kernel of the step (by measured device time, CUDA events recorded by the library
+          around each stage inside a second timed region), algorithmic bytes / duration vs MEASURED_PEAKS.
+cpu_baseline / --impl reference: the CPU oracle (a port: the reference's PyTorch half is an absent
+          submodule and TensorFlow is not installable) on the host cores, bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+WORKLOAD = dict(model="RotatE", nentity=14541, nrelation=237, hidden_dim=1000, gamma=9.0, batch=1024,
+                negatives=256, adversarial_temperature=1.0, lr=5e-5)
+WORKLOAD_NAME = "RotatE FB15k-237-shaped (E=14541,R=237) H=1000 gamma=9 B=1024 N=256 -adv, fwd+loss+bwd+dense Adam"
+CPU_SAMPLE_B = 64  # positives per CPU-baseline step (x256 negatives): ~5 s of host work per step here
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed regions run."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag, self.max_mhz = index, [], False, None
+        self.reasons = set()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                     "sw_thermal_slowdown": 0x20, "hw_power_brake_slowdown": 0x80}
+            while not self.stop_flag:
+                util = nv.nvmlDeviceGetUtilizationRates(h).gpu
+                mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((mhz, util))
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+                time.sleep(0.1)
+        except Exception as e:  # pragma: no cover
+            self.reasons.add("sampler_error:%s" % type(e).__name__)
+
+    def summary(self):
+        import statistics
+        loaded = [m for m, u in self.samples if u > 0] or [m for m, _ in self.samples]
+        return {"sm_mhz": statistics.median(loaded) if loaded else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def algorithmic_bytes(w):
+    """Per-launch algorithmic bytes of each stage (DESIGN.md 'Kernels'; SURVEY 8(d) terms)."""
+    B, N, H = w["batch"], w["negatives"], w["hidden_dim"]
+    De, Dr = 2 * H, H
+    E, R = w["nentity"], w["nrelation"]
+    rows = B * N
+    return {
+        "score_forward(neg)": rows * (De * 4 + 8 + 4) + B * (De + Dr + De) * 4,   # candidate row + index + score
+        "score_backward(neg)": rows * (2 * De * 4 + 8 + 4) + B * (2 * De + Dr) * 4 * 2,  # row read + grad row add
+        "adam(entity)": E * De * 28,   # p,m,v read+write, g read
+        "adam(relation+modulus)": R * Dr * 28,
+        "zero_grad": (E * De + R * Dr) * 4,
+        "step": rows * (3 * De * 4 + 16) + B * (2 * De + Dr) * 12 + (E * De + R * Dr) * 24,
+    }
+
+
+def synthetic_batch(nentity, nrelation, batch, negatives, seed):
+    """SURVEY 8(d) synthetic inputs: uniform triples and negatives, w = sqrt(1/c), c ~ U{8..200}, modes alternate."""
+    import torch
+    g = torch.Generator().manual_seed(int(seed))
+    pos = torch.stack([torch.randint(0, nentity, (batch,), generator=g),
+                       torch.randint(0, nrelation, (batch,), generator=g),
+                       torch.randint(0, nentity, (batch,), generator=g)], dim=1)
+    neg = torch.randint(0, nentity, (batch, negatives), generator=g)
+    w = torch.sqrt(1.0 / torch.randint(8, 201, (batch,), generator=g).to(torch.float32))
+    return pos, neg, w, ("head-batch" if seed % 2 == 0 else "tail-batch")
+
+
+def cpu_baseline(steps, warmup, threads=None):
+    """The oracle's train_step on the host cores: bounded sample (CPU_SAMPLE_B positives x N negatives per step)."""
+    import torch
+    from oracle import kge_oracle as ko
+    w = WORKLOAD
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    m = ko.make_model(w["model"], w["nentity"], w["nrelation"], w["hidden_dim"], w["gamma"], seed=0)
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, m.parameters()), lr=w["lr"])
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=w["adversarial_temperature"])
+    times = []
+    for s in range(warmup + steps):
+        batch = ko.synthetic_batch(w["nentity"], w["nrelation"], CPU_SAMPLE_B, w["negatives"], seed=s)
+        t0 = time.perf_counter()
+        ko.train_step(m, opt, iter([batch]), args)
+        if s >= warmup:
+            times.append(time.perf_counter() - t0)
+    total = sum(times)
+    return {"value": CPU_SAMPLE_B * w["negatives"] * len(times) / total, "unit": "triples*neg/s", "cores": cores,
+            "kind": "port",
+            "sample": "%d steps of %d positives x %d negatives (1/%d of the batch) incl. dense Adam over the full "
+                      "tables, torch %s CPU fp32" % (len(times), CPU_SAMPLE_B, w["negatives"],
+                                                    w["batch"] // CPU_SAMPLE_B, torch.__version__),
+            "ms_per_step": 1e3 * total / len(times)}
+
+
+def run_reference(a):
+    """--impl reference: the reference path's CPU implementation on the host cores (oracle port), rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    base = cpu_baseline(max(1, a.steps), max(0, a.warmup))
+    line = {
+        "impl": "reference", "metric": "train_triples_neg_per_sec", "value": base["value"], "unit": "triples*neg/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": base["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAME, "reference_arm": "CPU oracle (port) on host cores; " + base["sample"]},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": base["value"], "unit": "triples*neg/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(a):
+    import numpy as np
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    w = WORKLOAD
+    K, W = a.steps, max(a.warmup, 3)
+
+    torch.manual_seed(0)
+    model = kb.KGEModel(w["model"], w["nentity"], w["nrelation"], w["hidden_dim"], w["gamma"], True, False).to(dev)
+    model.deterministic = bool(a.deterministic)
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, model.parameters()), lr=w["lr"])
+    targs = argparse.Namespace(cuda=True, negative_adversarial_sampling=True,
+                               adversarial_temperature=w["adversarial_temperature"], uni_weight=False,
+                               regularization=0.0)
+    group = model._fused_adam_plan(opt)
+    nb = min(K + W, 32)
+    host = []
+    for s in range(nb):
+        pos, neg, sw, mode = synthetic_batch(w["nentity"], w["nrelation"], w["batch"], w["negatives"],
+                                             seed=1000 * rank + s)
+        host.append((pos.pin_memory(), neg.pin_memory(), sw.pin_memory(), mode))
+    devb = [(p.to(dev), n.to(dev), s.to(dev), m) for p, n, s, m in host]
+    h2d = sum(t.numel() * t.element_size() for t in host[0][:3])
+    units = w["batch"] * w["negatives"]
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_steps(n, start):
+        out = None
+        for i in range(n):
+            p, ng, s, m = devb[(start + i) % nb]
+            out = model._fused_step(opt, group, p, ng, s, m, True, w["adversarial_temperature"], False, 0.0)
+        return out
+
+    def timed(fn):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    sampler = ClockSampler(local_rank)
+    device_steps(W, 0)  # warm-up (also allocates the workspace and Adam state)
+    sampler.start()
+    # ---- value: K steps, batches resident in HBM, no host sync inside -------------------------------
+    ms_value = timed(lambda: device_steps(K, W))
+    # ---- second timed region with per-stage CUDA events (roofline of the dominant kernel) -----------
+    lib.kge_profile_enable(1)
+    ms_prof = timed(lambda: device_steps(K, W))
+    nst = lib.kge_profile_num_stages()
+    ms_sum = (C.c_float * nst)()
+    launches = (C.c_int64 * nst)()
+    lib.kge_profile_read(ms_sum, launches, 1)
+    lib.kge_profile_enable(0)
+    stages = {lib.kge_profile_stage_name(i).decode(): (ms_sum[i], launches[i]) for i in range(nst)}
+    # ---- e2e: the public API with the batch in pinned host memory ------------------------------------
+    it = iter([host[(W + i) % nb] for i in range(K + 3)])
+    for _ in range(3):
+        kb.KGEModel.train_step(model, opt, it, targs)
+    last_log = {}
+
+    def e2e_steps():
+        for _ in range(K):
+            last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
+    ms_e2e = timed(e2e_steps)
+    # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
+    ev = eval_bench(model, w, dev, timed, rank)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    total_units = units * K * world
+    peak, peak_src = peaks()
+    ab = algorithmic_bytes(w)
+    dom = max((k for k in stages if stages[k][1] > 0), key=lambda k: stages[k][0])
+    dom_ms = stages[dom][0] / K
+    achieved = ab.get(dom, 0) / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
+    traffic = None
+    tpath = os.path.join(REPO, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(dom)
+    step_ms = ms_value / K
+    line = {
+        "metric": "train_triples_neg_per_sec", "value": total_units / (ms_value * 1e-3), "unit": "triples*neg/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAME,
+                   "parallelism": "single GPU" if world == 1 else "%d independent replicas (no exchange)" % world,
+                   "l2": "no flush: tables + Adam state + gradients = %.2f GB per step > 126 MB L2; the entity table "
+                         "itself (116 MB) is L2-resident for the gathers, as in any real run" %
+                         ((w["nentity"] * 2 * w["hidden_dim"] + w["nrelation"] * w["hidden_dim"]) * 16 / 1e9),
+                   "backward": "deterministic" if a.deterministic else "atomic"},
+        "e2e": {"value": total_units / (ms_e2e * 1e-3), "unit": "triples*neg/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 16, "ms_per_step": ms_e2e / K, "loss": last_log.get("loss")},
+        "gpu_launches": int(sum(v[1] for v in stages.values())),
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                     "kernel_ms": dom_ms, "algorithmic_bytes": ab.get(dom),
+                     "step": {"algorithmic_bytes": ab["step"], "achieved": ab["step"] / (step_ms * 1e-3) / 1e9,
+                              "frac": ab["step"] / (step_ms * 1e-3) / 1e9 / peak,
+                              "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12}},
+        "stages_ms_per_step": {k: v[0] / K for k, v in stages.items()},
+        "profiled_region_ms_per_step": ms_prof / K,
+        "eval": ev,
+        "clocks": sampler.summary(),
+    }
+    log("timing done; running the bounded CPU baseline sample ...")
+    base = cpu_baseline(steps=2, warmup=1) if not a.no_cpu_baseline else None
+    line["cpu_baseline"] = ({k: base[k] for k in ("value", "unit", "cores", "kind", "sample")} if base else None)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def eval_bench(model, w, dev, timed, rank):
+    """Filtered full-entity ranking throughput (queries/s): 1024 head-batch + 1024 tail-batch queries."""
+    import numpy as np
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    rng = np.random.RandomState(7 + rank)
+    nq = 1024
+    test = np.stack([rng.randint(0, w["nentity"], nq), rng.randint(0, w["nrelation"], nq),
+                     rng.randint(0, w["nentity"], nq)], 1).astype(np.int64)
+    extra = np.stack([rng.randint(0, w["nentity"], 8 * nq), rng.randint(0, w["nrelation"], 8 * nq),
+                      rng.randint(0, w["nentity"], 8 * nq)], 1).astype(np.int64)
+    # true triples sharing (h,r) / (r,t) with the test triples so that the filter lists are non-empty
+    share = test[rng.randint(0, nq, 4 * nq)].copy()
+    share[: 2 * nq, 2] = rng.randint(0, w["nentity"], 2 * nq)
+    share[2 * nq:, 0] = rng.randint(0, w["nentity"], 2 * nq)
+    all_true = [tuple(int(x) for x in t) for t in np.concatenate([test, extra, share])]
+    test_l = [tuple(int(x) for x in t) for t in test]
+    maps = model._filter_maps(all_true)
+    q = torch.from_numpy(test).to(dev)
+    csr = {}
+    for mode in ("head-batch", "tail-batch"):
+        ip, ix = kb.KGEModel.build_filter_csr(maps, test, mode, w["nentity"])
+        csr[mode] = (torch.from_numpy(ip).to(dev), torch.from_numpy(ix).to(dev))
+
+    def device_eval():
+        for mode in ("head-batch", "tail-batch"):
+            model.rank_queries(q, mode, *csr[mode])
+    device_eval()
+    ms = timed(device_eval)
+    eargs = argparse.Namespace(nentity=w["nentity"], nrelation=w["nrelation"], countries=False)
+    metrics = {}
+
+    def api_eval():
+        metrics.update(kb.KGEModel.test_step(model, test_l, all_true, eargs))
+    api_eval()
+    ms_api = timed(api_eval)
+    return {"metric": "eval_queries_per_sec", "value": 2 * nq / (ms * 1e-3), "unit": "queries/s",
+            "queries": 2 * nq, "candidates_per_query": w["nentity"], "ms": ms,
+            "e2e": {"value": 2 * nq / (ms_api * 1e-3), "unit": "queries/s", "ms": ms_api,
+                    "note": "KGEModel.test_step from Python triple lists: CSR filter build on host, H2D, D2H of ranks"},
+            "mrr_random_init": metrics.get("MRR")}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--deterministic", action="store_true", help="use the fixed-order backward variant")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        if a.steps > 8:
+            a.steps = 4  # each CPU step is ~5 s of host work: keep the arm within a few minutes
+            a.warmup = min(a.warmup, 1)
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

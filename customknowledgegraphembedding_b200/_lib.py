@@ -68,6 +68,10 @@ PROTOTYPES = {
     "kge_train_step_host": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                       C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _SZ, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
+    "kge_profile_enable": (C.c_int, [C.c_int]),
+    "kge_profile_num_stages": (C.c_int, []),
+    "kge_profile_stage_name": (C.c_char_p, [C.c_int]),
+    "kge_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int64), C.c_int]),
 }
 
 _lib = None

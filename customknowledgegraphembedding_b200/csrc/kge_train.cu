@@ -10,9 +10,52 @@
 //   loss scratch f32[2B+8] | l3 scratch f32[1024] | small f32[16] (loss3, reg sums, grad_modulus)
 //   grad_entity f32[E,De] | grad_relation f32[R,Dr]   (dense, as .grad in the reference)
 //   deterministic-backward scratch
+#include <vector>
+
 #include "kge_train.h"
 
 namespace kge {
+
+// ---- measurement hooks: CUDA events around each stage of the step (include/kge_b200.h) ----------
+enum Stage { ST_ZERO = 0, ST_FWD_NEG, ST_FWD_POS, ST_LOSS, ST_BWD_NEG, ST_BWD_POS, ST_REG, ST_ADAM_ENT, ST_ADAM_REL, ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"zero_grad", "score_forward(neg)", "score_forward(pos)", "loss",
+                                            "score_backward(neg)", "score_backward(pos)", "l3_reg",
+                                            "adam(entity)", "adam(relation+modulus)"};
+static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1};  // kernels per stage (memsets are not kernels)
+struct ProfRec { int stage; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_live;
+static std::vector<cudaEvent_t> g_prof_pool;
+static float g_prof_ms[ST_COUNT];
+static int64_t g_prof_launches[ST_COUNT];
+
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) {
+        cudaEvent_t e = g_prof_pool.back();
+        g_prof_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+struct ProfScope {
+    cudaStream_t st;
+    ProfRec rec;
+    bool on;
+    ProfScope(int stage, cudaStream_t s) : st(s), on(g_prof_on) {
+        if (!on) return;
+        rec.stage = stage;
+        rec.a = prof_event();
+        rec.b = prof_event();
+        cudaEventRecord(rec.a, st);
+    }
+    ~ProfScope() {
+        if (!on) return;
+        cudaEventRecord(rec.b, st);
+        g_prof_live.push_back(rec);
+    }
+};
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -75,31 +118,52 @@ static int train_step_device(const Params& P, int mode, float* ent, float* rel, 
         e = (expr);                                    \
         if (e != cudaSuccess) return fail_cuda(e, what); \
     } while (0)
-    KGE_TRY(cudaMemsetAsync(ws.grad_ent, 0, (size_t)P.E * P.De * sizeof(float), st), "memset grad_entity");
-    KGE_TRY(cudaMemsetAsync(ws.grad_rel, 0, (size_t)P.R * P.Dr * sizeof(float), st), "memset grad_relation");
-    KGE_TRY(cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st), "memset small");
-    KGE_TRY(launch_score_forward(P, mode, ent, rel, modulus, pos, neg, B, N, ws.score_neg, st), "forward(neg)");
-    KGE_TRY(launch_score_forward(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.score_pos, st),
-            "forward(pos)");
-    KGE_TRY(launch_loss(ws.score_neg, ws.score_pos, w, B, N, lo, ws.small, ws.dneg, ws.dpos, ws.loss_ws, st), "loss");
+    {
+        ProfScope ps(ST_ZERO, st);
+        KGE_TRY(cudaMemsetAsync(ws.grad_ent, 0, (size_t)P.E * P.De * sizeof(float), st), "memset grad_entity");
+        KGE_TRY(cudaMemsetAsync(ws.grad_rel, 0, (size_t)P.R * P.Dr * sizeof(float), st), "memset grad_relation");
+        KGE_TRY(cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st), "memset small");
+    }
+    {
+        ProfScope ps(ST_FWD_NEG, st);
+        KGE_TRY(launch_score_forward(P, mode, ent, rel, modulus, pos, neg, B, N, ws.score_neg, st), "forward(neg)");
+    }
+    {
+        ProfScope ps(ST_FWD_POS, st);
+        KGE_TRY(launch_score_forward(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.score_pos, st),
+                "forward(pos)");
+    }
+    {
+        ProfScope ps(ST_LOSS, st);
+        KGE_TRY(launch_loss(ws.score_neg, ws.score_pos, w, B, N, lo, ws.small, ws.dneg, ws.dpos, ws.loss_ws, st), "loss");
+    }
     float* gmod = (P.model == KGE_PROTATE) ? ws.small + 8 : nullptr;
     if (deterministic) {
-        KGE_TRY(launch_score_backward_det(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
-                                          ws.grad_rel, gmod, ws.det_ws, ws.det_bytes, st),
-                "backward_det(neg)");
+        {
+            ProfScope ps(ST_BWD_NEG, st);
+            KGE_TRY(launch_score_backward_det(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
+                                              ws.grad_rel, gmod, ws.det_ws, ws.det_bytes, st),
+                    "backward_det(neg)");
+        }
+        ProfScope ps(ST_BWD_POS, st);
         KGE_TRY(launch_score_backward_det(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.dpos,
                                           ws.grad_ent, ws.grad_rel, gmod, ws.det_ws, ws.det_bytes, st),
                 "backward_det(pos)");
     } else {
-        KGE_TRY(launch_score_backward_atomic(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
-                                             ws.grad_rel, gmod, st),
-                "backward(neg)");
+        {
+            ProfScope ps(ST_BWD_NEG, st);
+            KGE_TRY(launch_score_backward_atomic(P, mode, ent, rel, modulus, pos, neg, B, N, ws.dneg, ws.grad_ent,
+                                                 ws.grad_rel, gmod, st),
+                    "backward(neg)");
+        }
+        ProfScope ps(ST_BWD_POS, st);
         KGE_TRY(launch_score_backward_atomic(P, KGE_MODE_SINGLE, ent, rel, modulus, pos, nullptr, B, 1, ws.dpos,
                                              ws.grad_ent, ws.grad_rel, gmod, st),
                 "backward(pos)");
     }
     float l3 = 0.f;
     if (lo.regularization != 0.f) {
+        ProfScope ps(ST_REG, st);
         l3 = lo.regularization;
         KGE_TRY(launch_l3_sum_cubes(ent, (int64_t)P.E * P.De, ws.small + 4, ws.l3_ws, st), "l3(entity)");
         KGE_TRY(launch_l3_sum_cubes(rel, (int64_t)P.R * P.Dr, ws.small + 5, ws.l3_ws, st), "l3(relation)");
@@ -107,7 +171,11 @@ static int train_step_device(const Params& P, int mode, float* ent, float* rel, 
         KGE_TRY(cudaGetLastError(), "finalize_reg");
     }
     const AdamScalars a = adam_scalars(ao);
-    KGE_TRY(launch_adam(ent, ws.grad_ent, m_ent, v_ent, (int64_t)P.E * P.De, a, l3, 0, st), "adam(entity)");
+    {
+        ProfScope ps(ST_ADAM_ENT, st);
+        KGE_TRY(launch_adam(ent, ws.grad_ent, m_ent, v_ent, (int64_t)P.E * P.De, a, l3, 0, st), "adam(entity)");
+    }
+    ProfScope ps(ST_ADAM_REL, st);
     KGE_TRY(launch_adam(rel, ws.grad_rel, m_rel, v_rel, (int64_t)P.R * P.Dr, a, l3, 0, st), "adam(relation)");
     if (P.model == KGE_PROTATE) KGE_TRY(launch_adam(modulus, gmod, m_mod, v_mod, 1, a, 0.f, 0, st), "adam(modulus)");
 #undef KGE_TRY
@@ -137,6 +205,35 @@ static int check_train_args(const kge_model_desc* desc, Params* P, int mode, con
 using namespace kge;
 
 extern "C" {
+
+int kge_profile_enable(int on) {
+    g_prof_on = on != 0;
+    return KGE_OK;
+}
+int kge_profile_num_stages(void) { return ST_COUNT; }
+const char* kge_profile_stage_name(int stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : ""; }
+int kge_profile_read(float* ms_sum, int64_t* launches, int reset) {
+    for (const ProfRec& r : g_prof_live) {
+        cudaError_t e = cudaEventSynchronize(r.b);
+        if (e != cudaSuccess) return fail_cuda(e, "kge_profile_read");
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        g_prof_ms[r.stage] += ms;
+        g_prof_launches[r.stage] += kStageLaunches[r.stage];
+        g_prof_pool.push_back(r.a);
+        g_prof_pool.push_back(r.b);
+    }
+    g_prof_live.clear();
+    for (int i = 0; i < ST_COUNT; ++i) {
+        if (ms_sum) ms_sum[i] = g_prof_ms[i];
+        if (launches) launches[i] = g_prof_launches[i];
+        if (reset) {
+            g_prof_ms[i] = 0.f;
+            g_prof_launches[i] = 0;
+        }
+    }
+    return KGE_OK;
+}
 
 int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
                    float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,

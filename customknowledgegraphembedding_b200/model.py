@@ -178,7 +178,20 @@ class KGEModel(nn.Module):
             return model._train_step_generic(optimizer, positive_sample, negative_sample, subsampling_weight, mode,
                                              adv, alpha, uni, reg)
 
+        out = model._fused_step(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                                adv, alpha, uni, reg)
+        pos_l, neg_l, loss, regv = out.tolist() if isinstance(out, torch.Tensor) else (float(x) for x in out)
+        log = {"regularization": regv} if reg != 0.0 else {}
+        log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
+        return log
+
+    def _fused_step(self, optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                    adv, alpha, uni, reg, detach_weights=True, keras_adam=False):
+        """One call into kge_train_step(_host).  Batch on the host -> copies inside the C call, returns a numpy
+        [pos_loss, neg_loss, loss, reg]; batch on the device -> fully asynchronous, returns a device tensor."""
+        model = self
         lib = _lib.load()
+        dev = model.entity_embedding.device
         B, N = negative_sample.shape
         ent, rel, mod = model.entity_embedding, model.relation_embedding, model._modulus()
         st_e, st_r = model._adam_state(optimizer, ent), model._adam_state(optimizer, rel)
@@ -188,8 +201,8 @@ class KGEModel(nn.Module):
             s["step"] += 1
         step = int(st_e["step"])
         beta1, beta2 = group["betas"]
-        adam = AdamOpts(float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), step, 0)
-        loss_opts = LossOpts(int(adv), int(uni), 1, 0, alpha, reg)
+        adam = AdamOpts(float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), step, int(keras_adam))
+        loss_opts = LossOpts(int(adv), int(uni), int(detach_weights), 0, alpha, reg)
         desc = model._desc()
         host_batch = not positive_sample.is_cuda
         P = ops._ptr
@@ -211,21 +224,17 @@ class KGEModel(nn.Module):
                     None if w is None else C.c_void_p(w.data_ptr()), B, N, C.byref(loss_opts), C.byref(adam),
                     int(model.deterministic), out.ctypes.data_as(C.c_void_p), P(ws), ws.numel(), stream),
                     "kge_train_step_host")
-                pos_l, neg_l, loss, regv = (float(x) for x in out)
-            else:
-                pos = ops._need_cuda("positive_sample", positive_sample, torch.int64)
-                neg = ops._need_cuda("negative_sample", negative_sample, torch.int64)
-                w = None if uni else ops._need_cuda("subsampling_weight", subsampling_weight.to(dev), torch.float32)
-                ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
-                out = torch.empty(4, dtype=torch.float32, device=dev)
-                _lib.check(lib.kge_train_step(
-                    C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(pos), P(neg), P(w),
-                    B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out),
-                    C.c_void_p(out.data_ptr() + 12), P(ws), ws.numel(), stream), "kge_train_step")
-                pos_l, neg_l, loss, regv = out.tolist()
-        log = {"regularization": regv} if reg != 0.0 else {}
-        log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
-        return log
+                return out
+            pos = ops._need_cuda("positive_sample", positive_sample, torch.int64)
+            neg = ops._need_cuda("negative_sample", negative_sample, torch.int64)
+            w = None if uni else ops._need_cuda("subsampling_weight", subsampling_weight.to(dev), torch.float32)
+            ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
+            out = torch.zeros(4, dtype=torch.float32, device=dev)
+            _lib.check(lib.kge_train_step(
+                C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(pos), P(neg), P(w),
+                B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out),
+                C.c_void_p(out.data_ptr() + 12), P(ws), ws.numel(), stream), "kge_train_step")
+            return out
 
     def _train_step_generic(self, optimizer, positive_sample, negative_sample, subsampling_weight, mode,
                             adv, alpha, uni, reg):

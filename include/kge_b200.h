@@ -201,6 +201,17 @@ KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *ent
                         const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts, int deterministic,
                         float *host_loss4, void *ws, size_t ws_bytes, void *stream);
 
+/*
+ * Measurement hooks (bench.py): when enabled, kge_train_step* brackets each of its stages with CUDA
+ * events on the caller's stream.  kge_profile_read synchronises those events and returns, per stage, the
+ * summed device time in ms and the number of kernel launches since the last reset.  Stage names:
+ * kge_profile_stage_name(i), i in [0, kge_profile_num_stages()).
+ */
+KGE_API int kge_profile_enable(int on);
+KGE_API int kge_profile_num_stages(void);
+KGE_API const char *kge_profile_stage_name(int stage);
+KGE_API int kge_profile_read(float *ms_sum, int64_t *launches, int reset);
+
 typedef enum {
     KGE_WS_BACKWARD = 0, /* kge_score_backward (deterministic) */
     KGE_WS_LOSS = 1,
