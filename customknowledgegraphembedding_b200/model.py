@@ -338,7 +338,7 @@ class KGEModel(nn.Module):
         ranks = np.concatenate(ranks) if ranks else np.zeros(0, dtype=np.int64)
         model.last_eval = {"ranks": ranks, "n_tied_candidates": ties}
         if ties:
-            logging.warning("test_step: %d candidates tie exactly with a true score; ranks are 1 + #greater", ties)
+            logging.info("test_step: %d candidates tie exactly with a true score; ranks are 1 + #greater", ties)
         # upstream: per-query logs, then `sum([log[metric] for log in logs]) / len(logs)` -- the same builtin
         # sum over Python floats in query order, so equal ranks give bit-equal metrics
         logs = []
