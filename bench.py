@@ -99,6 +99,11 @@ def algorithmic_bytes(w):
         "adam(entity)": E * De * 28,   # p,m,v read+write, g read
         "adam(relation+modulus)": R * Dr * 28,
         "zero_grad": (E * De + R * Dr) * 4,
+        # second-generation step: the sweep reads every candidate row once; the entity pass reads the staged
+        # planes of the using positive once per use, and p, m, v of every row once (read + write)
+        "fused_sweep(scores+loss+dL/dq)": rows * (De * 4 + 8 + 4) + B * (3 * De + Dr) * 4 * 2,
+        "entity_gather+adam": rows * (De * 4 + 4 + 4) + 2 * B * De * 4 + E * De * 24,
+        "relation_gather+adam": B * Dr * 4 + R * Dr * 24,
         "step": rows * (3 * De * 4 + 16) + B * (2 * De + Dr) * 12 + (E * De + R * Dr) * 24,
     }
 

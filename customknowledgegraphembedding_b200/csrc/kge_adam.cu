@@ -29,11 +29,7 @@ AdamScalars adam_scalars(const kge_adam_opts& o) {
 }
 
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamScalars& a, float l3) {
-    if (l3 != 0.f) g = fmaf(3.0f * l3 * p, fabsf(p), g);  // d/dp l3 |p|^3
-    m = fmaf(a.beta1, m, (1.0f - a.beta1) * g);
-    v = fmaf(a.beta2, v, (1.0f - a.beta2) * g * g);
-    const float denom = fmaf(sqrtf(v), a.inv_sqrt_bc2, a.eps);
-    p -= a.step_size * (m / denom);
+    adam_update(p, g, m, v, a.beta1, a.beta2, a.step_size, a.inv_sqrt_bc2, a.eps, l3);
 }
 
 template <bool HAS_G>

@@ -284,6 +284,19 @@ __global__ void __launch_bounds__(256) det_modulus_kernel(const float* __restric
     if (threadIdx.x == 0) grad_modulus[0] += acc;
 }
 
+// exclusive scan of counts -> offsets (+ a copy in cursor), then scatter every use into its bucket
+cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
+                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st) {
+    const long long total = BN + 2 * B;
+    const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
+    const int nblocks = (int)((E + kScanBlock - 1) / kScanBlock);
+    scan_block_kernel<<<nblocks, 256, 0, st>>>(counts, offsets, block_sums, E);
+    scan_sums_kernel<<<1, 1024, 0, st>>>(block_sums, nblocks);
+    scan_add_kernel<<<(unsigned)((E + 1 + 255) / 256), 256, 0, st>>>(offsets, block_sums, E, cursor);
+    det_fill_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, cursor, items);
+    return cudaGetLastError();
+}
+
 template <int MODEL>
 static cudaError_t launch_det_model(const Params& P, int mode, const float* ent, const float* rel,
                                     const float* modulus, const int64_t* pos, const int64_t* neg, int64_t B,

@@ -125,4 +125,14 @@ __device__ __forceinline__ void red_add(float* p, const float (&x)[VEC]) {
     }
 }
 
+// Adam on one element (torch.optim.Adam / keras via the precomputed scalars, see kge_adam.cu)
+__device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, float beta1, float beta2,
+                                            float step_size, float inv_sqrt_bc2, float eps, float l3) {
+    if (l3 != 0.f) g = fmaf(3.0f * l3 * p, fabsf(p), g);  // d/dp l3 |p|^3
+    m = fmaf(beta1, m, (1.0f - beta1) * g);
+    v = fmaf(beta2, v, (1.0f - beta2) * g * g);
+    const float denom = fmaf(sqrtf(v), inv_sqrt_bc2, eps);
+    p -= step_size * (m / denom);
+}
+
 }  // namespace kge

@@ -39,7 +39,11 @@ cudaError_t launch_score_backward_det(const Params& P, int mode, const float* en
                                       int64_t N, const float* dscore, float* grad_ent, float* grad_rel,
                                       float* grad_modulus, void* ws, size_t ws_bytes, cudaStream_t st);
 
+cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
+                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st);
+
 // K2
+cudaError_t launch_loss_final(const float* terms, int64_t B, float* loss3, cudaStream_t st);
 size_t loss_workspace_bytes(int64_t B);
 cudaError_t launch_loss(const float* neg_score, const float* pos_score, const float* w, int64_t B, int64_t N,
                         const kge_loss_opts& o, float* loss3, float* dneg, float* dpos, float* ws, cudaStream_t st);

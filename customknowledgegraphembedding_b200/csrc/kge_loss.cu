@@ -90,6 +90,11 @@ __global__ void __launch_bounds__(256) loss_final_kernel(const float* __restrict
     }
 }
 
+cudaError_t launch_loss_final(const float* terms, int64_t B, float* loss3, cudaStream_t st) {
+    loss_final_kernel<<<1, 256, 0, st>>>(terms, (int)B, loss3);
+    return cudaGetLastError();
+}
+
 size_t loss_workspace_bytes(int64_t B) { return (size_t)(2 * B + 8) * sizeof(float); }
 
 cudaError_t launch_loss(const float* neg_score, const float* pos_score, const float* w, int64_t B, int64_t N,

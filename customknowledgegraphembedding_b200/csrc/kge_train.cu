@@ -10,52 +10,16 @@
 //   loss scratch f32[2B+8] | l3 scratch f32[1024] | small f32[16] (loss3, reg sums, grad_modulus)
 //   grad_entity f32[E,De] | grad_relation f32[R,Dr]   (dense, as .grad in the reference)
 //   deterministic-backward scratch
-#include <vector>
-
+#include "kge_prof.h"
 #include "kge_train.h"
 
 namespace kge {
 
-// ---- measurement hooks: CUDA events around each stage of the step (include/kge_b200.h) ----------
-enum Stage { ST_ZERO = 0, ST_FWD_NEG, ST_FWD_POS, ST_LOSS, ST_BWD_NEG, ST_BWD_POS, ST_REG, ST_ADAM_ENT, ST_ADAM_REL, ST_COUNT };
-static const char* kStageNames[ST_COUNT] = {"zero_grad", "score_forward(neg)", "score_forward(pos)", "loss",
-                                            "score_backward(neg)", "score_backward(pos)", "l3_reg",
-                                            "adam(entity)", "adam(relation+modulus)"};
-static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1};  // kernels per stage (memsets are not kernels)
-struct ProfRec { int stage; cudaEvent_t a, b; };
-static bool g_prof_on = false;
-static std::vector<ProfRec> g_prof_live;
-static std::vector<cudaEvent_t> g_prof_pool;
-static float g_prof_ms[ST_COUNT];
-static int64_t g_prof_launches[ST_COUNT];
-
-static cudaEvent_t prof_event() {
-    if (!g_prof_pool.empty()) {
-        cudaEvent_t e = g_prof_pool.back();
-        g_prof_pool.pop_back();
-        return e;
-    }
-    cudaEvent_t e;
-    cudaEventCreate(&e);
-    return e;
-}
-struct ProfScope {
-    cudaStream_t st;
-    ProfRec rec;
-    bool on;
-    ProfScope(int stage, cudaStream_t s) : st(s), on(g_prof_on) {
-        if (!on) return;
-        rec.stage = stage;
-        rec.a = prof_event();
-        rec.b = prof_event();
-        cudaEventRecord(rec.a, st);
-    }
-    ~ProfScope() {
-        if (!on) return;
-        cudaEventRecord(rec.b, st);
-        g_prof_live.push_back(rec);
-    }
-};
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof_live;
+std::vector<cudaEvent_t> g_prof_pool;
+float g_prof_ms[ST_COUNT];
+int64_t g_prof_launches[ST_COUNT];
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -66,6 +30,8 @@ struct TrainWs {
     float *score_neg, *score_pos, *dneg, *dpos, *loss_ws, *l3_ws, *small, *grad_ent, *grad_rel;
     void* det_ws;
     size_t det_bytes;
+    void* fused_ws;
+    size_t fused_bytes;
     size_t total;
 };
 
@@ -82,6 +48,7 @@ static TrainWs carve(const Params& P, int64_t B, int64_t N, bool host_batch, voi
         w.neg = (int64_t*)take((size_t)B * N * sizeof(int64_t));
         w.w = (float*)take((size_t)B * sizeof(float));
     }
+    const size_t v1_begin = off;
     w.score_neg = (float*)take((size_t)B * N * sizeof(float));
     w.score_pos = (float*)take((size_t)B * sizeof(float));
     w.dneg = (float*)take((size_t)B * N * sizeof(float));
@@ -93,6 +60,11 @@ static TrainWs carve(const Params& P, int64_t B, int64_t N, bool host_batch, voi
     w.grad_rel = (float*)take((size_t)P.R * P.Dr * sizeof(float));
     w.det_bytes = backward_det_workspace_bytes(P, B, N);
     w.det_ws = take(w.det_bytes);
+    // the second-generation step overlays the same region (only one of the two runs in a call)
+    w.fused_ws = w.score_neg;
+    w.fused_bytes = fused_step_workspace_bytes(P, B, N);
+    const size_t v1_bytes = off - v1_begin;
+    if (w.fused_bytes > v1_bytes) off = v1_begin + ((w.fused_bytes + 255) & ~(size_t)255);
     w.total = off;
     return w;
 }
@@ -111,8 +83,18 @@ __global__ void finalize_reg_kernel(float* small, float lambda) {
 static int train_step_device(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
                              float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod, const int64_t* pos,
                              const int64_t* neg, const float* w, int64_t B, int64_t N, const kge_loss_opts& lo,
-                             const kge_adam_opts& ao, int deterministic, const TrainWs& ws, cudaStream_t st) {
+                             const kge_adam_opts& ao, int variant, const TrainWs& ws, cudaStream_t st,
+                             float** out_small) {
     cudaError_t e;
+    *out_small = ws.small;
+    // variant: 0 default / 1 deterministic -> second-generation step when applicable (always fixed-order);
+    //          2 / 3 force the first-generation kernels (atomic / deterministic backward)
+    if (variant <= 1 && fused_step_applicable(P, lo, B, N, ent, rel)) {
+        e = launch_train_step_fused(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N,
+                                    lo, ao, ws.fused_ws, ws.fused_bytes, out_small, st);
+        return e == cudaSuccess ? KGE_OK : fail_cuda(e, "train_step(fused)");
+    }
+    const int deterministic = (variant == 1 || variant == 3) ? 1 : 0;
 #define KGE_TRY(expr, what)                            \
     do {                                               \
         e = (expr);                                    \
@@ -251,12 +233,13 @@ int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* r
     if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "train step needs %zu workspace bytes, got %zu", need, ws_bytes);
     cudaStream_t st = (cudaStream_t)stream;
     const TrainWs w = carve(P, B, N, false, ws);
+    float* small = nullptr;
     rc = train_step_device(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                            adam_v_relation, adam_m_modulus, adam_v_modulus, positive, negative, subsampling_weight, B, N, *loss_opts,
-                           *adam_opts, deterministic, w, st);
+                           *adam_opts, deterministic, w, st, &small);
     if (rc) return rc;
-    cudaError_t e = cudaMemcpyAsync(loss3, w.small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
-    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, w.small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    cudaError_t e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step(copy loss)");
 }
 
@@ -276,6 +259,7 @@ int kge_train_step_host(const kge_model_desc* desc, int mode, float* entity, flo
     if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "train step needs %zu workspace bytes, got %zu", need, ws_bytes);
     cudaStream_t st = (cudaStream_t)stream;
     const TrainWs w = carve(P, B, N, true, ws);
+    float* small = nullptr;
     cudaError_t e = cudaMemcpyAsync(w.pos, host_positive, (size_t)B * 3 * sizeof(int64_t), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess)
         e = cudaMemcpyAsync(w.neg, host_negative, (size_t)B * N * sizeof(int64_t), cudaMemcpyHostToDevice, st);
@@ -284,9 +268,9 @@ int kge_train_step_host(const kge_model_desc* desc, int mode, float* entity, flo
     if (e != cudaSuccess) return fail_cuda(e, "kge_train_step_host(H2D)");
     rc = train_step_device(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                            adam_v_relation, adam_m_modulus, adam_v_modulus, w.pos, w.neg, host_subsampling_weight ? w.w : nullptr, B,
-                           N, *loss_opts, *adam_opts, deterministic, w, st);
+                           N, *loss_opts, *adam_opts, deterministic, w, st, &small);
     if (rc) return rc;
-    e = cudaMemcpyAsync(host_loss4, w.small, 4 * sizeof(float), cudaMemcpyDeviceToHost, st);
+    e = cudaMemcpyAsync(host_loss4, small, 4 * sizeof(float), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step_host(D2H)");
 }

@@ -1,7 +1,17 @@
-// Fused train step (host-side composition of the kernels) -- see kge_train.cu.
+// Fused train step (host-side composition of the kernels) -- see kge_train.cu / kge_train_fused.cu.
 #pragma once
 #include "kge_internal.h"
 
 namespace kge {
 size_t train_step_workspace_bytes(const Params& P, int64_t B, int64_t N, bool host_batch);
+
+// second-generation step (kge_train_fused.cu)
+size_t fused_step_workspace_bytes(const Params& P, int64_t B, int64_t N);
+bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, int64_t N, const void* ent,
+                           const void* rel);
+cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                                    float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                                    const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                                    const kge_loss_opts& lo, const kge_adam_opts& ao, void* ws, size_t ws_bytes,
+                                    float** out_small, cudaStream_t st);
 }

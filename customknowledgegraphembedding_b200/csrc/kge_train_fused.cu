@@ -1,0 +1,847 @@
+// Fused train step, second generation (sm_100a): no dense gradient table, no float atomics.
+//
+//  F1 sweep      one CTA per positive b.  Every thread owns fixed coordinates of every row, so the
+//                staged planes q_b and the dL/dq accumulators live in registers.  ONE pass over the N
+//                candidate rows produces the scores AND dL/dq: the self-adversarial softmax weights are
+//                folded in with the online-softmax recurrence (running max m, rescale on change), so the
+//                rows are never re-read.  Row sums cross threads through one shared-memory reduction per
+//                group of RPI rows.  Writes: scores S[b,:], planes Q[b], row stats (m_b, scale_b), loss
+//                terms, compact per-positive gradient rows GH[b], GR[b], GT[b]; counts every row use.
+//  F2 buckets    integer histogram (done in F1) -> exclusive scan -> fill -> per-bucket sort: for each
+//                entity the list of its uses in ascending order.
+//  F2b dscore    S[b,n] <- dL/ds[b,n] from (S, m_b, scale_b); loss terms -> loss3.
+//  F3 entity     one CTA per entity row (grid-stride): dL/d(row) = sum over its uses, rebuilt from
+//                (Q[b], row, dL/ds) coordinate by coordinate in registers in that fixed order, plus the
+//                GH/GT rows of positives it heads/tails; then Adam on the row in the same registers.
+//                Rows without uses take the g = 0 Adam update (dense-Adam semantics of the reference).
+//  F4 relation   one CTA per relation row: sum GR[b] over b ascending, Adam; pRotatE modulus likewise.
+//
+// Replaces the body of KGEModel.train_step (loss restated at
+// /root/reference/tensorflow_codes/model.py:4-44).  Results are bit-reproducible run to run.
+#include <vector>
+
+#include "kge_coord.cuh"
+#include "kge_internal.h"
+#include "kge_prof.h"
+#include "kge_train.h"
+
+namespace kge {
+
+// all threads get sum over the block of each v[i]; red: NV*32 floats.  Fixed order.
+template <int NV>
+__device__ __forceinline__ void block_reduce_vals(float (&v)[NV], float* red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        v[i] = warp_sum(v[i]);
+        if (lane == 0) red[i * 32 + warp] = v[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        float t = 0.f;
+        for (int w = 0; w < nw; ++w) t += red[i * 32 + w];
+        v[i] = t;
+    }
+    __syncthreads();
+}
+
+template <int CP, int CH>
+__device__ __forceinline__ void load_coords(float (&x)[CP][CH][4], const float* __restrict__ row, int H, int tid, int T,
+                                            int plane_stride) {
+#pragma unroll
+    for (int p = 0; p < CP; ++p)
+#pragma unroll
+        for (int j = 0; j < CH; ++j) {
+            const int k0 = 4 * (tid + j * T);
+            float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k0 < H) val = __ldg(reinterpret_cast<const float4*>(row + p * plane_stride + k0));
+            x[p][j][0] = val.x; x[p][j][1] = val.y; x[p][j][2] = val.z; x[p][j][3] = val.w;
+        }
+}
+
+struct SweepArgs {
+    const float* ent;
+    const float* rel;
+    const float* modulus;
+    const int64_t* pos;
+    const int64_t* neg;
+    const float* w;
+    int B, N, adv, uni;
+    float alpha;
+    float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
+    int* counts;
+};
+
+// ------------------------------------------------------------------------------------------------
+// F1
+// ------------------------------------------------------------------------------------------------
+template <int MODEL, int CH, int RPI>
+__global__ void __launch_bounds__(256)
+train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
+    constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL), RP = rel_planes_of(MODEL);
+    __shared__ float red[4 * 32 * 2];      // block reductions: up to 8 values x 32 warps
+    __shared__ float red2[2][RPI * 32];    // row-sum partials of the sweep, double-buffered by row group
+    __shared__ float sh_cn[RPI][2], sh_fin[8];
+
+    const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = (T + 31) >> 5;
+    const int H = P.H, N = A.N;
+    const bool head = head_i != 0;
+    const long long b = blockIdx.x;
+    const long long h = A.pos[3 * b], r = A.pos[3 * b + 1], t = A.pos[3 * b + 2];
+    const float* hrow = A.ent + h * (long long)P.De;
+    const float* trow = A.ent + t * (long long)P.De;
+    const float* rrow = A.rel + r * (long long)P.Dr + rel_offset<MODEL>(H, 0);
+    if (MODEL == KGE_PROTATE) kc.modulus = __ldg(A.modulus);
+
+    // ---- coef_b = w_b / sum(w) or 1/B -------------------------------------------------------------
+    float coef;
+    if (A.uni) {
+        coef = 1.0f / (float)A.B;
+    } else {
+        float part[1] = {0.f};
+        for (int i = tid; i < A.B; i += T) part[0] += __ldg(A.w + i);
+        block_reduce_vals<1>(part, red);
+        coef = __ldg(A.w + b) / part[0];
+    }
+    if (tid == 0) {  // every use of an entity row is counted for the bucket build (integer atomics)
+        atomicAdd(A.counts + h, 1);
+        atomicAdd(A.counts + t, 1);
+    }
+
+    // ---- stage the candidate-independent planes in registers ------------------------------------------
+    float q[QP][CH][4];
+    {
+        float fe[CP][CH][4], rv[RP][CH][4];
+        load_coords<CP, CH>(fe, head ? trow : hrow, H, tid, T, H);
+        load_coords<RP, CH>(rv, rrow, H, tid, T, H);
+        float nrm[2] = {0.f, 0.f};
+        if constexpr (MODEL == KGE_INTERHT) {
+            float ss[2] = {0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    ss[0] = fmaf(fe[0][j][i], fe[0][j][i], ss[0]);
+                    ss[1] = fmaf(fe[1][j][i], fe[1][j][i], ss[1]);
+                }
+            block_reduce_vals<2>(ss, red);
+            nrm[0] = 1.0f / sqrtf(ss[0]);
+            nrm[1] = 1.0f / sqrtf(ss[1]);
+        }
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float qq[3], e2[2] = {fe[0][j][i], (CP > 1) ? fe[CP - 1][j][i] : 0.f};
+                float r2[2] = {rv[0][j][i], (RP > 1) ? rv[RP - 1][j][i] : 0.f};
+                float cr, sr;
+                stage_coord<MODEL>(qq, e2, r2, head, kc, nrm, cr, sr);
+#pragma unroll
+                for (int p = 0; p < QP; ++p) q[p][j][i] = qq[p];
+            }
+#pragma unroll
+        for (int p = 0; p < QP; ++p)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const int k0 = 4 * (tid + j * T);
+                if (k0 < H)
+                    *reinterpret_cast<float4*>(A.Q + (b * QP + p) * H + k0) =
+                        make_float4(q[p][j][0], q[p][j][1], q[p][j][2], q[p][j][3]);
+            }
+    }
+
+    // ---- the sweep -------------------------------------------------------------------------------
+    float acc[QP][CH][4];
+#pragma unroll
+    for (int p = 0; p < QP; ++p)
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[p][j][i] = 0.f;
+    // online-softmax state, replicated in the lanes of warp 0
+    float m_run = -INFINITY, z_run = 0.f, l_run = 0.f, g_run = 0.f;
+
+    for (int n0 = 0; n0 < N; n0 += RPI) {
+        float c[RPI][CP][CH][4];
+        float sg[(MODEL == KGE_INTERHT) ? RPI : 1][CH][4];
+#pragma unroll
+        for (int rr = 0; rr < RPI; ++rr) {
+            const int n = n0 + rr;
+            const long long cid = (n < N) ? A.neg[b * N + n] : 0;
+            if (n < N && tid == rr) atomicAdd(A.counts + cid, 1);
+            load_coords<CP, CH>(c[rr], A.ent + cid * (long long)P.De, H, tid, T, H);
+        }
+        if constexpr (MODEL == KGE_INTERHT) {  // candidate norms first
+            float ss[2 * RPI];
+#pragma unroll
+            for (int rr = 0; rr < RPI; ++rr) {
+                ss[2 * rr] = ss[2 * rr + 1] = 0.f;
+#pragma unroll
+                for (int j = 0; j < CH; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        ss[2 * rr] = fmaf(c[rr][0][j][i], c[rr][0][j][i], ss[2 * rr]);
+                        ss[2 * rr + 1] = fmaf(c[rr][1][j][i], c[rr][1][j][i], ss[2 * rr + 1]);
+                    }
+            }
+            block_reduce_vals<2 * RPI>(ss, red);
+            if (tid < RPI) {
+                sh_cn[tid][0] = 1.0f / sqrtf(ss[2 * tid]);
+                sh_cn[tid][1] = 1.0f / sqrtf(ss[2 * tid + 1]);
+            }
+            __syncthreads();
+        }
+        // phase a: row sums; c is rewritten into the backward direction
+        float* redp = red2[(n0 / RPI) & 1];
+        float part[RPI];
+#pragma unroll
+        for (int rr = 0; rr < RPI; ++rr) {
+            part[rr] = 0.f;
+            float cn[2] = {0.f, 0.f};
+            if constexpr (MODEL == KGE_INTERHT) {
+                cn[0] = sh_cn[rr][0];
+                cn[1] = sh_cn[rr][1];
+            }
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float qq[3] = {q[0][j][i], (QP > 1) ? q[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? q[QP > 2 ? 2 : 0][j][i] : 0.f};
+                    float cc[2] = {c[rr][0][j][i], (CP > 1) ? c[rr][CP - 1][j][i] : 0.f};
+                    float s1 = 0.f;
+                    const bool live = 4 * (tid + j * T) < H;
+                    const float term = head ? fwd_coord<MODEL, true>(qq, cc, kc, cn, s1) : fwd_coord<MODEL, false>(qq, cc, kc, cn, s1);
+                    part[rr] += live ? term : 0.f;
+                    c[rr][0][j][i] = cc[0];
+                    if (CP > 1) c[rr][CP - 1][j][i] = cc[1];
+                    if constexpr (MODEL == KGE_INTERHT) sg[rr][j][i] = live ? s1 : 0.f;
+                }
+            part[rr] = warp_sum(part[rr]);
+            if (lane == 0) redp[rr * 32 + warp] = part[rr];
+        }
+        __syncthreads();
+        // Every warp finishes the rows itself (lane rr takes row rr) and advances its own copy of the softmax
+        // recurrence: identical arithmetic in every warp, so no second barrier and no serial section.
+        float wgt_lane, sc = 1.0f;
+        {
+            const int n = n0 + lane;
+            const bool valid = lane < RPI && n < N;
+            float tot = 0.f;
+            if (lane < RPI)
+                for (int w = 0; w < nw; ++w) tot += redp[lane * 32 + w];
+            const float s = score_from_sum<MODEL>(tot, kc);
+            if (valid && warp == 0) A.S[b * N + n] = s;
+            const float ls = valid ? log_sigmoid(-s) : 0.f;
+            const float sig = valid ? sigmoidf(s) : 0.f;
+            if (A.adv) {
+                const float a = valid ? s * A.alpha : -INFINITY;
+                const float m_new = fmaxf(m_run, warp_max(a));
+                sc = (m_run == -INFINITY) ? 0.f : expf(m_run - m_new);
+                const float e = valid ? expf(a - m_new) : 0.f;
+                z_run = z_run * sc + warp_sum(e);
+                l_run = l_run * sc + warp_sum(e * ls);
+                if (MODEL == KGE_PROTATE) g_run = g_run * sc + warp_sum(e * sig * tot);
+                m_run = m_new;
+                wgt_lane = e * sig;
+            } else {
+                l_run += warp_sum(ls);
+                if (MODEL == KGE_PROTATE) g_run += warp_sum(sig * tot);
+                wgt_lane = sig;
+            }
+        }
+        // phase b: acc = acc * sc + sum_r wgt_r * ds_r/dq
+        if (sc != 1.0f) {
+#pragma unroll
+            for (int p = 0; p < QP; ++p)
+#pragma unroll
+                for (int j = 0; j < CH; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[p][j][i] *= sc;
+        }
+#pragma unroll
+        for (int rr = 0; rr < RPI; ++rr) {
+            const float wgt = __shfl_sync(0xffffffffu, wgt_lane, rr);
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float aa[3] = {acc[0][j][i], (QP > 1) ? acc[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? acc[QP > 2 ? 2 : 0][j][i] : 0.f};
+                    const float dd[2] = {c[rr][0][j][i], (CP > 1) ? c[rr][CP - 1][j][i] : 0.f};
+                    const float s1 = (MODEL == KGE_INTERHT) ? sg[(MODEL == KGE_INTERHT) ? rr : 0][j][i] : 0.f;
+                    if (head) dq_accumulate<MODEL, true>(aa, dd, s1, wgt, kc);
+                    else dq_accumulate<MODEL, false>(aa, dd, s1, wgt, kc);
+#pragma unroll
+                    for (int p = 0; p < QP; ++p) acc[p][j][i] = aa[p];
+                }
+        }
+    }
+
+    // ---- row statistics -> every thread ------------------------------------------------------------
+    if (tid == 0) {
+        sh_fin[0] = m_run;
+        sh_fin[1] = z_run;
+        sh_fin[2] = l_run;
+        sh_fin[3] = g_run;
+    }
+    __syncthreads();
+    const float m_b = sh_fin[0];
+    const float denom = A.adv ? sh_fin[1] : (float)N;
+    const float negterm = sh_fin[2] / denom;
+    const float scale_b = 0.5f * coef / denom;  // dL/ds_n = scale_b * e_n * sigma(s_n)
+    const float gsum = sh_fin[3];
+    // dL/dq of the negative part
+#pragma unroll
+    for (int p = 0; p < QP; ++p)
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[p][j][i] *= scale_b;
+
+    // ---- positive score in 'single' form, its gradient, and the chain to (h, r, t) ------------------
+    float he[CP][CH][4], te[CP][CH][4], rv[RP][CH][4];
+    load_coords<CP, CH>(he, hrow, H, tid, T, H);
+    load_coords<CP, CH>(te, trow, H, tid, T, H);
+    load_coords<RP, CH>(rv, rrow, H, tid, T, H);
+    float nh[2] = {0.f, 0.f}, nt[2] = {0.f, 0.f};
+    if constexpr (MODEL == KGE_INTERHT) {
+        float ss[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ss[0] = fmaf(he[0][j][i], he[0][j][i], ss[0]);
+                ss[1] = fmaf(he[1][j][i], he[1][j][i], ss[1]);
+                ss[2] = fmaf(te[0][j][i], te[0][j][i], ss[2]);
+                ss[3] = fmaf(te[1][j][i], te[1][j][i], ss[3]);
+            }
+        block_reduce_vals<4>(ss, red);
+        nh[0] = 1.0f / sqrtf(ss[0]); nh[1] = 1.0f / sqrtf(ss[1]);
+        nt[0] = 1.0f / sqrtf(ss[2]); nt[1] = 1.0f / sqrtf(ss[3]);
+    }
+    // q1 = planes in single form (fixed entity = head); equal to q in tail-batch mode
+    float q1[QP][CH][4], crs[CH][4], srs[CH][4];
+    float d1[CP][CH][4], sg1[CH][4];
+    float ptot[1] = {0.f};
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float qq[3], e2[2] = {he[0][j][i], (CP > 1) ? he[CP - 1][j][i] : 0.f};
+            float r2[2] = {rv[0][j][i], (RP > 1) ? rv[RP - 1][j][i] : 0.f};
+            float cr = 0.f, sr = 0.f;
+            stage_coord<MODEL>(qq, e2, r2, false, kc, nh, cr, sr);
+            crs[j][i] = cr;
+            srs[j][i] = sr;
+#pragma unroll
+            for (int p = 0; p < QP; ++p) q1[p][j][i] = qq[p];
+            float cc[2] = {te[0][j][i], (CP > 1) ? te[CP - 1][j][i] : 0.f};
+            float s1 = 0.f;
+            const float term = fwd_coord<MODEL, false>(qq, cc, kc, nt, s1);
+            ptot[0] += (4 * (tid + j * T) < H) ? term : 0.f;
+            d1[0][j][i] = cc[0];
+            if (CP > 1) d1[CP - 1][j][i] = cc[1];
+            sg1[j][i] = (4 * (tid + j * T) < H) ? s1 : 0.f;
+        }
+    block_reduce_vals<1>(ptot, red);
+    const float s_pos = score_from_sum<MODEL>(ptot[0], kc);
+    const float dpos = -0.5f * coef * sigmoidf(-s_pos);
+
+    // dL/dq1 from the positive score; dL/dt (candidate side of the positive score)
+    float gq1[QP][CH][4], gt_c[CP][CH][4];
+    float dots[2] = {0.f, 0.f};  // InterHT: <a_hat, d a_hat>, <b_hat, d b_hat> of the candidate t
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float aa[3] = {0.f, 0.f, 0.f};
+            const float dd[2] = {d1[0][j][i], (CP > 1) ? d1[CP - 1][j][i] : 0.f};
+            dq_accumulate<MODEL, false>(aa, dd, sg1[j][i], dpos, kc);
+#pragma unroll
+            for (int p = 0; p < QP; ++p) gq1[p][j][i] = aa[p];
+            float gc[2] = {0.f, 0.f};
+            if constexpr (MODEL == KGE_INTERHT) {
+                // v = A*bc - ac*Bv + M ; u = dL/dv ; d ac = -u*Bv ; d bc = u*A
+                const float u = -dpos * sg1[j][i];
+                const float d_ac = -u * q1[1][j][i], d_bc = u * q1[0][j][i];
+                gc[0] = d_ac;
+                gc[1] = d_bc;
+                dots[0] = fmaf(dd[0], d_ac, dots[0]);
+                dots[1] = fmaf(dd[1] - 1.0f, d_bc, dots[1]);
+            } else {
+                const float qq[3] = {q1[0][j][i], (QP > 1) ? q1[QP > 1 ? 1 : 0][j][i] : 0.f, 0.f};
+                const float cc[2] = {te[0][j][i], (CP > 1) ? te[CP - 1][j][i] : 0.f};
+                dc_accumulate<MODEL, false>(gc, qq, cc, dpos, kc);
+            }
+            gt_c[0][j][i] = gc[0];
+            if (CP > 1) gt_c[CP - 1][j][i] = gc[1];
+        }
+    if constexpr (MODEL == KGE_INTERHT) {
+        block_reduce_vals<2>(dots, red);
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                gt_c[0][j][i] = (gt_c[0][j][i] - d1[0][j][i] * dots[0]) * nt[0];
+                gt_c[1][j][i] = (gt_c[1][j][i] - (d1[1][j][i] - 1.0f) * dots[1]) * nt[1];
+            }
+    }
+
+    // chain: mode-form planes (q, acc) and single-form planes (q1, gq1)
+    if (!head) {  // same planes: add the two dL/dq
+#pragma unroll
+        for (int p = 0; p < QP; ++p)
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) gq1[p][j][i] += acc[p][j][i];
+    }
+    float dA[4] = {0.f, 0.f, 0.f, 0.f};  // InterHT: <A,dA>,<Bh,dB> for the single-form chain and the mode-form chain
+    if constexpr (MODEL == KGE_INTERHT) {
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                dA[0] = fmaf(q1[0][j][i], gq1[0][j][i], dA[0]);
+                dA[1] = fmaf(q1[1][j][i] - 1.0f, gq1[1][j][i], dA[1]);
+                dA[2] = fmaf(q[0][j][i], acc[0][j][i], dA[2]);
+                dA[3] = fmaf(q[1][j][i] - 1.0f, acc[1][j][i], dA[3]);
+            }
+        block_reduce_vals<4>(dA, red);
+    }
+    float* gh = A.GH + b * (long long)P.De;
+    float* gt = A.GT + b * (long long)P.De;
+    float* gr = A.GR + b * (long long)P.Dr;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+        const int k0 = 4 * (tid + j * T);
+        float oh[CP][4], ot[CP][4], orl[RP][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            // single-form chain: fixed entity = h
+            float ge[2], grr[2];
+            const float g1[3] = {gq1[0][j][i], (QP > 1) ? gq1[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? gq1[QP > 2 ? 2 : 0][j][i] : 0.f};
+            const float qa[3] = {q1[0][j][i], (QP > 1) ? q1[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? q1[QP > 2 ? 2 : 0][j][i] : 0.f};
+            const float e2[2] = {he[0][j][i], (CP > 1) ? he[CP - 1][j][i] : 0.f};
+            const float r2[2] = {rv[0][j][i], (RP > 1) ? rv[RP - 1][j][i] : 0.f};
+            chain_coord<MODEL>(ge, grr, g1, qa, e2, r2, false, kc, crs[j][i], srs[j][i], dA[0], dA[1], nh);
+            oh[0][i] = ge[0];
+            if (CP > 1) oh[CP - 1][i] = ge[1];
+            orl[0][i] = grr[0];
+            if (RP > 1) orl[RP - 1][i] = grr[1];
+            ot[0][i] = gt_c[0][j][i];
+            if (CP > 1) ot[CP - 1][i] = gt_c[CP - 1][j][i];
+            if (head) {  // mode-form chain: fixed entity = t
+                const float g2[3] = {acc[0][j][i], (QP > 1) ? acc[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? acc[QP > 2 ? 2 : 0][j][i] : 0.f};
+                const float qb[3] = {q[0][j][i], (QP > 1) ? q[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? q[QP > 2 ? 2 : 0][j][i] : 0.f};
+                const float t2[2] = {te[0][j][i], (CP > 1) ? te[CP - 1][j][i] : 0.f};
+                chain_coord<MODEL>(ge, grr, g2, qb, t2, r2, true, kc, crs[j][i], srs[j][i], dA[2], dA[3], nt);
+                ot[0][i] += ge[0];
+                if (CP > 1) ot[CP - 1][i] += ge[1];
+                orl[0][i] += grr[0];
+                if (RP > 1) orl[RP - 1][i] += grr[1];
+            }
+        }
+        if (k0 < H) {
+#pragma unroll
+            for (int p = 0; p < CP; ++p) {
+                *reinterpret_cast<float4*>(gh + p * H + k0) = make_float4(oh[p][0], oh[p][1], oh[p][2], oh[p][3]);
+                *reinterpret_cast<float4*>(gt + p * H + k0) = make_float4(ot[p][0], ot[p][1], ot[p][2], ot[p][3]);
+            }
+#pragma unroll
+            for (int p = 0; p < RP; ++p)
+                *reinterpret_cast<float4*>(gr + rel_offset<MODEL>(H, p) + k0) =
+                    make_float4(orl[p][0], orl[p][1], orl[p][2], orl[p][3]);
+            if constexpr (MODEL == KGE_INTERHT) {  // the outer thirds of the relation row get no gradient
+                *reinterpret_cast<float4*>(gr + k0) = make_float4(0.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4*>(gr + 2 * H + k0) = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    }
+    if (tid == 0) {
+        A.stats[2 * b] = m_b;
+        A.stats[2 * b + 1] = scale_b;
+        A.terms[b] = coef * log_sigmoid(s_pos);
+        A.terms[A.B + b] = coef * negterm;
+        if (MODEL == KGE_PROTATE) A.GM[b] = -(scale_b * gsum + dpos * ptot[0]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F2: per-bucket sort (one warp per entity): ascending item order whatever order the fill produced
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, int* __restrict__ out, long long E) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long e = warp; e < E; e += nwarps) {
+        const int beg = offsets[e], end = offsets[e + 1];
+        for (int idx = beg + lane; idx < end; idx += 32) {
+            const int it = in[idx];
+            int rank = 0;
+            for (int j = beg; j < end; ++j) rank += (in[j] < it) ? 1 : 0;
+            out[beg + rank] = it;
+        }
+    }
+}
+
+// F2b: S[b,n] <- dL/ds[b,n] = scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s))
+__global__ void __launch_bounds__(256)
+dscore_kernel(float* __restrict__ S, const float* __restrict__ stats, long long BN, int N, int adv, float alpha) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < BN; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / N;
+        const float s = S[i];
+        const float sc = stats[2 * b + 1];
+        S[i] = adv ? sc * expf(s * alpha - stats[2 * b]) * sigmoidf(s) : sc * sigmoidf(s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F3: entity-major gradient gather fused with Adam
+// ------------------------------------------------------------------------------------------------
+struct EntityArgs {
+    float* ent;
+    float* m;
+    float* v;
+    const float* Q;
+    const float* G;  // dL/ds [B,N]
+    const float* GH;
+    const float* GT;
+    const int* offsets;
+    const int* items;
+    int N;
+    long long BN, B;
+};
+
+template <int MODEL, int CH>
+__global__ void __launch_bounds__(256)
+train_entity_adam_kernel(Params P, CoordConsts kc, int head_i, const float* __restrict__ modulus, EntityArgs A,
+                         AdamScalars ad, float l3) {
+    constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
+    __shared__ float red[2 * 32];
+    const int tid = threadIdx.x, T = blockDim.x, H = P.H;
+    const bool head = head_i != 0;
+    if (MODEL == KGE_PROTATE) kc.modulus = __ldg(modulus);
+    for (long long e = blockIdx.x; e < P.E; e += gridDim.x) {
+        const int beg = A.offsets[e], end = A.offsets[e + 1];
+        float* row = A.ent + e * (long long)P.De;
+        float c[CP][CH][4], gc[CP][CH][4];
+#pragma unroll
+        for (int p = 0; p < CP; ++p)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const int k0 = 4 * (tid + j * T);
+                float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (k0 < H) val = *reinterpret_cast<const float4*>(row + p * H + k0);
+                c[p][j][0] = val.x; c[p][j][1] = val.y; c[p][j][2] = val.z; c[p][j][3] = val.w;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) gc[p][j][i] = 0.f;
+            }
+        float cn[2] = {0.f, 0.f};
+        if constexpr (MODEL == KGE_INTERHT) {
+            if (beg < end) {  // uniform over the block
+                float ss[2] = {0.f, 0.f};
+#pragma unroll
+                for (int j = 0; j < CH; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        ss[0] = fmaf(c[0][j][i], c[0][j][i], ss[0]);
+                        ss[1] = fmaf(c[1][j][i], c[1][j][i], ss[1]);
+                    }
+                block_reduce_vals<2>(ss, red);
+                cn[0] = 1.0f / sqrtf(ss[0]);
+                cn[1] = 1.0f / sqrtf(ss[1]);
+            }
+        }
+#pragma unroll 2
+        for (int jj = beg; jj < end; ++jj) {
+            const int item = A.items[jj];
+            if (item < A.BN) {
+                const float g = A.G[item];
+                const float* qb = A.Q + (long long)(item / A.N) * (QP * H);
+                float q[QP][CH][4];
+                load_coords<QP, CH>(q, qb, H, tid, T, H);
+                if constexpr (MODEL == KGE_INTERHT) {
+                    // v, u = dL/dv, d a_hat, d b_hat, then the two row dots of the normalisation backward
+                    float dac[CH][4], dbc[CH][4], dots[2] = {0.f, 0.f};
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float ac = c[0][j][i] * cn[0], bh = c[1][j][i] * cn[1], bc = bh + 1.0f;
+                            const float Aq = q[0][j][i], Bv = q[QP > 1 ? 1 : 0][j][i], Mq = q[QP > 2 ? 2 : 0][j][i];
+                            const float v = head ? (ac * Bv - Aq * bc + Mq) : (Aq * bc - ac * Bv + Mq);
+                            const float u = (4 * (tid + j * T) < H) ? -g * sgnf(v) : 0.f;
+                            dac[j][i] = head ? (u * Bv) : (-u * Bv);
+                            dbc[j][i] = head ? (-u * Aq) : (u * Aq);
+                            dots[0] = fmaf(ac, dac[j][i], dots[0]);
+                            dots[1] = fmaf(bh, dbc[j][i], dots[1]);
+                        }
+                    block_reduce_vals<2>(dots, red);
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float ac = c[0][j][i] * cn[0], bh = c[1][j][i] * cn[1];
+                            gc[0][j][i] += (dac[j][i] - ac * dots[0]) * cn[0];
+                            gc[CP - 1][j][i] += (dbc[j][i] - bh * dots[1]) * cn[1];
+                        }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float qq[3] = {q[0][j][i], (QP > 1) ? q[QP > 1 ? 1 : 0][j][i] : 0.f, 0.f};
+                            const float cc[2] = {c[0][j][i], (CP > 1) ? c[CP - 1][j][i] : 0.f};
+                            float g2[2] = {gc[0][j][i], (CP > 1) ? gc[CP - 1][j][i] : 0.f};
+                            if (head) dc_accumulate<MODEL, true>(g2, qq, cc, g, kc);
+                            else dc_accumulate<MODEL, false>(g2, qq, cc, g, kc);
+                            gc[0][j][i] = g2[0];
+                            if (CP > 1) gc[CP - 1][j][i] = g2[1];
+                        }
+                }
+            } else {  // this entity is the head / tail of positive b: add its compact gradient row
+                const long long j2 = item - A.BN;
+                const float* src = (j2 < A.B) ? (A.GH + j2 * P.De) : (A.GT + (j2 - A.B) * P.De);
+                float x[CP][CH][4];
+                load_coords<CP, CH>(x, src, H, tid, T, H);
+#pragma unroll
+                for (int p = 0; p < CP; ++p)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) gc[p][j][i] += x[p][j][i];
+            }
+        }
+        // Adam on the row, in the registers that hold it (rows without uses: g = 0)
+        float* mrow = A.m + e * (long long)P.De;
+        float* vrow = A.v + e * (long long)P.De;
+#pragma unroll
+        for (int p = 0; p < CP; ++p)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const int k0 = 4 * (tid + j * T);
+                if (k0 < H) {
+                    float4 mm = *reinterpret_cast<float4*>(mrow + p * H + k0);
+                    float4 vv = *reinterpret_cast<float4*>(vrow + p * H + k0);
+                    adam_update(c[p][j][0], gc[p][j][0], mm.x, vv.x, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+                    adam_update(c[p][j][1], gc[p][j][1], mm.y, vv.y, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+                    adam_update(c[p][j][2], gc[p][j][2], mm.z, vv.z, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+                    adam_update(c[p][j][3], gc[p][j][3], mm.w, vv.w, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+                    *reinterpret_cast<float4*>(row + p * H + k0) = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
+                    *reinterpret_cast<float4*>(mrow + p * H + k0) = mm;
+                    *reinterpret_cast<float4*>(vrow + p * H + k0) = vv;
+                }
+            }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F4: relation rows (sum GR[b] over b ascending) + Adam; pRotatE modulus
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+train_relation_adam_kernel(int Dr, const int64_t* __restrict__ pos, int B, const float* __restrict__ GR, float* rel,
+                           float* m, float* v, AdamScalars ad, float l3, int* scratch) {
+    // warp 0 lists the positives that use relation r, in ascending b (ballot + popc keeps the order)
+    extern __shared__ int match[];  // up to B entries
+    __shared__ int nmatch;
+    const long long r = blockIdx.x;
+    if (threadIdx.x < 32) {
+        int count = 0;
+        for (int base = 0; base < B; base += 32) {
+            const int b = base + threadIdx.x;
+            const bool hit = (b < B) && (pos[3 * (long long)b + 1] == r);
+            const unsigned mask = __ballot_sync(0xffffffffu, hit);
+            if (hit) match[count + __popc(mask & ((1u << threadIdx.x) - 1u))] = b;
+            count += __popc(mask);
+        }
+        if (threadIdx.x == 0) nmatch = count;
+    }
+    __syncthreads();
+    const int nm = nmatch;
+    for (int k = threadIdx.x; k < Dr; k += blockDim.x) {
+        float g = 0.f;
+        for (int j = 0; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
+        const long long i = r * Dr + k;
+        float pp = rel[i], mm = m[i], vv = v[i];
+        adam_update(pp, g, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+        rel[i] = pp;
+        m[i] = mm;
+        v[i] = vv;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+train_modulus_adam_kernel(const float* __restrict__ GM, int B, float* modulus, float* m, float* v, AdamScalars ad) {
+    __shared__ float red[32];
+    float acc = 0.f;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) acc += GM[b];
+    acc = block_sum(acc, red);
+    if (threadIdx.x == 0) {
+        float pp = modulus[0], mm = m[0], vv = v[0];
+        adam_update(pp, acc, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, 0.f);
+        modulus[0] = pp;
+        m[0] = mm;
+        v[0] = vv;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static inline size_t fz_align(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct FusedWs {
+    float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms, *small, *l3_ws;
+    int *counts, *offsets, *cursor, *items, *items_sorted, *block_sums;
+    size_t total;
+};
+
+static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
+    FusedWs w{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        void* p = base ? (void*)((char*)base + off) : nullptr;
+        off += fz_align(bytes);
+        return p;
+    };
+    const size_t qdim = (size_t)model_planes(P.model) * P.H;
+    w.S = (float*)take((size_t)B * N * sizeof(float));
+    w.Q = (float*)take((size_t)B * qdim * sizeof(float));
+    w.GH = (float*)take((size_t)B * P.De * sizeof(float));
+    w.GT = (float*)take((size_t)B * P.De * sizeof(float));
+    w.GR = (float*)take((size_t)B * P.Dr * sizeof(float));
+    w.GM = (float*)take((size_t)B * sizeof(float));
+    w.stats = (float*)take((size_t)2 * B * sizeof(float));
+    w.terms = (float*)take((size_t)(2 * B + 8) * sizeof(float));
+    w.small = (float*)take(16 * sizeof(float));
+    w.l3_ws = (float*)take(1024 * sizeof(float));
+    w.counts = (int*)take((size_t)(P.E + 1) * sizeof(int));
+    w.offsets = (int*)take((size_t)(P.E + 1) * sizeof(int));
+    w.cursor = (int*)take((size_t)(P.E + 1) * sizeof(int));
+    w.items = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
+    w.items_sorted = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
+    w.block_sums = (int*)take((size_t)((P.E + 1024) / 1024 + 2) * sizeof(int));
+    w.total = off;
+    return w;
+}
+
+size_t fused_step_workspace_bytes(const Params& P, int64_t B, int64_t N) { return fused_carve(P, B, N, nullptr).total; }
+
+bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, int64_t N, const void* ent,
+                           const void* rel) {
+    if (!lo.detach_weights && lo.negative_adversarial_sampling) return false;  // TF graph-model gradient: v1 path
+    if (P.interht_eps != 0.f) return false;
+    if (!vec4_ok(P, ent, rel)) return false;
+    if (P.H > 4096) return false;
+    if (B * N + 2 * B >= 0x7fffffffLL) return false;
+    return true;
+}
+
+__global__ void fused_finalize_reg_kernel(float* small, float lambda) {
+    const float reg = lambda * (small[4] + small[5]);
+    small[3] = reg;
+    small[2] += reg;
+}
+
+template <int MODEL, int CH, int RPI>
+static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                                const kge_loss_opts& lo, const AdamScalars& ad, const FusedWs& ws, cudaStream_t st) {
+    cudaError_t e;
+    const int head = (mode == KGE_MODE_HEAD_BATCH) ? 1 : 0;
+    CoordConsts kc{P.gamma, P.phase_div, P.inv_phase_div, 0.f};
+    const int chunks = (P.H / 4 + CH - 1) / CH;
+    const int threads = std::max(32, ((chunks + 31) / 32) * 32);
+    const long long BN = B * N;
+    {
+        ProfScope ps(ST_SWEEP, st);
+        if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
+        SweepArgs A{ent, rel, modulus, pos, neg, w, (int)B, (int)N, lo.negative_adversarial_sampling, lo.uni_weight,
+                    lo.adversarial_temperature, ws.S, ws.Q, ws.GH, ws.GT, ws.GR, ws.GM, ws.stats, ws.terms, ws.counts};
+        train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)B, threads, 0, st>>>(P, kc, head, A);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    {
+        ProfScope ps(ST_BUCKETS, st);
+        if ((e = launch_scan_fill(mode, pos, neg, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items, ws.block_sums,
+                                  st)) != cudaSuccess)
+            return e;
+        const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
+        bucket_sort_kernel<<<sb, 256, 0, st>>>(ws.offsets, ws.items, ws.items_sorted, P.E);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    {
+        ProfScope ps(ST_DSCORE, st);
+        const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
+        dscore_kernel<<<db, 256, 0, st>>>(ws.S, ws.stats, BN, (int)N, lo.negative_adversarial_sampling,
+                                          lo.adversarial_temperature);
+        if ((e = launch_loss_final(ws.terms, B, ws.small, st)) != cudaSuccess) return e;
+    }
+    float l3 = 0.f;
+    if (lo.regularization != 0.f) {
+        ProfScope ps(ST_REG, st);
+        l3 = lo.regularization;
+        if ((e = launch_l3_sum_cubes(ent, (int64_t)P.E * P.De, ws.small + 4, ws.l3_ws, st)) != cudaSuccess) return e;
+        if ((e = launch_l3_sum_cubes(rel, (int64_t)P.R * P.Dr, ws.small + 5, ws.l3_ws, st)) != cudaSuccess) return e;
+        fused_finalize_reg_kernel<<<1, 1, 0, st>>>(ws.small, l3);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    {
+        ProfScope ps(ST_ENTITY, st);
+        EntityArgs A{ent, m_ent, v_ent, ws.Q, ws.S, ws.GH, ws.GT, ws.offsets, ws.items_sorted, (int)N, BN, B};
+        const int blocks = (int)std::min<long long>(P.E, 32LL * sm_count());
+        train_entity_adam_kernel<MODEL, CH><<<blocks, threads, 0, st>>>(P, kc, head, modulus, A, ad, l3);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    {
+        ProfScope ps(ST_RELATION, st);
+        train_relation_adam_kernel<<<(unsigned)P.R, 256, (size_t)B * sizeof(int), st>>>(P.Dr, pos, (int)B, ws.GR, rel, m_rel, v_rel, ad, l3, nullptr);
+        if (MODEL == KGE_PROTATE) train_modulus_adam_kernel<<<1, 256, 0, st>>>(ws.GM, (int)B, modulus, m_mod, v_mod, ad);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+template <int MODEL>
+static cudaError_t fused_dispatch_ch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                                     float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                                     const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                                     const kge_loss_opts& lo, const AdamScalars& ad, const FusedWs& ws, cudaStream_t st) {
+    constexpr bool IH = (MODEL == KGE_INTERHT);
+#define KGE_GO(CH, RPI) \
+    return fused_launch<MODEL, CH, RPI>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N, lo, ad, ws, st)
+    if (P.H <= 1024) { KGE_GO(1, (IH ? 4 : 8)); }
+    if (P.H <= 2048) { KGE_GO(2, (IH ? 2 : 4)); }
+    KGE_GO(4, (IH ? 1 : 2));
+#undef KGE_GO
+}
+
+// out_small: device float[16]: [0..2] loss3, [3] reg
+cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                                    float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                                    const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                                    const kge_loss_opts& lo, const kge_adam_opts& ao, void* wsp, size_t ws_bytes,
+                                    float** out_small, cudaStream_t st) {
+    if (ws_bytes < fused_step_workspace_bytes(P, B, N)) return cudaErrorInvalidValue;
+    const FusedWs ws = fused_carve(P, B, N, wsp);
+    *out_small = ws.small;
+    const AdamScalars ad = adam_scalars(ao);
+#define KGE_CASE(M) \
+    case M: return fused_dispatch_ch<M>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N, lo, ad, ws, st)
+    switch (P.model) {
+        KGE_CASE(KGE_TRANSE);
+        KGE_CASE(KGE_DISTMULT);
+        KGE_CASE(KGE_COMPLEX);
+        KGE_CASE(KGE_ROTATE);
+        KGE_CASE(KGE_PROTATE);
+        KGE_CASE(KGE_INTERHT);
+    }
+#undef KGE_CASE
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace kge

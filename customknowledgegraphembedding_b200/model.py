@@ -145,7 +145,8 @@ class KGEModel(nn.Module):
         if g.get("amsgrad") or g.get("weight_decay", 0) != 0 or g.get("maximize") or g.get("differentiable"):
             return None
         mine = [p for p in self.parameters() if p.requires_grad]
-        if len(g["params"]) != len(mine) or any(a is not b for a, b in zip(sorted(g["params"], key=id), sorted(mine, key=id))):
+        theirs = [p for p in g["params"] if p.requires_grad]  # Adam skips parameters that never get a gradient
+        if len(theirs) != len(mine) or any(a is not b for a, b in zip(sorted(theirs, key=id), sorted(mine, key=id))):
             return None
         return g
 

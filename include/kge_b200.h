@@ -180,6 +180,10 @@ KGE_API int kge_eval_rank(const kge_model_desc *desc, int mode, const float *ent
  * Fused train step, tables and batch resident in HBM.  Replaces the body of KGEModel.train_step (U9) /
  * Trainer.train_step_fn (supervisor.py:15-28): both score passes, the loss, the backward and dense Adam
  * on both tables (+ the pRotatE modulus) in one call.  `mode` HEAD_BATCH or TAIL_BATCH.
+ *   deterministic: step variant.  0 (default) and 1 run the second-generation step (fused score+loss+dL/dq
+ *     sweep, entity-major gradient gather fused with Adam; fixed summation order, bit-reproducible) whenever it
+ *     applies, else the first-generation kernels with the atomic (0) / fixed-order (1) backward;
+ *     2 / 3 force the first-generation kernels with the atomic / fixed-order backward.
  *   adam_m_*, adam_v_*: optimizer state, same shapes as the parameters (modulus: 1 float each; NULL unless pRotatE).
  *   loss3 (device, 3 floats): positive_sample_loss, negative_sample_loss, loss (+ reg4[0] when -r).
  *   reg1 (device, 1 float, may be NULL when regularization == 0): the regularisation term.
