@@ -18,6 +18,9 @@
 //
 // Replaces the body of KGEModel.train_step (loss restated at
 // /root/reference/tensorflow_codes/model.py:4-44).  Results are bit-reproducible run to run.
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <vector>
 
 #include "kge_coord.cuh"
@@ -162,15 +165,22 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     // online-softmax state, replicated in the lanes of warp 0
     float m_run = -INFINITY, z_run = 0.f, l_run = 0.f, g_run = 0.f;
 
+    // every candidate use is counted for the bucket build (integer atomics, off the critical path)
+    for (int n = tid; n < N; n += T) atomicAdd(A.counts + __ldg(A.neg + b * N + n), 1);
+    int cid[RPI];
+#pragma unroll
+    for (int rr = 0; rr < RPI; ++rr) cid[rr] = (rr < N) ? (int)__ldg(A.neg + b * N + rr) : 0;
+
     for (int n0 = 0; n0 < N; n0 += RPI) {
         float c[RPI][CP][CH][4];
         float sg[(MODEL == KGE_INTERHT) ? RPI : 1][CH][4];
 #pragma unroll
+        for (int rr = 0; rr < RPI; ++rr) load_coords<CP, CH>(c[rr], A.ent + (long long)cid[rr] * P.De, H, tid, T, H);
+        // candidate ids of the NEXT row group: their latency hides behind this group's arithmetic
+#pragma unroll
         for (int rr = 0; rr < RPI; ++rr) {
-            const int n = n0 + rr;
-            const long long cid = (n < N) ? A.neg[b * N + n] : 0;
-            if (n < N && tid == rr) atomicAdd(A.counts + cid, 1);
-            load_coords<CP, CH>(c[rr], A.ent + cid * (long long)P.De, H, tid, T, H);
+            const int n = n0 + RPI + rr;
+            cid[rr] = (n < N) ? (int)__ldg(A.neg + b * N + n) : 0;
         }
         if constexpr (MODEL == KGE_INTERHT) {  // candidate norms first
             float ss[2 * RPI];
@@ -471,7 +481,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
 // F2: per-bucket sort (one warp per entity): ascending item order whatever order the fill produced
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, int* __restrict__ out, long long E) {
+bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, int* __restrict__ out,
+                   int* __restrict__ out_b, long long E, int N) {
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -482,6 +493,7 @@ bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, 
             int rank = 0;
             for (int j = beg; j < end; ++j) rank += (in[j] < it) ? 1 : 0;
             out[beg + rank] = it;
+            out_b[beg + rank] = it / N;  // positive index of a candidate use (unused for head / tail uses)
         }
     }
 }
@@ -510,6 +522,7 @@ struct EntityArgs {
     const float* GT;
     const int* offsets;
     const int* items;
+    const int* items_b;
     int N;
     long long BN, B;
 };
@@ -559,7 +572,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, int head_i, const float* __re
             const int item = A.items[jj];
             if (item < A.BN) {
                 const float g = A.G[item];
-                const float* qb = A.Q + (long long)(item / A.N) * (QP * H);
+                const float* qb = A.Q + (long long)A.items_b[jj] * (QP * H);
                 float q[QP][CH][4];
                 load_coords<QP, CH>(q, qb, H, tid, T, H);
                 if constexpr (MODEL == KGE_INTERHT) {
@@ -694,7 +707,7 @@ static inline size_t fz_align(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct FusedWs {
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms, *small, *l3_ws;
-    int *counts, *offsets, *cursor, *items, *items_sorted, *block_sums;
+    int *counts, *offsets, *cursor, *items, *items_sorted, *items_b, *block_sums;
     size_t total;
 };
 
@@ -722,6 +735,7 @@ static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
     w.cursor = (int*)take((size_t)(P.E + 1) * sizeof(int));
     w.items = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
     w.items_sorted = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
+    w.items_b = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
     w.block_sums = (int*)take((size_t)((P.E + 1024) / 1024 + 2) * sizeof(int));
     w.total = off;
     return w;
@@ -735,7 +749,7 @@ bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, 
     if (P.interht_eps != 0.f) return false;
     if (!vec4_ok(P, ent, rel)) return false;
     if (P.H > 4096) return false;
-    if (B * N + 2 * B >= 0x7fffffffLL) return false;
+    if (B * N + 2 * B >= 0x7fffffffLL || P.E >= 0x7fffffffLL) return false;
     return true;
 }
 
@@ -771,7 +785,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                                   st)) != cudaSuccess)
             return e;
         const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
-        bucket_sort_kernel<<<sb, 256, 0, st>>>(ws.offsets, ws.items, ws.items_sorted, P.E);
+        bucket_sort_kernel<<<sb, 256, 0, st>>>(ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     {
@@ -792,7 +806,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     }
     {
         ProfScope ps(ST_ENTITY, st);
-        EntityArgs A{ent, m_ent, v_ent, ws.Q, ws.S, ws.GH, ws.GT, ws.offsets, ws.items_sorted, (int)N, BN, B};
+        EntityArgs A{ent, m_ent, v_ent, ws.Q, ws.S, ws.GH, ws.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B};
         const int blocks = (int)std::min<long long>(P.E, 32LL * sm_count());
         train_entity_adam_kernel<MODEL, CH><<<blocks, threads, 0, st>>>(P, kc, head, modulus, A, ad, l3);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
@@ -814,6 +828,19 @@ static cudaError_t fused_dispatch_ch(const Params& P, int mode, float* ent, floa
     constexpr bool IH = (MODEL == KGE_INTERHT);
 #define KGE_GO(CH, RPI) \
     return fused_launch<MODEL, CH, RPI>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N, lo, ad, ws, st)
+    // tuning override (experiments only): KGE_SWEEP_CFG="CH,RPI"
+    static int o_ch = -1, o_rpi = -1;
+    if (o_ch < 0) {
+        o_ch = 0;
+        if (const char* e = getenv("KGE_SWEEP_CFG")) sscanf(e, "%d,%d", &o_ch, &o_rpi);
+    }
+    if (!IH && o_ch > 0 && P.H <= 1024 * o_ch) {
+        if (o_ch == 1 && o_rpi == 4) { KGE_GO(1, 4); }
+        if (o_ch == 1 && o_rpi == 2) { KGE_GO(1, 2); }
+        if (o_ch == 2 && o_rpi == 4) { KGE_GO(2, 4); }
+        if (o_ch == 2 && o_rpi == 2) { KGE_GO(2, 2); }
+        if (o_ch == 2 && o_rpi == 8) { KGE_GO(2, 8); }
+    }
     if (P.H <= 1024) { KGE_GO(1, (IH ? 4 : 8)); }
     if (P.H <= 2048) { KGE_GO(2, (IH ? 2 : 4)); }
     KGE_GO(4, (IH ? 1 : 2));
