@@ -16,7 +16,7 @@ ABI_VERSION = 1
 # kge_model_id / kge_mode / kge_ws_kind
 MODEL_IDS = {"TransE": 0, "DistMult": 1, "ComplEx": 2, "RotatE": 3, "pRotatE": 4, "InterHT": 5}
 MODE_IDS = {"single": 0, "head-batch": 1, "tail-batch": 2}
-WS_BACKWARD, WS_LOSS, WS_EVAL, WS_TRAIN_STEP, WS_TRAIN_STEP_HOST = range(5)
+WS_BACKWARD, WS_LOSS, WS_EVAL, WS_TRAIN_STEP, WS_TRAIN_STEP_HOST, WS_TRAIN_APPLY = range(6)
 
 KGE_OK = 0
 KGE_ERR_INVALID_ARGUMENT = -1
@@ -47,6 +47,10 @@ class AdamOpts(C.Structure):
     ]
 
 
+class StepBuffers(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("S", "Q", "GH", "GT", "GR", "GM", "stats", "terms")]
+
+
 _P = C.c_void_p
 _I64 = C.c_int64
 _SZ = C.c_size_t
@@ -67,6 +71,11 @@ PROTOTYPES = {
                                  C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _P, _SZ, _P]),
     "kge_train_step_host": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                       C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _SZ, _P]),
+    "kge_train_sweep": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
+                                  C.POINTER(StepBuffers), _P]),
+    "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
+                                  C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P, _P,
+                                  _P, _SZ, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
     "kge_profile_enable": (C.c_int, [C.c_int]),
     "kge_profile_num_stages": (C.c_int, []),

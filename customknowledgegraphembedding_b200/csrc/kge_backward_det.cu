@@ -284,6 +284,14 @@ __global__ void __launch_bounds__(256) det_modulus_kernel(const float* __restric
     if (threadIdx.x == 0) grad_modulus[0] += acc;
 }
 
+cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, int* counts,
+                             cudaStream_t st) {
+    const long long total = BN + 2 * B;
+    const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
+    det_histogram_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, counts);
+    return cudaGetLastError();
+}
+
 // exclusive scan of counts -> offsets (+ a copy in cursor), then scatter every use into its bucket
 cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
                              int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st) {

@@ -39,6 +39,8 @@ cudaError_t launch_score_backward_det(const Params& P, int mode, const float* en
                                       int64_t N, const float* dscore, float* grad_ent, float* grad_rel,
                                       float* grad_modulus, void* ws, size_t ws_bytes, cudaStream_t st);
 
+cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, int* counts,
+                             cudaStream_t st);
 cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
                              int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st);
 

@@ -243,6 +243,56 @@ int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* r
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step(copy loss)");
 }
 
+int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
+                    const float* modulus, const int64_t* positive, const int64_t* negative,
+                    const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
+                    const float* wsum, int64_t B_total, const kge_step_buffers* out, void* stream) {
+    Params P;
+    int rc = make_params(desc, &P);
+    if (rc) return rc;
+    if (mode != KGE_MODE_HEAD_BATCH && mode != KGE_MODE_TAIL_BATCH)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "negative batch mode %d not supported", mode);
+    if (B <= 0 || N <= 0 || B_total < B) return fail(KGE_ERR_INVALID_ARGUMENT, "bad batch sizes");
+    if (!entity || !relation || !positive || !negative || !loss_opts || !out)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if (!loss_opts->uni_weight && !subsampling_weight)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "subsampling_weight is NULL without uni_weight");
+    if (P.model == KGE_PROTATE && !modulus) return fail(KGE_ERR_INVALID_ARGUMENT, "pRotatE needs modulus");
+    if (!fused_step_applicable(P, *loss_opts, B_total, N, entity, relation))
+        return fail(KGE_ERR_UNSUPPORTED, "kge_train_sweep: the fused step does not apply to this configuration");
+    cudaError_t e = launch_train_sweep(P, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
+                                       *loss_opts, wsum, B_total, *out, (cudaStream_t)stream);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_sweep");
+}
+
+int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
+                    float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
+                    float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
+                    const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
+                    const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
+                    int64_t entity_hi, float* loss3, float* reg1, void* ws, size_t ws_bytes, void* stream) {
+    Params P;
+    int rc = check_train_args(desc, &P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                              adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all,
+                              (const void*)1, B_all, N, loss_opts, adam_opts);
+    if (rc) return rc;
+    if (!gathered || !loss3) return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if (entity_lo < 0 || entity_hi < entity_lo || entity_hi > P.E) return fail(KGE_ERR_INVALID_ARGUMENT, "bad entity range");
+    if (!fused_step_applicable(P, *loss_opts, B_all, N, entity, relation))
+        return fail(KGE_ERR_UNSUPPORTED, "kge_train_apply: the fused step does not apply to this configuration");
+    const size_t need = fused_step_workspace_bytes(P, B_all, N);
+    if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "train apply needs %zu workspace bytes, got %zu", need, ws_bytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* small = nullptr;
+    cudaError_t e = launch_train_apply(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                                       adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
+                                       *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, ws, ws_bytes, &small, st);
+    if (e != cudaSuccess) return fail_cuda(e, "kge_train_apply");
+    e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_apply(copy loss)");
+}
+
 int kge_train_step_host(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
                         float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
                         float* adam_m_modulus, float* adam_v_modulus, const int64_t* host_positive, const int64_t* host_negative,

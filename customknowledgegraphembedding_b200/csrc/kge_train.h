@@ -14,4 +14,13 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
                                     const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
                                     const kge_loss_opts& lo, const kge_adam_opts& ao, void* ws, size_t ws_bytes,
                                     float** out_small, cudaStream_t st);
+cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
+                               const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                               const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
+                               cudaStream_t st);
+cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                               float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                               const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
+                               const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
+                               int64_t e_hi, void* ws, size_t ws_bytes, float** out_small, cudaStream_t st);
 }

@@ -73,7 +73,9 @@ struct SweepArgs {
     int B, N, adv, uni;
     float alpha;
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
-    int* counts;
+    int* counts;         // NULL: uses are counted later (multi-rank apply phase)
+    const float* wsum;   // NULL: sum the B local weights; else device scalar with the global sum
+    int B_total;         // positives of the global batch (uniform weights: coef = 1 / B_total)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -100,14 +102,16 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     // ---- coef_b = w_b / sum(w) or 1/B -------------------------------------------------------------
     float coef;
     if (A.uni) {
-        coef = 1.0f / (float)A.B;
+        coef = 1.0f / (float)A.B_total;
+    } else if (A.wsum != nullptr) {
+        coef = __ldg(A.w + b) / __ldg(A.wsum);
     } else {
         float part[1] = {0.f};
         for (int i = tid; i < A.B; i += T) part[0] += __ldg(A.w + i);
         block_reduce_vals<1>(part, red);
         coef = __ldg(A.w + b) / part[0];
     }
-    if (tid == 0) {  // every use of an entity row is counted for the bucket build (integer atomics)
+    if (tid == 0 && A.counts != nullptr) {  // every use of an entity row is counted for the bucket build
         atomicAdd(A.counts + h, 1);
         atomicAdd(A.counts + t, 1);
     }
@@ -166,7 +170,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     float m_run = -INFINITY, z_run = 0.f, l_run = 0.f, g_run = 0.f;
 
     // every candidate use is counted for the bucket build (integer atomics, off the critical path)
-    for (int n = tid; n < N; n += T) atomicAdd(A.counts + __ldg(A.neg + b * N + n), 1);
+    if (A.counts != nullptr)
+        for (int n = tid; n < N; n += T) atomicAdd(A.counts + __ldg(A.neg + b * N + n), 1);
     int cid[RPI];
 #pragma unroll
     for (int rr = 0; rr < RPI; ++rr) cid[rr] = (rr < N) ? (int)__ldg(A.neg + b * N + rr) : 0;
@@ -471,8 +476,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     if (tid == 0) {
         A.stats[2 * b] = m_b;
         A.stats[2 * b + 1] = scale_b;
-        A.terms[b] = coef * log_sigmoid(s_pos);
-        A.terms[A.B + b] = coef * negterm;
+        A.terms[2 * b] = coef * log_sigmoid(s_pos);
+        A.terms[2 * b + 1] = coef * negterm;
         if (MODEL == KGE_PROTATE) A.GM[b] = -(scale_b * gsum + dpos * ptot[0]);
     }
 }
@@ -525,6 +530,7 @@ struct EntityArgs {
     const int* items_b;
     int N;
     long long BN, B;
+    long long e_lo, e_hi;  // rows this rank owns
 };
 
 template <int MODEL, int CH>
@@ -536,7 +542,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, int head_i, const float* __re
     const int tid = threadIdx.x, T = blockDim.x, H = P.H;
     const bool head = head_i != 0;
     if (MODEL == KGE_PROTATE) kc.modulus = __ldg(modulus);
-    for (long long e = blockIdx.x; e < P.E; e += gridDim.x) {
+    for (long long e = A.e_lo + blockIdx.x; e < A.e_hi; e += gridDim.x) {
         const int beg = A.offsets[e], end = A.offsets[e + 1];
         float* row = A.ent + e * (long long)P.De;
         float c[CP][CH][4], gc[CP][CH][4];
@@ -700,6 +706,23 @@ train_modulus_adam_kernel(const float* __restrict__ GM, int B, float* modulus, f
     }
 }
 
+// loss terms [B][2] (pos, neg) -> loss3, fixed order
+__global__ void __launch_bounds__(256) loss_final2_kernel(const float* __restrict__ terms, int B, float* loss3) {
+    __shared__ float red[32];
+    float p = 0.f, n = 0.f;
+    for (int i = threadIdx.x; i < B; i += blockDim.x) {
+        p += terms[2 * i];
+        n += terms[2 * i + 1];
+    }
+    p = block_sum(p, red);
+    n = block_sum(n, red);
+    if (threadIdx.x == 0) {
+        loss3[0] = -p;
+        loss3[1] = -n;
+        loss3[2] = (-p + -n) / 2.0f;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -759,30 +782,58 @@ __global__ void fused_finalize_reg_kernel(float* small, float lambda) {
     small[2] += reg;
 }
 
+// One step = sweep (data-parallel over positives) + apply (entity-row-parallel over [e_lo, e_hi)).
+// Single GPU: both phases on the local batch.  Multi rank: sweep on the local batch, the per-positive
+// buffers are all-gathered by the caller, apply runs on the global batch for the rows this rank owns.
+struct FusedCall {
+    int phase;  // 0 both, 1 sweep only, 2 apply only
+    // sweep
+    const int64_t* pos;
+    const int64_t* neg;
+    const float* w;
+    int64_t B;
+    const float* wsum;
+    int64_t B_total;
+    // apply
+    const int64_t* pos_all;
+    const int64_t* neg_all;
+    int64_t B_all;
+    long long e_lo, e_hi;
+    // per-positive buffers (sweep: written for the local batch; apply: read for the global batch)
+    float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
+};
+
 template <int MODEL, int CH, int RPI>
 static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
                                 float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
-                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
-                                const kge_loss_opts& lo, const AdamScalars& ad, const FusedWs& ws, cudaStream_t st) {
+                                const FusedCall& fc, int64_t N, const kge_loss_opts& lo, const AdamScalars& ad,
+                                const FusedWs& ws, cudaStream_t st) {
     cudaError_t e;
     const int head = (mode == KGE_MODE_HEAD_BATCH) ? 1 : 0;
     CoordConsts kc{P.gamma, P.phase_div, P.inv_phase_div, 0.f};
     const int chunks = (P.H / 4 + CH - 1) / CH;
     const int threads = std::max(32, ((chunks + 31) / 32) * 32);
+    if (fc.phase != 2) {
+        ProfScope ps(ST_SWEEP, st);
+        if (fc.phase == 0 && (e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
+        SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
+                    lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
+                    fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
+        train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (fc.phase == 1) return cudaSuccess;
+    }
+    const int64_t B = fc.B_all;
     const long long BN = B * N;
     {
-        ProfScope ps(ST_SWEEP, st);
-        if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
-        SweepArgs A{ent, rel, modulus, pos, neg, w, (int)B, (int)N, lo.negative_adversarial_sampling, lo.uni_weight,
-                    lo.adversarial_temperature, ws.S, ws.Q, ws.GH, ws.GT, ws.GR, ws.GM, ws.stats, ws.terms, ws.counts};
-        train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)B, threads, 0, st>>>(P, kc, head, A);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    }
-    {
         ProfScope ps(ST_BUCKETS, st);
-        if ((e = launch_scan_fill(mode, pos, neg, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items, ws.block_sums,
-                                  st)) != cudaSuccess)
+        if ((e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
+        if (fc.phase == 2) {
+            if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
+            if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, st)) != cudaSuccess) return e;
+        }
+        if ((e = launch_scan_fill(mode, fc.pos_all, fc.neg_all, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items,
+                                  ws.block_sums, st)) != cudaSuccess)
             return e;
         const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
         bucket_sort_kernel<<<sb, 256, 0, st>>>(ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N);
@@ -791,9 +842,10 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     {
         ProfScope ps(ST_DSCORE, st);
         const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
-        dscore_kernel<<<db, 256, 0, st>>>(ws.S, ws.stats, BN, (int)N, lo.negative_adversarial_sampling,
+        dscore_kernel<<<db, 256, 0, st>>>(fc.S, fc.stats, BN, (int)N, lo.negative_adversarial_sampling,
                                           lo.adversarial_temperature);
-        if ((e = launch_loss_final(ws.terms, B, ws.small, st)) != cudaSuccess) return e;
+        loss_final2_kernel<<<1, 256, 0, st>>>(fc.terms, (int)B, ws.small);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     float l3 = 0.f;
     if (lo.regularization != 0.f) {
@@ -804,17 +856,20 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         fused_finalize_reg_kernel<<<1, 1, 0, st>>>(ws.small, l3);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
-    {
+    if (fc.e_hi > fc.e_lo) {
         ProfScope ps(ST_ENTITY, st);
-        EntityArgs A{ent, m_ent, v_ent, ws.Q, ws.S, ws.GH, ws.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B};
-        const int blocks = (int)std::min<long long>(P.E, 32LL * sm_count());
+        EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
+                     fc.e_lo, fc.e_hi};
+        const int blocks = (int)std::min<long long>(fc.e_hi - fc.e_lo, 32LL * sm_count());
         train_entity_adam_kernel<MODEL, CH><<<blocks, threads, 0, st>>>(P, kc, head, modulus, A, ad, l3);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     {
+        // relation rows and the modulus are replicated: every rank applies the same fixed-order update
         ProfScope ps(ST_RELATION, st);
-        train_relation_adam_kernel<<<(unsigned)P.R, 256, (size_t)B * sizeof(int), st>>>(P.Dr, pos, (int)B, ws.GR, rel, m_rel, v_rel, ad, l3, nullptr);
-        if (MODEL == KGE_PROTATE) train_modulus_adam_kernel<<<1, 256, 0, st>>>(ws.GM, (int)B, modulus, m_mod, v_mod, ad);
+        train_relation_adam_kernel<<<(unsigned)P.R, 256, (size_t)B * sizeof(int), st>>>(P.Dr, fc.pos_all, (int)B, fc.GR, rel,
+                                                                                         m_rel, v_rel, ad, l3, nullptr);
+        if (MODEL == KGE_PROTATE) train_modulus_adam_kernel<<<1, 256, 0, st>>>(fc.GM, (int)B, modulus, m_mod, v_mod, ad);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     return cudaSuccess;
@@ -823,28 +878,33 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
 template <int MODEL>
 static cudaError_t fused_dispatch_ch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
                                      float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
-                                     const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
-                                     const kge_loss_opts& lo, const AdamScalars& ad, const FusedWs& ws, cudaStream_t st) {
+                                     const FusedCall& fc, int64_t N, const kge_loss_opts& lo, const AdamScalars& ad,
+                                     const FusedWs& ws, cudaStream_t st) {
     constexpr bool IH = (MODEL == KGE_INTERHT);
 #define KGE_GO(CH, RPI) \
-    return fused_launch<MODEL, CH, RPI>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N, lo, ad, ws, st)
-    // tuning override (experiments only): KGE_SWEEP_CFG="CH,RPI"
-    static int o_ch = -1, o_rpi = -1;
-    if (o_ch < 0) {
-        o_ch = 0;
-        if (const char* e = getenv("KGE_SWEEP_CFG")) sscanf(e, "%d,%d", &o_ch, &o_rpi);
-    }
-    if (!IH && o_ch > 0 && P.H <= 1024 * o_ch) {
-        if (o_ch == 1 && o_rpi == 4) { KGE_GO(1, 4); }
-        if (o_ch == 1 && o_rpi == 2) { KGE_GO(1, 2); }
-        if (o_ch == 2 && o_rpi == 4) { KGE_GO(2, 4); }
-        if (o_ch == 2 && o_rpi == 2) { KGE_GO(2, 2); }
-        if (o_ch == 2 && o_rpi == 8) { KGE_GO(2, 8); }
-    }
+    return fused_launch<MODEL, CH, RPI>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, ad, ws, st)
     if (P.H <= 1024) { KGE_GO(1, (IH ? 4 : 8)); }
     if (P.H <= 2048) { KGE_GO(2, (IH ? 2 : 4)); }
     KGE_GO(4, (IH ? 1 : 2));
 #undef KGE_GO
+}
+
+static cudaError_t fused_dispatch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                                  float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                                  const FusedCall& fc, int64_t N, const kge_loss_opts& lo, const AdamScalars& ad,
+                                  const FusedWs& ws, cudaStream_t st) {
+#define KGE_CASE(M) \
+    case M: return fused_dispatch_ch<M>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, ad, ws, st)
+    switch (P.model) {
+        KGE_CASE(KGE_TRANSE);
+        KGE_CASE(KGE_DISTMULT);
+        KGE_CASE(KGE_COMPLEX);
+        KGE_CASE(KGE_ROTATE);
+        KGE_CASE(KGE_PROTATE);
+        KGE_CASE(KGE_INTERHT);
+    }
+#undef KGE_CASE
+    return cudaErrorInvalidValue;
 }
 
 // out_small: device float[16]: [0..2] loss3, [3] reg
@@ -856,19 +916,35 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
     if (ws_bytes < fused_step_workspace_bytes(P, B, N)) return cudaErrorInvalidValue;
     const FusedWs ws = fused_carve(P, B, N, wsp);
     *out_small = ws.small;
-    const AdamScalars ad = adam_scalars(ao);
-#define KGE_CASE(M) \
-    case M: return fused_dispatch_ch<M>(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, pos, neg, w, B, N, lo, ad, ws, st)
-    switch (P.model) {
-        KGE_CASE(KGE_TRANSE);
-        KGE_CASE(KGE_DISTMULT);
-        KGE_CASE(KGE_COMPLEX);
-        KGE_CASE(KGE_ROTATE);
-        KGE_CASE(KGE_PROTATE);
-        KGE_CASE(KGE_INTERHT);
-    }
-#undef KGE_CASE
-    return cudaErrorInvalidValue;
+    FusedCall fc{0, pos, neg, w, B, nullptr, B, pos, neg, B, 0, P.E, ws.S, ws.Q, ws.GH, ws.GT, ws.GR, ws.GM, ws.stats, ws.terms};
+    return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
+                          ws, st);
+}
+
+// multi-rank pieces (kge_train_sweep / kge_train_apply)
+cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
+                               const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
+                               const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
+                               cudaStream_t st) {
+    FusedWs ws{};  // the sweep alone needs no workspace
+    FusedCall fc{1, pos, neg, w, B, wsum, B_total, nullptr, nullptr, 0, 0, 0, o.S, o.Q, o.GH, o.GT, o.GR, o.GM, o.stats, o.terms};
+    kge_adam_opts ao{0.f, 0.9f, 0.999f, 1e-8f, 1, 0};
+    return fused_dispatch(P, mode, const_cast<float*>(ent), const_cast<float*>(rel), const_cast<float*>(modulus), nullptr,
+                          nullptr, nullptr, nullptr, nullptr, nullptr, fc, N, lo, adam_scalars(ao), ws, st);
+}
+
+cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
+                               float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
+                               const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
+                               const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
+                               int64_t e_hi, void* wsp, size_t ws_bytes, float** out_small, cudaStream_t st) {
+    if (ws_bytes < fused_step_workspace_bytes(P, B_all, N)) return cudaErrorInvalidValue;
+    const FusedWs ws = fused_carve(P, B_all, N, wsp);
+    *out_small = ws.small;
+    FusedCall fc{2, nullptr, nullptr, nullptr, 0, nullptr, B_all, pos_all, neg_all, B_all, e_lo, e_hi,
+                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms};
+    return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
+                          ws, st);
 }
 
 }  // namespace kge

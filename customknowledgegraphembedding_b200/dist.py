@@ -1,0 +1,209 @@
+"""Multi-GPU plumbing: one process per GPU, ``torch.distributed`` (NCCL) between the kernel calls.
+
+The path shards twice:
+
+* **eval** -- candidates are row-range sharded: each rank counts ``score > true`` over its entity range for ALL
+  queries (``kge_eval_rank(entity_lo, entity_hi)``) and the integer counters are summed with one all-reduce.
+* **train** -- positives are data-parallel in the sweep (``kge_train_sweep``), entity rows are owner-parallel in
+  the apply (``kge_train_apply``): the per-positive buffers are all-gathered, each rank gathers gradients and
+  applies Adam for the rows it owns, the updated row ranges are broadcast back.  The loss and every update are
+  those of ONE step on the global batch (sum of subsampling weights all-reduced first), bit-identical on every
+  rank and independent of which rank swept which positive.
+
+The reference's own mechanism is replicas with an implicit gradient all-reduce under ``tf.distribute``
+(/root/reference/tensorflow_codes/run.py:8-17, supervisor.py:26-30); this keeps its semantics (replicated
+tables, one optimizer step per global batch) and replaces the dense gradient all-reduce.
+
+The two kernel calls are the methods ``_sweep`` / ``_apply`` (and ``local_fn`` for eval) so that the host logic
+is testable on CPU over ``gloo`` with stand-ins (tests/test_dist_cpu.py).
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib, ops
+from ._lib import AdamOpts, LossOpts, StepBuffers
+
+
+def shard_range(n: int, rank: int, world: int):
+    """Contiguous row range of ``rank``: ceil(n / world) rows each, the tail ranks may be short or empty."""
+    rows = (n + world - 1) // world
+    lo = min(rank * rows, n)
+    return lo, min(lo + rows, n)
+
+
+def _world(group=None):
+    if not dist.is_available() or not dist.is_initialized():
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def _coalesced(group, device):
+    """Batch several NCCL calls into one group launch when torch exposes the coalescing manager."""
+    cm = getattr(dist, "_coalescing_manager", None)
+    if cm is None or device.type != "cuda":
+        return contextlib.nullcontext()
+    try:
+        return cm(group=group, device=device, async_ops=False)
+    except TypeError:  # signature differs in this torch: fall back to one launch per call
+        return contextlib.nullcontext()
+
+
+# --------------------------------------------------------------------------------------------------
+# eval
+# --------------------------------------------------------------------------------------------------
+def rank_queries_sharded(model, queries, mode, filter_indptr=None, filter_idx=None, group=None, local_fn=None):
+    """(true_score, n_greater, n_equal) over ALL entities, each rank scoring only its row range."""
+    rank, world = _world(group)
+    lo, hi = shard_range(model.nentity, rank, world)
+    fn = local_fn if local_fn is not None else model.rank_queries
+    true_score, n_greater, n_equal = fn(queries, mode, filter_indptr, filter_idx, entity_lo=lo, entity_hi=hi)
+    if world > 1:
+        counts = torch.stack([n_greater, n_equal])
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
+        n_greater, n_equal = counts[0], counts[1]
+    return true_score, n_greater, n_equal
+
+
+def test_step(model, test_triples, all_true_triples, args, group=None, local_fn=None):
+    """``KGEModel.test_step`` with the candidates sharded over the ranks of ``group``; same metrics on every rank."""
+    def rank_fn(queries, mode, indptr, idx):
+        return rank_queries_sharded(model, queries, mode, indptr, idx, group=group, local_fn=local_fn)
+    return type(model).test_step(model, test_triples, all_true_triples, args, rank_fn=rank_fn)
+
+
+# --------------------------------------------------------------------------------------------------
+# train
+# --------------------------------------------------------------------------------------------------
+_BUFFERS = ("S", "Q", "GH", "GT", "GR", "GM", "stats", "terms")
+
+
+class DataParallelStep:
+    """``step.train_step(train_iterator, args)`` == ``KGEModel.train_step`` on the concatenation of every rank's batch."""
+
+    def __init__(self, model, optimizer, group=None):
+        self.model, self.optimizer, self.group = model, optimizer, group
+        self.rank, self.world = _world(group)
+        self.lo, self.hi = shard_range(model.nentity, self.rank, self.world)
+        self._local: Dict[str, torch.Tensor] = {}
+        self._gathered: Dict[str, torch.Tensor] = {}
+        self._ws: Optional[torch.Tensor] = None
+        self._shape = None
+
+    # ---- buffers -----------------------------------------------------------------------------------
+    def _row_sizes(self, N):
+        m = self.model
+        planes = {"ComplEx": 2, "RotatE": 2, "InterHT": 3}.get(m.model_name, 1)
+        return {"S": N, "Q": planes * m.hidden_dim, "GH": m.entity_dim, "GT": m.entity_dim, "GR": m.relation_dim,
+                "GM": 1, "stats": 2, "terms": 2}
+
+    def _ensure(self, B, N, dev):
+        if self._shape == (B, N, dev):
+            return
+        sizes = self._row_sizes(N)
+        self._local = {k: torch.empty(B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
+        self._gathered = {k: torch.empty(self.world * B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
+        self._gathered["pos"] = torch.empty((self.world * B, 3), dtype=torch.int64, device=dev)
+        self._gathered["neg"] = torch.empty((self.world * B, N), dtype=torch.int64, device=dev)
+        self._shape = (B, N, dev)
+
+    # ---- the two kernel calls (overridable: tests/test_dist_cpu.py) ------------------------------------
+    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
+        m = self.model
+        B, N = neg.shape
+        bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        with torch.cuda.device(pos.device):
+            _lib.check(_lib.load().kge_train_sweep(
+                C.byref(m._desc()), ops.mode_id(mode), ops._ptr(m.entity_embedding), ops._ptr(m.relation_embedding),
+                ops._ptr(m._modulus()), ops._ptr(pos), ops._ptr(neg), ops._ptr(w), B, N, C.byref(loss_opts),
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._stream()), "kge_train_sweep")
+
+    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out):
+        m, opt = self.model, self.optimizer
+        B_all, N = neg_all.shape
+        ent, rel, mod = m.entity_embedding, m.relation_embedding, m._modulus()
+        st_e, st_r = opt.state[ent], opt.state[rel]
+        st_m = opt.state[mod] if mod is not None else None
+        desc = m._desc()
+        need = ops.workspace_bytes(_lib.WS_TRAIN_APPLY, desc, B_all, N)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=ent.device)
+        bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
+        P = ops._ptr
+        with torch.cuda.device(ent.device):
+            _lib.check(_lib.load().kge_train_apply(
+                C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
+                P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
+                P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
+                C.byref(adam), C.byref(bufs), self.lo, self.hi, P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws),
+                self._ws.numel(), ops._stream()), "kge_train_apply")
+
+    # ---- one global step -----------------------------------------------------------------------------
+    def train_step(self, train_iterator, args, sync: bool = True):
+        m, opt = self.model, self.optimizer
+        m.train()
+        positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
+        if mode not in ("head-batch", "tail-batch"):
+            raise ValueError("mode %s not supported" % mode)
+        group_opts = m._fused_adam_plan(opt)
+        if group_opts is None:
+            raise RuntimeError("DataParallelStep needs torch.optim.Adam / FusedAdam over exactly the model's parameters")
+        dev = m.entity_embedding.device
+        adv = bool(getattr(args, "negative_adversarial_sampling", False))
+        uni = bool(getattr(args, "uni_weight", False))
+        reg = float(getattr(args, "regularization", 0.0))
+        loss_opts = LossOpts(int(adv), int(uni), 1, 0, float(getattr(args, "adversarial_temperature", 1.0)), reg)
+        pos = positive_sample.to(dev, non_blocking=True).contiguous()
+        neg = negative_sample.to(dev, non_blocking=True).contiguous()
+        w = subsampling_weight.to(dev, dtype=torch.float32, non_blocking=True).contiguous()
+        B, N = neg.shape
+        self._ensure(B, N, dev)
+        # global sum of the subsampling weights: the loss is that of ONE step on the global batch
+        wsum = w.sum().reshape(1)
+        if self.world > 1:
+            dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
+        self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
+        if self.world > 1:
+            with _coalesced(self.group, dev):
+                dist.all_gather_into_tensor(self._gathered["pos"], pos, group=self.group)
+                dist.all_gather_into_tensor(self._gathered["neg"], neg, group=self.group)
+                for k in _BUFFERS:
+                    dist.all_gather_into_tensor(self._gathered[k], self._local[k], group=self.group)
+            pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
+        else:
+            pos_all, neg_all = pos, neg
+            for k in _BUFFERS:
+                self._gathered[k] = self._local[k]
+        states = [m._adam_state(opt, p) for p in (m.entity_embedding, m.relation_embedding)]
+        if m._modulus() is not None:
+            states.append(m._adam_state(opt, m._modulus()))
+        for s in states:
+            s["step"] += 1
+        b1, b2 = group_opts["betas"]
+        adam = AdamOpts(float(group_opts["lr"]), float(b1), float(b2), float(group_opts["eps"]), int(states[0]["step"]), 0)
+        out = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._apply(mode, pos_all, neg_all, loss_opts, adam, out)
+        self._share_rows()
+        if not sync:
+            return out
+        pos_l, neg_l, loss, regv = out.tolist()
+        log = {"regularization": regv} if reg != 0.0 else {}
+        log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
+        return log
+
+    def _share_rows(self):
+        """Every rank broadcasts the entity rows it owns (its Adam update) to the others."""
+        if self.world <= 1:
+            return
+        ent = self.model.entity_embedding.data
+        with _coalesced(self.group, ent.device):
+            for r in range(self.world):
+                lo, hi = shard_range(self.model.nentity, r, self.world)
+                if hi > lo:
+                    src = dist.get_global_rank(self.group, r) if self.group is not None else r
+                    dist.broadcast(ent[lo:hi], src=src, group=self.group)

@@ -314,15 +314,18 @@ class KGEModel(nn.Module):
                              entity_lo, entity_hi, to(filter_indptr), to(filter_idx))
 
     @staticmethod
-    def test_step(model, test_triples, all_true_triples, args):
+    def test_step(model, test_triples, all_true_triples, args, rank_fn=None):
         """Evaluate the model on test or valid datasets: filtered MRR / MR / HITS@1,3,10 over
-        head-batch then tail-batch queries (same query order and metric arithmetic as upstream)."""
+        head-batch then tail-batch queries (same query order and metric arithmetic as upstream).
+        ``rank_fn(queries, mode, filter_indptr, filter_idx)`` replaces the local K5 call (dist.test_step)."""
         model.eval()
         if getattr(args, "countries", False):
             raise NotImplementedError("--countries AUC-PR evaluation is outside the B200 hot path (SURVEY 8(f) N4)")
         dev = model.entity_embedding.device
-        if dev.type != "cuda":
+        if dev.type != "cuda" and rank_fn is None:
             raise RuntimeError("KGEModel.test_step: model is on %s; move it to a CUDA device (no CPU fallback)" % dev)
+        if rank_fn is None:
+            rank_fn = model.rank_queries
         nentity = getattr(args, "nentity", None) or model.nentity
         T = np.asarray(test_triples, dtype=np.int64).reshape(-1, 3)
         maps = model._filter_maps(all_true_triples)
@@ -332,8 +335,8 @@ class KGEModel(nn.Module):
             for lo in range(0, len(T), chunk):
                 q = T[lo:lo + chunk]
                 indptr, idx = KGEModel.build_filter_csr(maps, q, mode, nentity)
-                _, n_greater, n_equal = model.rank_queries(torch.from_numpy(q), mode, torch.from_numpy(indptr),
-                                                           torch.from_numpy(idx))
+                _, n_greater, n_equal = rank_fn(torch.from_numpy(q), mode, torch.from_numpy(indptr),
+                                                torch.from_numpy(idx))
                 ranks.append((1 + n_greater).cpu().numpy())
                 ties += int(n_equal.sum().item())
         ranks = np.concatenate(ranks) if ranks else np.zeros(0, dtype=np.int64)

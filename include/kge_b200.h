@@ -206,6 +206,40 @@ KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *ent
                         float *host_loss4, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * Multi-GPU split of the step (one process per GPU; the caller does the NCCL plumbing between the two calls).
+ * The step shards twice: positives are data-parallel in the SWEEP, entity rows are owner-parallel in the APPLY.
+ *
+ *   kge_train_sweep  : scores, loss terms and dL/dq for the B LOCAL positives; writes the per-positive buffers
+ *                      (S [B,N] scores, Q [B,planes*H] staged planes, GH/GT [B,De], GR [B,Dr] compact gradient
+ *                      rows, GM [B], stats [B,2], terms [B,2]).  wsum: device scalar = sum of the subsampling
+ *                      weights over the GLOBAL batch (all-reduced by the caller; NULL = local sum);
+ *                      B_total = positives of the global batch (uniform weighting).
+ *   (caller)         : all-gather every buffer, positive and negative over the ranks -> B_all = sum of B.
+ *   kge_train_apply  : on the gathered buffers: dL/ds, the per-entity use lists, then for the entity rows
+ *                      [entity_lo, entity_hi) this rank owns: gradient gather + Adam (m, v of other rows are not
+ *                      touched); relation rows and the pRotatE modulus are replicated and updated identically on
+ *                      every rank (fixed summation order).  loss3 / reg1 as in kge_train_step.
+ *   (caller)         : all-gather (or broadcast) the updated row ranges of the entity table.
+ * Applies when kge_train_step's second-generation path applies; otherwise KGE_ERR_UNSUPPORTED.
+ */
+typedef struct {
+    float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
+} kge_step_buffers;
+
+KGE_API int kge_train_sweep(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
+                            const float *modulus, const int64_t *positive, const int64_t *negative,
+                            const float *subsampling_weight, int64_t B, int64_t N, const kge_loss_opts *loss_opts,
+                            const float *wsum, int64_t B_total, const kge_step_buffers *out, void *stream);
+
+KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
+                            float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
+                            float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus,
+                            const int64_t *positive_all, const int64_t *negative_all, int64_t B_all, int64_t N,
+                            const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
+                            const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, float *loss3,
+                            float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/*
  * Measurement hooks (bench.py): when enabled, kge_train_step* brackets each of its stages with CUDA
  * events on the caller's stream.  kge_profile_read synchronises those events and returns, per stage, the
  * summed device time in ms and the number of kernel launches since the last reset.  Stage names:
@@ -221,7 +255,8 @@ typedef enum {
     KGE_WS_LOSS = 1,
     KGE_WS_EVAL = 2,
     KGE_WS_TRAIN_STEP = 3,
-    KGE_WS_TRAIN_STEP_HOST = 4
+    KGE_WS_TRAIN_STEP_HOST = 4,
+    KGE_WS_TRAIN_APPLY = 5 /* kge_train_apply: pass B_all as B */
 } kge_ws_kind;
 
 /* Bytes of workspace the call of that kind needs for (desc, B, N) -- for KGE_WS_EVAL pass Q as B and the

@@ -1,0 +1,41 @@
+"""torchrun --nproc-per-node 2 scratch/dist_check.py : real 2-GPU run of dist.DataParallelStep / dist.test_step
+against the single-process result on the concatenated batch."""
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import customknowledgegraphembedding_b200 as kb
+from customknowledgegraphembedding_b200 import dist as kd
+from oracle import kge_oracle as ko
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), 1e-3
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+E, R, H, B, N = 2000, 11, 256, 64, 128
+for name in ("RotatE", "TransE", "InterHT"):
+    om = ko.make_model(name, E, R, H, 12.0, seed=0)
+    de, dr, tr = ko.model_flags(name)
+    def mk():
+        m = kb.KGEModel(name, E, R, H, 12.0, de, dr, tr); m.load_state_dict(om.state_dict()); return m.cuda()
+    a, b = mk(), mk()
+    oa = torch.optim.Adam(filter(lambda p: p.requires_grad, a.parameters()), lr=lr)
+    ob = torch.optim.Adam(filter(lambda p: p.requires_grad, b.parameters()), lr=lr)
+    args = ko.Args(negative_adversarial_sampling=True, cuda=True, nentity=E, nrelation=R)
+    step = kd.DataParallelStep(b, ob)
+    for s in range(3):
+        batches = [ko.synthetic_batch(E, R, B, N, seed=100 * s + r, mode="tail-batch" if s % 2 else "head-batch") for r in range(world)]
+        full = (torch.cat([x[0] for x in batches]), torch.cat([x[1] for x in batches]), torch.cat([x[2] for x in batches]), batches[0][3])
+        la = kb.KGEModel.train_step(a, oa, iter([full]), args)
+        lb = step.train_step(iter([batches[rank]]), args)
+        d = float((a.entity_embedding - b.entity_embedding).abs().max())
+        dr_ = float((a.relation_embedding - b.relation_embedding).abs().max())
+        if rank == 0:
+            print(name, "step", s, "loss single", la["loss"], "sharded", lb["loss"], "max|dE|", d, "max|dR|", dr_, flush=True)
+        assert abs(la["loss"] - lb["loss"]) <= 2e-6 * abs(la["loss"]) and d <= 5e-3 * lr and dr_ <= 5e-3 * lr
+    rng = np.random.RandomState(1)
+    true = [(int(x), int(y), int(z)) for x, y, z in zip(rng.randint(0, 50, 600), rng.randint(0, R, 600), rng.randint(0, E, 600))]
+    m1 = kb.KGEModel.test_step(a, true[:100], true, args); r1 = a.last_eval["ranks"].copy()
+    m2 = kd.test_step(a, true[:100], true, args); r2 = a.last_eval["ranks"]
+    assert np.array_equal(r1, r2) and m1 == m2
+    if rank == 0:
+        print(name, "sharded eval == single eval, MRR", m2["MRR"], flush=True)
+dist.barrier(); dist.destroy_process_group()
+if rank == 0: print("DIST CHECK OK")
