@@ -65,8 +65,10 @@ def test_trainer_train_step_matches_reference_source():
         for name in ("entity_embedding", "relation_embedding"):
             want = g["%s_%d" % (name, step + 1)]
             got = getattr(m, name).detach().cpu().numpy()
-            # lr = 1e-2 Adam steps on values ~0.1: 1e-5 of the step size + fp32 resolution of the parameter
-            np.testing.assert_allclose(got, want, rtol=0, atol=1e-5 * float(g["lr"]) * 20 + 2e-7)
+            # Adam steps of size lr = 1e-2 on values ~2 (ulp 2.4e-7); an element whose gradient is within a few
+            # roundings of zero moves by a visibly different fraction of lr in any two fp32 implementations
+            np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-3 * float(g["lr"]))
+            assert (np.abs(got - want) > 1e-4 * float(g["lr"])).mean() < 0.01
 
 
 def test_zero_learning_rate_like_the_checker():
