@@ -209,6 +209,11 @@ int kge_eval_rank(const kge_model_desc* desc, int mode, const float* entity, con
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_eval_rank");
 }
 
+int kge_eval_set_tensor_path(int on) {
+    eval_set_tensor_path(on);
+    return KGE_OK;
+}
+
 size_t kge_workspace_bytes(int kind, const kge_model_desc* desc, int64_t B, int64_t N) {
     Params P;
     if (kind == KGE_WS_LOSS) return loss_workspace_bytes(B);

@@ -357,7 +357,8 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
 // ---- launcher --------------------------------------------------------------------------------
 static inline size_t ev_align(size_t x) { return (x + 255) & ~(size_t)255; }
 
-size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t /*nfilter*/) {
+size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter) {
+    if (eval_mma_applies(P)) return eval_mma_workspace_bytes(P, Q, nfilter);
     size_t total = ev_align((size_t)Q * model_planes(P.model) * P.H * sizeof(float));
     if (P.model == KGE_INTERHT) total += 2 * ev_align((size_t)P.E * sizeof(float));
     return total + 256;
@@ -411,14 +412,39 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
     return cudaSuccess;
 }
 
+cudaError_t launch_eval_stage(const Params& P, bool head, const float* ent, const float* rel, const int64_t* queries,
+                              int64_t Q, float* Qs, cudaStream_t st) {
+    const size_t smem = (size_t)(model_planes(P.model) * P.H + 4 + 32) * sizeof(float);
+#define KGE_CASE(M)                                                                                                  \
+    case M:                                                                                                          \
+        if (smem > 48 * 1024)                                                                                        \
+            cudaFuncSetAttribute(eval_stage_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);      \
+        eval_stage_kernel<M><<<(unsigned)Q, 128, smem, st>>>(P, head ? 1 : 0, ent, rel, queries, Qs);               \
+        break
+    switch (P.model) {
+        KGE_CASE(KGE_TRANSE);
+        KGE_CASE(KGE_DISTMULT);
+        KGE_CASE(KGE_COMPLEX);
+        KGE_CASE(KGE_ROTATE);
+        KGE_CASE(KGE_PROTATE);
+        KGE_CASE(KGE_INTERHT);
+        default: return cudaErrorInvalidValue;
+    }
+#undef KGE_CASE
+    return cudaGetLastError();
+}
+
 cudaError_t launch_eval_rank(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
                              const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
                              const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
                              int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes,
                              cudaStream_t st) {
-    if (ws_bytes < eval_workspace_bytes(P, Q, 0)) return cudaErrorInvalidValue;
     auto* ng = reinterpret_cast<unsigned long long*>(n_greater);
     auto* ne = reinterpret_cast<unsigned long long*>(n_equal);
+    if (eval_mma_applies(P))
+        return launch_eval_rank_mma(P, mode, ent, rel, queries, Q, e_lo, e_hi, filter_indptr, filter_idx, true_score, ng,
+                                    ne, accumulate, ws, ws_bytes, st);
+    if (ws_bytes < eval_workspace_bytes(P, Q, 0)) return cudaErrorInvalidValue;
     const bool head = (mode == KGE_MODE_HEAD_BATCH);
 #define KGE_CASE(M)                                                                                                  \
     case M:                                                                                                          \

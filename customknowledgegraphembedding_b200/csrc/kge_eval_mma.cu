@@ -1,0 +1,543 @@
+// K5-T: tcgen05 path of the filtered full-entity ranking for the GEMM-shaped models (sm_100a).
+//
+// For DistMult and ComplEx the score of (query q, candidate e) is a dot product over K = entity_dim
+// coordinates: S = Qs [Q,K] x Ent^T [K,E].  This file runs that product on the 5th-gen
+// tensor cores and keeps the ranking-by-counting epilogue of K5 (kge_eval.cu): the [Q,E] matrix never leaves
+// the SM, two integer counters per query do.
+//
+//   precision   3xTF32: every fp32 operand x is split into hi = tf32(x) and lo = tf32(x - hi); the tile
+//               accumulates lo*hi + hi*lo + hi*hi in fp32 (TMEM).  Relative error per product <= ~3 * 2^-22,
+//               i.e. the same order as fp32 summation-order noise over K terms.
+//   operands    split once per call into K-major workspaces [rows, Kpad] (Kpad = K rounded up to 32, zero
+//               filled), read by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 2-stage ring of
+//               96 KB stages: A = 128 queries x 32 k (hi, lo), B = 256 entities x 32 k (hi, lo).
+//   MMA         one elected thread: 12 x tcgen05.mma.cta_group::1.kind::tf32 (M128 N256 K8) per stage,
+//               tcgen05.commit releases the stage / publishes the accumulator.
+//   accumulator 2 x 256 TMEM columns (all 512): the epilogue of tile i overlaps the MMAs of tile i+1.
+//   epilogue    4 warps, thread = query row (TMEM lane), tcgen05.ld 32x32b.x32; each score is compared with
+//               the query's true score; the true entity and the filtered candidates are skipped BY ID
+//               (sorted per-query filter list + cursor), so no bit-exact re-evaluation is needed.
+//   true score  the same kernel in DIAG mode: B = the gathered true-entity rows of the 128 queries, the
+//               diagonal of the tile is the true score -- same arithmetic as every other candidate, so a
+//               candidate with an identical row ties exactly (n_equal keeps its meaning).
+//   schedule    persistent CTAs (one per SM), tile = (entity tile, query tile) with the query tile fastest so
+//               that concurrently running CTAs share the B tile in L2.
+#include <cuda.h>
+
+#include <algorithm>
+#include <climits>
+
+#include "kge_internal.h"
+
+namespace kge {
+namespace mma {
+
+constexpr int BM = 128;      // queries per tile (TMEM lanes)
+constexpr int BN = 256;      // entities per tile (TMEM columns per accumulator)
+constexpr int BK = 32;       // fp32 coordinates per stage row = 128 bytes = one swizzle span
+constexpr int UMMA_K = 8;    // K of one tcgen05.mma.kind::tf32
+constexpr int STAGES = 2;
+constexpr int kThreads = 192;  // warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..5 epilogue
+constexpr uint32_t A_BYTES = BM * BK * 4;                    // 16 KB
+constexpr uint32_t B_BYTES = BN * BK * 4;                    // 32 KB
+constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;  // hi + lo of both = 96 KB
+constexpr uint32_t SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + 128;
+constexpr uint32_t TMEM_COLS = 512;
+constexpr long long kEntityChunk = 32768;  // rows of the split B workspace per pass
+
+// ---- PTX wrappers ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > (1LL << 32)) __trap();  // ~2 s at 1.9 GHz
+    }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+
+// Shared-memory matrix descriptor, K-major operand, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
+// bits [0,14) start >> 4 | [16,30) LBO >> 4 (unused with swizzle, 1) | [32,46) SBO >> 4 | [46,48) version 1 |
+// [61,64) layout 2 = SWIZZLE_128B.  Advancing K by 8 tf32 = 32 B adds 2 to the start field.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+// Instruction descriptor kind::tf32: D fp32 (bits [4,6) = 1), A/B tf32 (bits [7,10) = [10,13) = 2), both K-major,
+// N >> 3 at bit 17, M >> 4 at bit 24.
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// 32 lanes x 32 consecutive columns -> 32 registers per thread (thread = lane = accumulator row)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
+        "tcgen05.wait::ld.sync.aligned;"  // same asm statement: no consumer can be scheduled before the wait
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ---- operand split ------------------------------------------------------------------------------
+// round-to-nearest-even onto the tf32 grid (10 explicit mantissa bits); inputs are finite table values
+__device__ __forceinline__ float tf32_rne(float x) {
+    uint32_t u = __float_as_uint(x);
+    u += 0xFFFu + ((u >> 13) & 1u);
+    return __uint_as_float(u & 0xFFFFE000u);
+}
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+    hi = tf32_rne(x);
+    lo = tf32_rne(x - hi);  // x - hi is exact in fp32
+}
+
+// rows of `src` (pitch floats apart; row = gather ? row named by the query : row0 + r) -> hi / lo [rows, Kpad]
+__global__ void __launch_bounds__(256)
+split_rows_kernel(const float* __restrict__ src, long long pitch, long long row0, const int64_t* __restrict__ queries,
+                  int gather_col, long long rows, int K, int Kpad, float* __restrict__ hi, float* __restrict__ lo) {
+    const int k4n = Kpad >> 2;
+    const long long total = rows * k4n;
+    const bool vec = (K % 4 == 0) && (pitch % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / k4n;
+        const int k = (int)(i - r * k4n) * 4;
+        const long long srow = (gather_col >= 0) ? queries[3 * r + gather_col] : row0 + r;
+        const float* p = src + srow * pitch + k;
+        float x[4];
+        if (vec && k + 3 < K) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+            x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) x[j] = (k + j < K) ? __ldg(p + j) : 0.f;
+        }
+        float h[4], l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) split_tf32(x[j], h[j], l[j]);
+        *reinterpret_cast<float4*>(hi + r * Kpad + k) = make_float4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<float4*>(lo + r * Kpad + k) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+// ---- per-query sorted filter lists ------------------------------------------------------------------
+// One warp per query: rank sort of its CSR segment (ties broken by position) into int32 ids.  Segments are
+// short (wn18rr: mean 1.4-2.1, p99 14, max 473 -- SURVEY 8(c)); O(n^2 / 32) per warp.
+__global__ void __launch_bounds__(256)
+filter_sort_kernel(const int64_t* __restrict__ indptr, const int64_t* __restrict__ idx, long long Q, int* __restrict__ sidx) {
+    const int lane = threadIdx.x & 31;
+    const long long q = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (q >= Q) return;
+    const long long b = indptr[q], n = indptr[q + 1] - b;
+    for (long long i = lane; i < n; i += 32) {
+        const int64_t x = idx[b + i];
+        long long rank = 0;
+        for (long long j = 0; j < n; ++j) {
+            const int64_t y = idx[b + j];
+            rank += (y < x || (y == x && j < i)) ? 1 : 0;
+        }
+        sidx[b + rank] = (int)x;
+    }
+}
+
+// ---- the tile kernel ------------------------------------------------------------------------------
+struct TileArgs {
+    long long Q;
+    long long b_row_id0;  // global entity id of row 0 of the B workspace (count mode)
+    long long b_rows;     // rows of the B workspace that are candidates
+    int nkb;              // Kpad / BK
+    int nqt;              // query tiles
+    int net;              // entity tiles (count mode)
+    int true_col;         // column of `queries` naming the true entity: 0 head-batch, 2 tail-batch
+    const int64_t* queries;
+    const int64_t* indptr;  // CSR offsets of the filter lists (NULL = unfiltered)
+    const int* sidx;        // per-query sorted filter ids
+    float* true_score;
+    unsigned long long* n_greater;
+    unsigned long long* n_equal;
+};
+
+template <bool DIAG>
+__global__ void __launch_bounds__(kThreads, 1)
+eval_mma_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
+                const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo, const TileArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms are 1024-byte aligned
+    const uint32_t bars = base + STAGES * STAGE_BYTES;
+    // barriers: full[s] @ +0, empty[s] @ +16, tfull[a] @ +32, tempty[a] @ +48, TMEM base address @ +64
+    auto full = [&](int s) { return bars + 8u * s; };
+    auto empty = [&](int s) { return bars + 16u + 8u * s; };
+    auto tfull = [&](int s) { return bars + 32u + 8u * s; };
+    auto tempty = [&](int s) { return bars + 48u + 8u * s; };
+    const uint32_t tmem_slot = bars + 64u;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmAhi);
+        tma_prefetch_desc(&tmAlo);
+        tma_prefetch_desc(&tmBhi);
+        tma_prefetch_desc(&tmBlo);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full(s), 1);   // the producer's arrive.expect_tx
+            mbar_init(empty(s), 1);  // tcgen05.commit of the MMA thread
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull(s), 1);   // tcgen05.commit after the last k-block
+            mbar_init(tempty(s), 4);  // one lane of each epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    const int ntiles = DIAG ? a.nqt : a.nqt * a.net;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const int qt = DIAG ? tile : tile % a.nqt;
+                const int brow = DIAG ? qt * BM : (tile / a.nqt) * BN;
+                for (int kb = 0; kb < a.nkb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(empty(s), ((it / STAGES) & 1u) ^ 1u);
+                    mbar_arrive_expect_tx(full(s), STAGE_BYTES);
+                    const uint32_t st = base + s * STAGE_BYTES;
+                    tma_load_2d(st, &tmAhi, full(s), kb * BK, qt * BM);
+                    tma_load_2d(st + A_BYTES, &tmAlo, full(s), kb * BK, qt * BM);
+                    tma_load_2d(st + 2 * A_BYTES, &tmBhi, full(s), kb * BK, brow);
+                    tma_load_2d(st + 2 * A_BYTES + B_BYTES, &tmBlo, full(s), kb * BK, brow);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+                const int acc = tcount & 1u;
+                mbar_wait(tempty(acc), ((tcount >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d = tmem_base + acc * BN;
+                for (int kb = 0; kb < a.nkb; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    mbar_wait(full(s), (it / STAGES) & 1u);
+                    tc_fence_after();
+                    const uint32_t st = base + s * STAGE_BYTES;
+                    const uint64_t ahi = umma_desc_sw128(st), alo = umma_desc_sw128(st + A_BYTES);
+                    const uint64_t bhi = umma_desc_sw128(st + 2 * A_BYTES), blo = umma_desc_sw128(st + 2 * A_BYTES + B_BYTES);
+                    // small terms first: lo*hi, hi*lo, then hi*hi
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, alo + 2 * k, bhi + 2 * k, (kb | k) != 0);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, blo + 2 * k, 1u);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, bhi + 2 * k, 1u);
+                    umma_commit(empty(s));  // frees the stage once these MMAs have read it
+                }
+                umma_commit(tfull(acc));  // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4, thread = query row =====
+        const int wq = warp & 3;
+        const int row = wq * 32 + lane;
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            const int acc = tcount & 1u;
+            const int qt = DIAG ? tile : tile % a.nqt;
+            const long long q = (long long)qt * BM + row;
+            const bool qok = q < a.Q;
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
+            if constexpr (DIAG) {
+                mbar_wait(tfull(acc), (tcount >> 1) & 1u);
+                tc_fence_after();
+                float v[32];
+                tmem_ld32(taddr + wq * 32, v);  // columns = the rows this warp owns: the diagonal block
+                float s = 0.f;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) s = (j == lane) ? v[j] : s;
+                if (qok) a.true_score[q] = s;
+            } else {
+                const long long e0 = a.b_row_id0 + (long long)(tile / a.nqt) * BN;  // global id of column 0
+                const long long e_end = a.b_row_id0 + a.b_rows;
+                float t = 0.f;
+                int te = -1, cur = 0, fe = 0, nextf = INT_MAX;
+                if (qok) {
+                    t = a.true_score[q];
+                    te = (int)a.queries[3 * q + a.true_col];
+                    if (a.indptr != nullptr) {
+                        int lo = (int)a.indptr[q];
+                        fe = (int)a.indptr[q + 1];
+                        int hi = fe;  // first entry >= e0
+                        while (lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            if (a.sidx[mid] < e0) lo = mid + 1;
+                            else hi = mid;
+                        }
+                        cur = lo;
+                        if (cur < fe) nextf = a.sidx[cur];
+                    }
+                }
+                mbar_wait(tfull(acc), (tcount >> 1) & 1u);
+                tc_fence_after();
+                int gt = 0, eq = 0;
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    float v[32];
+                    __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the per-lane paths below
+                    tmem_ld32(taddr + c * 32, v);
+                    const long long eb = e0 + c * 32;
+                    const bool live = qok && eb < e_end;
+                    const bool special = ((unsigned long long)((long long)te - eb) < 32ull) ||
+                                         ((unsigned long long)((long long)nextf - eb) < 32ull) || (eb + 32 > e_end);
+                    if (!live) {
+                        // padding rows / columns past the candidate range: nothing to count
+                    } else if (!special) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            gt += (v[j] > t) ? 1 : 0;
+                            eq += (v[j] == t) ? 1 : 0;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const long long e = eb + j;
+                            bool ok = (e < e_end) && (e != te);
+                            if (e == nextf) {
+                                ok = false;
+                                do {
+                                    ++cur;
+                                    nextf = (cur < fe) ? a.sidx[cur] : INT_MAX;
+                                } while (nextf == e);
+                            }
+                            gt += (ok && v[j] > t) ? 1 : 0;
+                            eq += (ok && v[j] == t) ? 1 : 0;
+                        }
+                    }
+                }
+                if (gt) atomicAdd(a.n_greater + q, (unsigned long long)gt);
+                if (eq) atomicAdd(a.n_equal + q, (unsigned long long)eq);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(acc));
+        }
+    }
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+static inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
+static inline int kpad_of(int K) { return (K + BK - 1) / BK * BK; }
+
+struct Layout {
+    size_t qs, ahi, alo, thi, tlo, bhi, blo, sidx, total;
+};
+static Layout layout(const Params& P, int64_t Q, int64_t nfilter) {
+    const int Kpad = kpad_of(P.De);
+    const size_t qk = al((size_t)Q * Kpad * sizeof(float));
+    const size_t bk = al((size_t)std::min<long long>(std::max<long long>(P.E, 1), kEntityChunk) * Kpad * sizeof(float));
+    Layout L;
+    size_t o = 0;
+    L.qs = o;   o += al((size_t)Q * P.De * sizeof(float));
+    L.ahi = o;  o += qk;
+    L.alo = o;  o += qk;
+    L.thi = o;  o += qk;
+    L.tlo = o;  o += qk;
+    L.bhi = o;  o += bk;
+    L.blo = o;  o += bk;
+    L.sidx = o; o += al((size_t)std::max<int64_t>(nfilter, 1) * sizeof(int));
+    L.total = o + 1024;  // slack to align the caller's pointer
+    return L;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// [rows, Kpad] fp32 row-major, box = box_rows x 32 floats (128 B), 128-byte swizzle, out-of-range rows read as 0
+static bool make_tmap(CUtensorMap* tm, const float* ptr, long long rows, int Kpad, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)std::max<long long>(rows, 1)};
+    const cuuint64_t strides[1] = {(cuuint64_t)Kpad * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace mma
+
+static int g_tensor_path = 1;
+void eval_set_tensor_path(int on) { g_tensor_path = on ? 1 : 0; }
+bool eval_mma_applies(const Params& P) {
+    return g_tensor_path && (P.model == KGE_DISTMULT || P.model == KGE_COMPLEX) && P.E < (1LL << 31);
+}
+size_t eval_mma_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter) { return mma::layout(P, Q, nfilter).total; }
+
+cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, const float* rel, const int64_t* queries,
+                                 int64_t Q, int64_t e_lo, int64_t e_hi, const int64_t* indptr, const int64_t* idx,
+                                 float* true_score, unsigned long long* n_greater, unsigned long long* n_equal,
+                                 int accumulate, void* ws, size_t ws_bytes, cudaStream_t st) {
+    using namespace mma;
+    cudaError_t e;
+    // the sorted copy of the filter lists lives in the workspace: its length (indptr[Q]) is read back here
+    int64_t nfilter = 0;
+    if (indptr != nullptr && idx != nullptr) {
+        if ((e = cudaMemcpyAsync(&nfilter, indptr + Q, sizeof(int64_t), cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    }
+    const Layout L = layout(P, Q, nfilter);
+    if (ws_bytes < L.total) return cudaErrorInvalidValue;
+    char* w = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+    float* Qs = (float*)(w + L.qs);
+    float *Ahi = (float*)(w + L.ahi), *Alo = (float*)(w + L.alo), *Thi = (float*)(w + L.thi), *Tlo = (float*)(w + L.tlo);
+    float *Bhi = (float*)(w + L.bhi), *Blo = (float*)(w + L.blo);
+    int* sidx = (int*)(w + L.sidx);
+    const int K = P.De, Kpad = kpad_of(K);
+    const bool head = (mode == KGE_MODE_HEAD_BATCH);
+    if (!accumulate) {
+        if ((e = cudaMemsetAsync(n_greater, 0, (size_t)Q * sizeof(unsigned long long), st)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(n_equal, 0, (size_t)Q * sizeof(unsigned long long), st)) != cudaSuccess) return e;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        if ((e = cudaFuncSetAttribute(eval_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(eval_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const int nsm = sm_count();
+    auto blocks_for = [&](long long work4) { return (unsigned)std::min<long long>((work4 + 255) / 256, 8LL * nsm); };
+
+    // 1  q = h o r / r o t (the candidate-independent factor, same kernel as the SIMT path), split into hi / lo
+    if ((e = launch_eval_stage(P, head, ent, rel, queries, Q, Qs, st)) != cudaSuccess) return e;
+    split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(Qs, K, 0, nullptr, -1, Q, K, Kpad, Ahi, Alo);
+    // 2  rows of the true entities, gathered and split
+    split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(ent, P.De, 0, queries, head ? 0 : 2, Q, K, Kpad, Thi, Tlo);
+    // 3  sorted filter lists
+    const bool filtered = indptr != nullptr && idx != nullptr && nfilter > 0;
+    if (filtered) filter_sort_kernel<<<(unsigned)((Q * 32 + 255) / 256), 256, 0, st>>>(indptr, idx, Q, sidx);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+
+    CUtensorMap tmAhi, tmAlo, tmThi, tmTlo, tmBhi, tmBlo;
+    if (!make_tmap(&tmAhi, Ahi, Q, Kpad, BM) || !make_tmap(&tmAlo, Alo, Q, Kpad, BM) || !make_tmap(&tmThi, Thi, Q, Kpad, BN) ||
+        !make_tmap(&tmTlo, Tlo, Q, Kpad, BN))
+        return cudaErrorNotSupported;
+
+    TileArgs a{};
+    a.Q = Q;
+    a.nkb = Kpad / BK;
+    a.nqt = (int)((Q + BM - 1) / BM);
+    a.true_col = head ? 0 : 2;
+    a.queries = queries;
+    a.indptr = filtered ? indptr : nullptr;
+    a.sidx = sidx;
+    a.true_score = true_score;
+    a.n_greater = n_greater;
+    a.n_equal = n_equal;
+    // 4  true scores: the diagonal of Qs x T^T
+    a.net = 1;
+    eval_mma_kernel<true><<<(unsigned)std::min(a.nqt, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmThi, tmTlo, a);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    // 5  candidates, one chunk of the split workspace at a time
+    for (long long c0 = e_lo; c0 < e_hi; c0 += kEntityChunk) {
+        const long long rows = std::min(kEntityChunk, e_hi - c0);
+        split_rows_kernel<<<blocks_for(rows * (Kpad / 4)), 256, 0, st>>>(ent, P.De, c0, nullptr, -1, rows, K, Kpad, Bhi, Blo);
+        if (!make_tmap(&tmBhi, Bhi, rows, Kpad, BN) || !make_tmap(&tmBlo, Blo, rows, Kpad, BN)) return cudaErrorNotSupported;
+        a.b_row_id0 = c0;
+        a.b_rows = rows;
+        a.net = (int)((rows + BN - 1) / BN);
+        const long long ntiles = (long long)a.nqt * a.net;
+        eval_mma_kernel<false><<<(unsigned)std::min<long long>(ntiles, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmBhi, tmBlo, a);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace kge

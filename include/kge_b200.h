@@ -177,6 +177,14 @@ KGE_API int kge_eval_rank(const kge_model_desc *desc, int mode, const float *ent
                   int64_t *n_equal, int accumulate, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * DistMult / ComplEx are dot products over entity_dim coordinates (U4, U5), so kge_eval_rank runs them as
+ * tcgen05 GEMM tiles (3xTF32 split operands fed by TMA, fp32 accumulation in TMEM, the same counting epilogue;
+ * csrc/kge_eval_mma.cu).  kge_eval_set_tensor_path(0) routes them through the fp32 CUDA-core tiles of the
+ * distance models instead (the exact-check runs of the tests compare the two); default 1.  Process-wide.
+ */
+KGE_API int kge_eval_set_tensor_path(int on);
+
+/*
  * Fused train step, tables and batch resident in HBM.  Replaces the body of KGEModel.train_step (U9) /
  * Trainer.train_step_fn (supervisor.py:15-28): both score passes, the loss, the backward and dense Adam
  * on both tables (+ the pRotatE modulus) in one call.  `mode` HEAD_BATCH or TAIL_BATCH.
