@@ -161,7 +161,7 @@ def run_reference(a):
         "e2e": {"value": base["value"], "unit": "triples*neg/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(a):
@@ -208,11 +208,21 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    dp = None
+    if world > 1:
+        # one GLOBAL step per call: positives data-parallel in the sweep, entity rows owner-parallel in the apply,
+        # NCCL all-gather of the per-positive buffers and of the updated row ranges (dist.DataParallelStep)
+        from customknowledgegraphembedding_b200 import dist as kd
+        dp = kd.DataParallelStep(model, opt)
+
     def device_steps(n, start):
         out = None
         for i in range(n):
             p, ng, s, m = devb[(start + i) % nb]
-            out = model._fused_step(opt, group, p, ng, s, m, True, w["adversarial_temperature"], False, 0.0)
+            if dp is not None:
+                out = dp.train_step(iter([(p, ng, s, m)]), targs, sync=False)
+            else:
+                out = model._fused_step(opt, group, p, ng, s, m, True, w["adversarial_temperature"], False, 0.0)
         return out
 
     def timed(fn):
@@ -246,15 +256,19 @@ def run_ours(a):
     # ---- e2e: the public API with the batch in pinned host memory ------------------------------------
     it = iter([host[(W + i) % nb] for i in range(K + 3)])
     for _ in range(3):
-        kb.KGEModel.train_step(model, opt, it, targs)
+        dp.train_step(it, targs) if dp is not None else kb.KGEModel.train_step(model, opt, it, targs)
     last_log = {}
 
     def e2e_steps():
         for _ in range(K):
-            last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
+            if dp is not None:
+                last_log.update(dp.train_step(it, targs))
+            else:
+                last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
     ms_e2e = timed(e2e_steps)
     # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
-    ev = eval_bench(model, w, dev, timed, rank)
+    ev = eval_bench(model, w, dev, timed, rank, world)
+    ev_gemm = eval_gemm_bench(dev, timed, world)
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -279,7 +293,10 @@ def run_ours(a):
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD_NAME,
-                   "parallelism": "single GPU" if world == 1 else "%d independent replicas (no exchange)" % world,
+                   "parallelism": "single GPU" if world == 1 else
+                   "dp%d: %d positives per GPU, ONE optimizer step on the global batch of %d (sweep data-parallel, "
+                   "apply owner-parallel over entity rows; NCCL all-gather of per-positive buffers and updated rows)"
+                   % (world, w["batch"], w["batch"] * world),
                    "l2": "no flush: tables + Adam state + gradients = %.2f GB per step > 126 MB L2; the entity table "
                          "itself (116 MB) is L2-resident for the gathers, as in any real run" %
                          ((w["nentity"] * 2 * w["hidden_dim"] + w["nrelation"] * w["hidden_dim"]) * 16 / 1e9),
@@ -296,22 +313,23 @@ def run_ours(a):
         "stages_ms_per_step": {k: v[0] / K for k, v in stages.items()},
         "profiled_region_ms_per_step": ms_prof / K,
         "eval": ev,
+        "eval_gemm": ev_gemm,
         "clocks": sampler.summary(),
     }
     log("timing done; running the bounded CPU baseline sample ...")
     base = cpu_baseline(steps=2, warmup=1) if not a.no_cpu_baseline else None
     line["cpu_baseline"] = ({k: base[k] for k in ("value", "unit", "cores", "kind", "sample")} if base else None)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
 
-def eval_bench(model, w, dev, timed, rank):
+def eval_bench(model, w, dev, timed, rank, world=1):
     """Filtered full-entity ranking throughput (queries/s): 1024 head-batch + 1024 tail-batch queries."""
     import numpy as np
     import torch
     import customknowledgegraphembedding_b200 as kb
-    rng = np.random.RandomState(7 + rank)
+    rng = np.random.RandomState(7)  # the same queries on every rank: candidates are sharded, not queries
     nq = 1024
     test = np.stack([rng.randint(0, w["nentity"], nq), rng.randint(0, w["nrelation"], nq),
                      rng.randint(0, w["nentity"], nq)], 1).astype(np.int64)
@@ -330,26 +348,101 @@ def eval_bench(model, w, dev, timed, rank):
         ip, ix = kb.KGEModel.build_filter_csr(maps, test, mode, w["nentity"])
         csr[mode] = (torch.from_numpy(ip).to(dev), torch.from_numpy(ix).to(dev))
 
+    if world > 1:
+        from customknowledgegraphembedding_b200 import dist as kd
+
     def device_eval():
         for mode in ("head-batch", "tail-batch"):
-            model.rank_queries(q, mode, *csr[mode])
+            if world > 1:  # each rank scores its entity row range, one all-reduce of the integer counters
+                kd.rank_queries_sharded(model, q, mode, *csr[mode])
+            else:
+                model.rank_queries(q, mode, *csr[mode])
     device_eval()
     ms = timed(device_eval)
     eargs = argparse.Namespace(nentity=w["nentity"], nrelation=w["nrelation"], countries=False)
     metrics = {}
 
     def api_eval():
-        metrics.update(kb.KGEModel.test_step(model, test_l, all_true, eargs))
+        if world > 1:
+            metrics.update(kd.test_step(model, test_l, all_true, eargs))
+        else:
+            metrics.update(kb.KGEModel.test_step(model, test_l, all_true, eargs))
     api_eval()
     ms_api = timed(api_eval)
     return {"metric": "eval_queries_per_sec", "value": 2 * nq / (ms * 1e-3), "unit": "queries/s",
             "queries": 2 * nq, "candidates_per_query": w["nentity"], "ms": ms,
+            "sharding": "none" if world == 1 else "entity rows over %d ranks, all-reduce of int64 counters" % world,
             "e2e": {"value": 2 * nq / (ms_api * 1e-3), "unit": "queries/s", "ms": ms_api,
                     "note": "KGEModel.test_step from Python triple lists: CSR filter build on host, H2D, D2H of ranks"},
             "mrr_random_init": metrics.get("MRR")}
 
 
+def eval_gemm_bench(dev, timed, world=1):
+    """BASELINE.json configs[3]: ComplEx / DistMult on FB15k sizes (14951 entities, 1345 relations), H = 1000,
+    filtered full-entity ranking as tcgen05 GEMM tiles (3xTF32).  Roofline: tensor pipe; peak = half the measured
+    dense bf16 rate (kind::tf32 runs at half the bf16 rate); achieved counts the 3 MMA passes actually issued."""
+    import numpy as np
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    E, R, H, nq = 14951, 1345, 1000, 4096
+    bf16 = None
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            bf16 = float(json.load(f).get("bf16_tflops", 0)) or None
+    peak, src = (bf16 / 2, "measured bf16_tflops / 2 (MEASURED_PEAKS.json)") if bf16 else (795.0, "fallback 1.59 PF bf16 / 2")
+    out = {}
+    if world > 1:
+        from customknowledgegraphembedding_b200 import dist as kd
+    for name, de, dr in (("ComplEx", True, True), ("DistMult", False, False)):
+        torch.manual_seed(1)
+        m = kb.KGEModel(name, E, R, H, 12.0, de, dr).to(dev)
+        rng = np.random.RandomState(11)
+        q = torch.from_numpy(np.stack([rng.randint(0, E, nq), rng.randint(0, R, nq), rng.randint(0, E, nq)], 1)).to(dev)
+        lens = rng.randint(0, 6, nq)
+        indptr = np.zeros(nq + 1, dtype=np.int64)
+        np.cumsum(lens, out=indptr[1:])
+        idx = torch.from_numpy(rng.randint(0, E, int(indptr[-1])).astype(np.int64)).to(dev)
+        indptr = torch.from_numpy(indptr).to(dev)
+
+        def run():
+            for mode in ("head-batch", "tail-batch"):
+                if world > 1:
+                    kd.rank_queries_sharded(m, q, mode, indptr, idx)
+                else:
+                    m.rank_queries(q, mode, indptr, idx)
+        run()
+        ms = timed(run)
+        flops = 2.0 * (2 * nq) * E * m.entity_dim
+        out[name] = {"value": 2 * nq / (ms * 1e-3), "unit": "queries/s", "queries": 2 * nq, "candidates_per_query": E,
+                     "ms": ms, "roofline": {"bound": "tensor", "achieved": 3 * flops / (ms * 1e-3) / 1e12, "peak": peak,
+                                            "unit": "TFLOP/s", "frac": 3 * flops / (ms * 1e-3) / 1e12 / peak,
+                                            "peak_source": src, "useful_tflops": flops / (ms * 1e-3) / 1e12,
+                                            "note": "whole call: operand split, true-score tile, sort of the filter "
+                                                    "lists and the counting tiles; 3 tf32 MMA passes per product"}}
+        del m
+    return out
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else a library prints (NCCL's version
+    banner, torchrun notices) was redirected to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # fd 1 -> stderr for the rest of the run
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
