@@ -67,6 +67,8 @@ PROTOTYPES = {
     "kge_l3_sum_cubes": (C.c_int, [_P, _I64, _P, _P, _SZ, _P]),
     "kge_adam_dense": (C.c_int, [_P, _P, _P, _P, _I64, C.POINTER(AdamOpts), C.c_float, C.c_int, _P]),
     "kge_eval_rank": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, C.c_int, _P, _SZ, _P]),
+    "kge_eval_rank_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P,
+                                      C.c_int, _P, _SZ, _P]),
     "kge_eval_set_tensor_path": (C.c_int, [C.c_int]),
     "kge_train_step": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                  C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _P, _SZ, _P]),

@@ -184,10 +184,12 @@ int kge_adam_dense(float* p, float* g, float* m, float* v, int64_t n, const kge_
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_adam_dense");
 }
 
-int kge_eval_rank(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
-                  const float* modulus, const int64_t* queries, int64_t Q, int64_t entity_lo, int64_t entity_hi,
-                  const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score, int64_t* n_greater,
-                  int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes, void* stream) {
+// shared body of kge_eval_rank / kge_eval_rank_shard.  shard_row0 < 0: `entity` addresses the full id space.
+static int eval_rank_impl(const kge_model_desc* desc, int mode, const float* entity, int64_t shard_row0,
+                          int64_t shard_rows, const float* relation, const float* modulus, const int64_t* queries,
+                          const float* query_rows, int64_t Q, int64_t entity_lo, int64_t entity_hi,
+                          const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
+                          int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes, void* stream) {
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -201,12 +203,42 @@ int kge_eval_rank(const kge_model_desc* desc, int mode, const float* entity, con
     if ((filter_indptr == nullptr) != (filter_idx == nullptr) && filter_indptr == nullptr)
         return fail(KGE_ERR_INVALID_ARGUMENT, "filter_idx without filter_indptr");
     if (P.model == KGE_PROTATE && !modulus) return fail(KGE_ERR_INVALID_ARGUMENT, "pRotatE needs modulus");
+    if (shard_row0 >= 0) {
+        if (!query_rows) return fail(KGE_ERR_INVALID_ARGUMENT, "a row-sharded table needs query_rows");
+        if (entity_lo < shard_row0 || entity_hi > shard_row0 + shard_rows)
+            return fail(KGE_ERR_INVALID_ARGUMENT, "candidate range [%lld, %lld) outside the shard [%lld, %lld)",
+                        (long long)entity_lo, (long long)entity_hi, (long long)shard_row0,
+                        (long long)(shard_row0 + shard_rows));
+        // the kernels address candidates by global id: rebase so that id e lands on shard row e - shard_row0.
+        // Only rows in [entity_lo, entity_hi) are dereferenced (every other row comes from query_rows).
+        entity = reinterpret_cast<const float*>(reinterpret_cast<uintptr_t>(entity) -
+                                                (uintptr_t)shard_row0 * (uintptr_t)P.De * sizeof(float));
+    }
     const size_t need = eval_workspace_bytes(P, Q, 0);
     if (!ws || ws_bytes < need) return fail(KGE_ERR_WORKSPACE, "eval needs %zu workspace bytes, got %zu", need, ws_bytes);
-    cudaError_t e = launch_eval_rank(P, mode, entity, relation, modulus, queries, Q, entity_lo, entity_hi,
+    cudaError_t e = launch_eval_rank(P, mode, entity, relation, modulus, queries, query_rows, Q, entity_lo, entity_hi,
                                      filter_indptr, filter_idx, true_score, n_greater, n_equal, accumulate, ws,
                                      ws_bytes, (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_eval_rank");
+}
+
+int kge_eval_rank(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
+                  const float* modulus, const int64_t* queries, int64_t Q, int64_t entity_lo, int64_t entity_hi,
+                  const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score, int64_t* n_greater,
+                  int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes, void* stream) {
+    return eval_rank_impl(desc, mode, entity, -1, 0, relation, modulus, queries, nullptr, Q, entity_lo, entity_hi,
+                          filter_indptr, filter_idx, true_score, n_greater, n_equal, accumulate, ws, ws_bytes, stream);
+}
+
+int kge_eval_rank_shard(const kge_model_desc* desc, int mode, const float* entity_shard, int64_t shard_row0,
+                        int64_t shard_rows, const float* relation, const float* modulus, const int64_t* queries,
+                        const float* query_rows, int64_t Q, int64_t entity_lo, int64_t entity_hi,
+                        const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score, int64_t* n_greater,
+                        int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes, void* stream) {
+    if (shard_row0 < 0 || shard_rows < 0) return fail(KGE_ERR_INVALID_ARGUMENT, "bad shard");
+    return eval_rank_impl(desc, mode, entity_shard, shard_row0, shard_rows, relation, modulus, queries, query_rows, Q,
+                          entity_lo, entity_hi, filter_indptr, filter_idx, true_score, n_greater, n_equal, accumulate, ws,
+                          ws_bytes, stream);
 }
 
 int kge_eval_set_tensor_path(int on) {

@@ -96,7 +96,7 @@ __device__ __forceinline__ float pair_score_seq(const float* __restrict__ qrow, 
 template <int MODEL>
 __global__ void __launch_bounds__(128)
 eval_stage_kernel(Params P, int head, const float* __restrict__ ent, const float* __restrict__ rel,
-                  const int64_t* __restrict__ queries, float* __restrict__ Qs) {
+                  const int64_t* __restrict__ queries, const float* __restrict__ qrows, float* __restrict__ Qs) {
     extern __shared__ __align__(16) float smem[];
     constexpr int planes = model_planes(MODEL);
     const int qdim = planes * P.H;
@@ -104,17 +104,23 @@ eval_stage_kernel(Params P, int head, const float* __restrict__ ent, const float
     float* aux = q + qdim;
     float* red = aux + 4;
     const long long b = blockIdx.x;
-    stage_positive<MODEL>(q, aux, red, P, ent, rel, queries[3 * b], queries[3 * b + 1], queries[3 * b + 2], head != 0);
+    // qrows [Q,2,De] (row-sharded tables): the head / tail rows of query b travel with the query
+    if (qrows != nullptr) stage_positive<MODEL>(q, aux, red, P, qrows, rel, 2 * b, queries[3 * b + 1], 2 * b + 1, head != 0);
+    else stage_positive<MODEL>(q, aux, red, P, ent, rel, queries[3 * b], queries[3 * b + 1], queries[3 * b + 2], head != 0);
     for (int k = threadIdx.x; k < qdim; k += blockDim.x) Qs[b * qdim + k] = q[k];
 }
 
 // ---- 2 norms (InterHT) -----------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-eval_inv_norm_kernel(Params P, const float* __restrict__ ent, float* __restrict__ ina, float* __restrict__ inb) {
+eval_inv_norm_kernel(Params P, const float* __restrict__ ent, long long e_lo, long long e_hi, float* __restrict__ ina,
+                     float* __restrict__ inb) {
+    // rows [e_lo, e_hi) of `ent` -> ina / inb [e - e_lo]
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (long long e = warp; e < P.E; e += nw) {
+    ina -= e_lo;
+    inb -= e_lo;
+    for (long long e = e_lo + warp; e < e_hi; e += nw) {
         const float* row = ent + e * (long long)P.De;
         float sa = 0.f, sb = 0.f;
         for (int k = lane; k < P.H; k += 32) {
@@ -135,18 +141,53 @@ eval_inv_norm_kernel(Params P, const float* __restrict__ ent, float* __restrict_
 }
 
 // ---- 3 true ----------------------------------------------------------------------------------
+// row of the true entity of query q: from the table, or from qrows [Q,2,De] when the table is row-sharded
+template <bool HEAD>
+__device__ __forceinline__ const float* true_row(const Params& P, const float* __restrict__ ent,
+                                                 const float* __restrict__ qrows, const int64_t* __restrict__ queries,
+                                                 long long q) {
+    if (qrows != nullptr) return qrows + (2 * q + (HEAD ? 0 : 1)) * (long long)P.De;
+    return ent + (HEAD ? queries[3 * q] : queries[3 * q + 2]) * (long long)P.De;
+}
+
+// InterHT: 1/|a|, 1/|b| of every query's true entity (one warp per query; same arithmetic as eval_inv_norm_kernel)
+template <bool HEAD>
+__global__ void __launch_bounds__(256)
+eval_true_norm_kernel(Params P, const float* __restrict__ ent, const float* __restrict__ qrows,
+                      const int64_t* __restrict__ queries, long long Q, float* __restrict__ tna, float* __restrict__ tnb) {
+    const int lane = threadIdx.x & 31;
+    const long long q = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (q >= Q) return;
+    const float* row = true_row<HEAD>(P, ent, qrows, queries, q);
+    float sa = 0.f, sb = 0.f;
+    for (int k = lane; k < P.H; k += 32) {
+        const float a = __ldg(row + k), b = __ldg(row + P.H + k);
+        sa = fmaf(a, a, sa);
+        sb = fmaf(b, b, sb);
+    }
+    float na = sqrtf(warp_sum(sa)), nb = sqrtf(warp_sum(sb));
+    if (P.interht_eps > 0.f) {
+        na = fmaxf(na, P.interht_eps);
+        nb = fmaxf(nb, P.interht_eps);
+    }
+    if (lane == 0) {
+        tna[q] = 1.0f / na;
+        tnb[q] = 1.0f / nb;
+    }
+}
+
 template <int MODEL, bool HEAD>
 __global__ void __launch_bounds__(128)
 eval_true_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
-                 const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
-                 const int64_t* __restrict__ queries, long long Q, float* __restrict__ true_score) {
+                 const float* __restrict__ qrows, const float* __restrict__ Qs, const float* __restrict__ tna,
+                 const float* __restrict__ tnb, const int64_t* __restrict__ queries, long long Q,
+                 float* __restrict__ true_score) {
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= Q) return;
     if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
-    const long long e = HEAD ? queries[3 * q] : queries[3 * q + 2];
     const int qdim = model_planes(MODEL) * P.H;
-    const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
-    true_score[q] = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b);
+    const float a = (MODEL == KGE_INTERHT) ? tna[q] : 0.f, b = (MODEL == KGE_INTERHT) ? tnb[q] : 0.f;
+    true_score[q] = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, true_row<HEAD>(P, ent, qrows, queries, q), P.H, c, a, b);
 }
 
 // ---- 5 filter --------------------------------------------------------------------------------
@@ -360,23 +401,27 @@ static inline size_t ev_align(size_t x) { return (x + 255) & ~(size_t)255; }
 size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter) {
     if (eval_mma_applies(P)) return eval_mma_workspace_bytes(P, Q, nfilter);
     size_t total = ev_align((size_t)Q * model_planes(P.model) * P.H * sizeof(float));
-    if (P.model == KGE_INTERHT) total += 2 * ev_align((size_t)P.E * sizeof(float));
+    if (P.model == KGE_INTERHT) total += 2 * ev_align((size_t)P.E * sizeof(float)) + 2 * ev_align((size_t)Q * sizeof(float));
     return total + 256;
 }
 
 template <int MODEL, bool HEAD>
 static cudaError_t launch_eval_model(const Params& P, const float* ent, const float* rel, const float* modulus,
-                                     const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                                     const int64_t* queries, const float* qrows, int64_t Q, int64_t e_lo, int64_t e_hi,
                                      const int64_t* indptr, const int64_t* idx, float* true_score,
                                      unsigned long long* n_greater, unsigned long long* n_equal, int accumulate,
                                      void* ws, cudaStream_t st) {
     const int qdim = model_planes(MODEL) * P.H;
     float* Qs = (float*)ws;
-    float* ina = nullptr;
-    float* inb = nullptr;
+    float *ina = nullptr, *inb = nullptr, *tna = nullptr, *tnb = nullptr;
     if (MODEL == KGE_INTERHT) {
-        ina = (float*)((char*)ws + ev_align((size_t)Q * qdim * sizeof(float)));
-        inb = (float*)((char*)ina + ev_align((size_t)P.E * sizeof(float)));
+        // candidate norms for rows [e_lo, e_hi) only, addressed by global id through an offset base
+        float* na = (float*)((char*)ws + ev_align((size_t)Q * qdim * sizeof(float)));
+        float* nb = (float*)((char*)na + ev_align((size_t)P.E * sizeof(float)));
+        tna = (float*)((char*)nb + ev_align((size_t)P.E * sizeof(float)));
+        tnb = (float*)((char*)tna + ev_align((size_t)Q * sizeof(float)));
+        ina = na - e_lo;
+        inb = nb - e_lo;
     }
     EvalConsts c{P.gamma, P.inv_phase_div, 0.f};
     cudaError_t e;
@@ -387,13 +432,16 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
     const size_t smem_stage = (size_t)(qdim + 4 + 32) * sizeof(float);
     if (smem_stage > 48 * 1024)
         cudaFuncSetAttribute(eval_stage_kernel<MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_stage);
-    eval_stage_kernel<MODEL><<<(unsigned)Q, 128, smem_stage, st>>>(P, HEAD ? 1 : 0, ent, rel, queries, Qs);
+    eval_stage_kernel<MODEL><<<(unsigned)Q, 128, smem_stage, st>>>(P, HEAD ? 1 : 0, ent, rel, queries, qrows, Qs);
     if (MODEL == KGE_INTERHT) {
-        const int blocks = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
-        eval_inv_norm_kernel<<<blocks, 256, 0, st>>>(P, ent, ina, inb);
+        if (e_hi > e_lo) {
+            const int blocks = (int)std::min<long long>((e_hi - e_lo + 7) / 8, 16LL * sm_count());
+            eval_inv_norm_kernel<<<blocks, 256, 0, st>>>(P, ent, e_lo, e_hi, ina + e_lo, inb + e_lo);
+        }
+        eval_true_norm_kernel<HEAD><<<(unsigned)((Q * 32 + 255) / 256), 256, 0, st>>>(P, ent, qrows, queries, Q, tna, tnb);
     }
-    eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + 127) / 128), 128, 0, st>>>(P, c, modulus, ent, Qs, ina, inb, queries,
-                                                                             Q, true_score);
+    eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + 127) / 128), 128, 0, st>>>(P, c, modulus, ent, qrows, Qs, tna, tnb,
+                                                                             queries, Q, true_score);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (e_hi > e_lo) {
         constexpr size_t smem = eval_tile_smem<MODEL>();
@@ -413,13 +461,13 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
 }
 
 cudaError_t launch_eval_stage(const Params& P, bool head, const float* ent, const float* rel, const int64_t* queries,
-                              int64_t Q, float* Qs, cudaStream_t st) {
+                              const float* qrows, int64_t Q, float* Qs, cudaStream_t st) {
     const size_t smem = (size_t)(model_planes(P.model) * P.H + 4 + 32) * sizeof(float);
 #define KGE_CASE(M)                                                                                                  \
     case M:                                                                                                          \
         if (smem > 48 * 1024)                                                                                        \
             cudaFuncSetAttribute(eval_stage_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);      \
-        eval_stage_kernel<M><<<(unsigned)Q, 128, smem, st>>>(P, head ? 1 : 0, ent, rel, queries, Qs);               \
+        eval_stage_kernel<M><<<(unsigned)Q, 128, smem, st>>>(P, head ? 1 : 0, ent, rel, queries, qrows, Qs);        \
         break
     switch (P.model) {
         KGE_CASE(KGE_TRANSE);
@@ -435,22 +483,22 @@ cudaError_t launch_eval_stage(const Params& P, bool head, const float* ent, cons
 }
 
 cudaError_t launch_eval_rank(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
-                             const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                             const int64_t* queries, const float* qrows, int64_t Q, int64_t e_lo, int64_t e_hi,
                              const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
                              int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes,
                              cudaStream_t st) {
     auto* ng = reinterpret_cast<unsigned long long*>(n_greater);
     auto* ne = reinterpret_cast<unsigned long long*>(n_equal);
     if (eval_mma_applies(P))
-        return launch_eval_rank_mma(P, mode, ent, rel, queries, Q, e_lo, e_hi, filter_indptr, filter_idx, true_score, ng,
+        return launch_eval_rank_mma(P, mode, ent, rel, queries, qrows, Q, e_lo, e_hi, filter_indptr, filter_idx, true_score, ng,
                                     ne, accumulate, ws, ws_bytes, st);
     if (ws_bytes < eval_workspace_bytes(P, Q, 0)) return cudaErrorInvalidValue;
     const bool head = (mode == KGE_MODE_HEAD_BATCH);
 #define KGE_CASE(M)                                                                                                  \
     case M:                                                                                                          \
-        return head ? launch_eval_model<M, true>(P, ent, rel, modulus, queries, Q, e_lo, e_hi, filter_indptr,        \
+        return head ? launch_eval_model<M, true>(P, ent, rel, modulus, queries, qrows, Q, e_lo, e_hi, filter_indptr, \
                                                  filter_idx, true_score, ng, ne, accumulate, ws, st)                 \
-                    : launch_eval_model<M, false>(P, ent, rel, modulus, queries, Q, e_lo, e_hi, filter_indptr,       \
+                    : launch_eval_model<M, false>(P, ent, rel, modulus, queries, qrows, Q, e_lo, e_hi, filter_indptr,\
                                                   filter_idx, true_score, ng, ne, accumulate, ws, st)
     switch (P.model) {
         KGE_CASE(KGE_TRANSE);

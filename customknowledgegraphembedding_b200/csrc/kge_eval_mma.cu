@@ -151,17 +151,18 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
     lo = tf32_rne(x - hi);  // x - hi is exact in fp32
 }
 
-// rows of `src` (pitch floats apart; row = gather ? row named by the query : row0 + r) -> hi / lo [rows, Kpad]
+// rows of `src` (pitch floats apart; row = gather ? row named by the query : row0 + r * row_stride) -> hi / lo [rows, Kpad]
 __global__ void __launch_bounds__(256)
-split_rows_kernel(const float* __restrict__ src, long long pitch, long long row0, const int64_t* __restrict__ queries,
-                  int gather_col, long long rows, int K, int Kpad, float* __restrict__ hi, float* __restrict__ lo) {
+split_rows_kernel(const float* __restrict__ src, long long pitch, long long row0, int row_stride,
+                  const int64_t* __restrict__ queries, int gather_col, long long rows, int K, int Kpad,
+                  float* __restrict__ hi, float* __restrict__ lo) {
     const int k4n = Kpad >> 2;
     const long long total = rows * k4n;
     const bool vec = (K % 4 == 0) && (pitch % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long r = i / k4n;
         const int k = (int)(i - r * k4n) * 4;
-        const long long srow = (gather_col >= 0) ? queries[3 * r + gather_col] : row0 + r;
+        const long long srow = (gather_col >= 0) ? queries[3 * r + gather_col] : row0 + r * row_stride;
         const float* p = src + srow * pitch + k;
         float x[4];
         if (vec && k + 3 < K) {
@@ -462,7 +463,7 @@ bool eval_mma_applies(const Params& P) {
 size_t eval_mma_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter) { return mma::layout(P, Q, nfilter).total; }
 
 cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, const float* rel, const int64_t* queries,
-                                 int64_t Q, int64_t e_lo, int64_t e_hi, const int64_t* indptr, const int64_t* idx,
+                                 const float* qrows, int64_t Q, int64_t e_lo, int64_t e_hi, const int64_t* indptr, const int64_t* idx,
                                  float* true_score, unsigned long long* n_greater, unsigned long long* n_equal,
                                  int accumulate, void* ws, size_t ws_bytes, cudaStream_t st) {
     using namespace mma;
@@ -496,10 +497,13 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
     auto blocks_for = [&](long long work4) { return (unsigned)std::min<long long>((work4 + 255) / 256, 8LL * nsm); };
 
     // 1  q = h o r / r o t (the candidate-independent factor, same kernel as the SIMT path), split into hi / lo
-    if ((e = launch_eval_stage(P, head, ent, rel, queries, Q, Qs, st)) != cudaSuccess) return e;
-    split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(Qs, K, 0, nullptr, -1, Q, K, Kpad, Ahi, Alo);
-    // 2  rows of the true entities, gathered and split
-    split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(ent, P.De, 0, queries, head ? 0 : 2, Q, K, Kpad, Thi, Tlo);
+    if ((e = launch_eval_stage(P, head, ent, rel, queries, qrows, Q, Qs, st)) != cudaSuccess) return e;
+    split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(Qs, K, 0, 1, nullptr, -1, Q, K, Kpad, Ahi, Alo);
+    // 2  rows of the true entities, gathered (from the table, or from qrows [Q,2,De] when it is row-sharded) and split
+    if (qrows != nullptr)
+        split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(qrows, P.De, head ? 0 : 1, 2, nullptr, -1, Q, K, Kpad, Thi, Tlo);
+    else
+        split_rows_kernel<<<blocks_for(Q * (Kpad / 4)), 256, 0, st>>>(ent, P.De, 0, 1, queries, head ? 0 : 2, Q, K, Kpad, Thi, Tlo);
     // 3  sorted filter lists
     const bool filtered = indptr != nullptr && idx != nullptr && nfilter > 0;
     if (filtered) filter_sort_kernel<<<(unsigned)((Q * 32 + 255) / 256), 256, 0, st>>>(indptr, idx, Q, sidx);
@@ -528,7 +532,7 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
     // 5  candidates, one chunk of the split workspace at a time
     for (long long c0 = e_lo; c0 < e_hi; c0 += kEntityChunk) {
         const long long rows = std::min(kEntityChunk, e_hi - c0);
-        split_rows_kernel<<<blocks_for(rows * (Kpad / 4)), 256, 0, st>>>(ent, P.De, c0, nullptr, -1, rows, K, Kpad, Bhi, Blo);
+        split_rows_kernel<<<blocks_for(rows * (Kpad / 4)), 256, 0, st>>>(ent, P.De, c0, 1, nullptr, -1, rows, K, Kpad, Bhi, Blo);
         if (!make_tmap(&tmBhi, Bhi, rows, Kpad, BN) || !make_tmap(&tmBlo, Blo, rows, Kpad, BN)) return cudaErrorNotSupported;
         a.b_row_id0 = c0;
         a.b_rows = rows;

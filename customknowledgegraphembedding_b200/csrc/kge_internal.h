@@ -62,19 +62,19 @@ cudaError_t launch_adam(float* p, float* g, float* m, float* v, int64_t n, const
 // K5
 size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter);
 cudaError_t launch_eval_rank(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
-                             const int64_t* queries, int64_t Q, int64_t e_lo, int64_t e_hi,
+                             const int64_t* queries, const float* query_rows, int64_t Q, int64_t e_lo, int64_t e_hi,
                              const int64_t* filter_indptr, const int64_t* filter_idx, float* true_score,
                              int64_t* n_greater, int64_t* n_equal, int accumulate, void* ws, size_t ws_bytes,
                              cudaStream_t st);
 
 // K5-T (kge_eval_mma.cu): tcgen05 tiles for DistMult / ComplEx
 cudaError_t launch_eval_stage(const Params& P, bool head, const float* ent, const float* rel, const int64_t* queries,
-                              int64_t Q, float* Qs, cudaStream_t st);
+                              const float* query_rows, int64_t Q, float* Qs, cudaStream_t st);
 void eval_set_tensor_path(int on);
 bool eval_mma_applies(const Params& P);
 size_t eval_mma_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter);
 cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, const float* rel, const int64_t* queries,
-                                 int64_t Q, int64_t e_lo, int64_t e_hi, const int64_t* indptr, const int64_t* idx,
+                                 const float* query_rows, int64_t Q, int64_t e_lo, int64_t e_hi, const int64_t* indptr, const int64_t* idx,
                                  float* true_score, unsigned long long* n_greater, unsigned long long* n_equal,
                                  int accumulate, void* ws, size_t ws_bytes, cudaStream_t st);
 

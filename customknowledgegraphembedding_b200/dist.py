@@ -207,3 +207,110 @@ class DataParallelStep:
                 if hi > lo:
                     src = dist.get_global_rank(self.group, r) if self.group is not None else r
                     dist.broadcast(ent[lo:hi], src=src, group=self.group)
+
+
+# --------------------------------------------------------------------------------------------------
+# row-sharded entity table (BASELINE configs[4]: 10M entities x 2000 floats = 80 GB)
+# --------------------------------------------------------------------------------------------------
+from .model import KGEModel  # noqa: E402  (after the replicated-table helpers on purpose)
+
+
+class RowShardedKGEModel(KGEModel):
+    """``KGEModel`` whose ``entity_embedding`` holds only the rows ``[lo, hi)`` this rank owns.
+
+    ``nentity`` stays the GLOBAL entity count (ids in triples are global); the relation table is replicated.
+    ``rank_queries`` / ``test_step`` give the same integers as the unsharded model: the rows the queries name
+    are exchanged (owners fill ``[Q,2,De]``, one all-reduce over zeros elsewhere -- exact), every rank counts
+    ``score > true`` over its own rows with ``kge_eval_rank_shard`` and the counters are summed.
+    """
+
+    INIT_BLOCK = 250_000  # rows per initialisation stream
+
+    def __init__(self, model_name, nentity, nrelation, hidden_dim, gamma, double_entity_embedding=False,
+                 double_relation_embedding=False, triple_relation_embedding=False, group=None, device=None, seed=0,
+                 rank_world=None):
+        # rank_world=(r, w): shard geometry without a process group (one-GPU emulation in the tests)
+        rank, world = rank_world if rank_world is not None else _world(group)
+        lo, hi = shard_range(nentity, rank, world)
+        # build the small tensors through the parent with a 1-row placeholder table, then install the shard
+        super().__init__(model_name, 1, nrelation, hidden_dim, gamma, double_entity_embedding,
+                         double_relation_embedding, triple_relation_embedding)
+        self.nentity = nentity
+        self.group, self.rank, self.world, self.lo, self.hi = group, rank, world, lo, hi
+        dev = torch.device(device) if device is not None else torch.device("cpu")
+        # shard-local generation (SURVEY 8(d)) that does not depend on the sharding: the table is defined in blocks
+        # of INIT_BLOCK rows, block i drawn from its own stream; a rank draws the blocks that overlap its rows.
+        r = self.embedding_range.item()
+        shard = torch.empty((hi - lo, self.entity_dim), dtype=torch.float32, device=dev)
+        blk = self.INIT_BLOCK
+        for b0 in range((lo // blk) * blk, hi, blk):
+            b1 = min(b0 + blk, nentity)
+            g = torch.Generator(device=dev).manual_seed(int(seed) * 1000003 + b0 // blk)
+            rows = torch.empty((b1 - b0, self.entity_dim), dtype=torch.float32, device=dev).uniform_(-r, r, generator=g)
+            s0, s1 = max(b0, lo), min(b1, hi)
+            shard[s0 - lo:s1 - lo] = rows[s0 - b0:s1 - b0]
+            del rows
+        self.entity_embedding = torch.nn.Parameter(shard)
+        g2 = torch.Generator().manual_seed(int(seed))  # the replicated relation table: same on every rank
+        rel = torch.empty((nrelation, self.relation_dim), dtype=torch.float32).uniform_(-r, r, generator=g2)
+        self.relation_embedding = torch.nn.Parameter(rel)
+        if device is not None:
+            self.to(dev)
+
+    @classmethod
+    def from_full(cls, model: KGEModel, group=None, rank_world=None):
+        """Shard an existing (replicated) model: this rank keeps rows [lo, hi).  For tests and checkpoints."""
+        de = model.entity_dim == 2 * model.hidden_dim
+        tr = model.relation_dim == 3 * model.hidden_dim
+        dr = model.relation_dim == 2 * model.hidden_dim
+        dev = model.entity_embedding.device
+        m = cls(model.model_name, model.nentity, model.nrelation, model.hidden_dim, model.gamma.item(), de, dr, tr,
+                group=group, device=dev, rank_world=rank_world)
+        with torch.no_grad():
+            m.entity_embedding.copy_(model.entity_embedding[m.lo:m.hi])
+            m.relation_embedding.copy_(model.relation_embedding)
+            if model._modulus() is not None:
+                m.modulus.copy_(model.modulus)
+        m.interht_eps = model.interht_eps
+        return m
+
+    def forward(self, sample, mode="single"):
+        raise NotImplementedError("RowShardedKGEModel: forward on a row-sharded table goes through "
+                                  "RowShardedStep / rank_queries (the rows have to be exchanged first)")
+
+    # ---- row exchange --------------------------------------------------------------------------------
+    def gather_rows(self, ids: torch.Tensor) -> torch.Tensor:
+        """Rows of the GLOBAL table for ``ids`` (same tensor on every rank) -> [len(ids), De] on every rank."""
+        ent = self.entity_embedding.detach()
+        ids = ids.to(ent.device)
+        mine = (ids >= self.lo) & (ids < self.hi)
+        out = torch.zeros((ids.numel(), self.entity_dim), dtype=torch.float32, device=ent.device)
+        sel = torch.nonzero(mine).view(-1)
+        if sel.numel():
+            out[sel] = ent[ids[sel] - self.lo]
+        if self.world > 1 and dist.is_initialized():
+            dist.all_reduce(out, op=dist.ReduceOp.SUM, group=self.group)  # exactly one rank holds each row: x + 0
+        return out
+
+    # ---- eval ------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def rank_queries(self, queries, mode, filter_indptr=None, filter_idx=None, entity_lo=None, entity_hi=None,
+                     local_fn=None):
+        dev = self.entity_embedding.device
+        queries = queries.to(dev).contiguous()
+        Q = queries.shape[0]
+        qrows = self.gather_rows(queries[:, [0, 2]].reshape(-1)).view(Q, 2, self.entity_dim)
+        to = lambda t: None if t is None else t.to(dev, non_blocking=True)
+        fn = local_fn if local_fn is not None else self._rank_local
+        true_score, n_greater, n_equal = fn(queries, qrows, mode, to(filter_indptr), to(filter_idx))
+        if self.world > 1 and dist.is_initialized():
+            counts = torch.stack([n_greater, n_equal])
+            dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=self.group)
+            n_greater, n_equal = counts[0], counts[1]
+        return true_score, n_greater, n_equal
+
+    def _rank_local(self, queries, qrows, mode, indptr, idx):
+        mod = self._modulus()
+        return ops.eval_rank_shard(self._desc(), mode, self.entity_embedding.detach(), self.lo,
+                                   self.relation_embedding.detach(), None if mod is None else mod.detach(), queries,
+                                   qrows, self.lo, self.hi, indptr, idx)

@@ -176,3 +176,45 @@ def eval_rank(desc: ModelDesc, mode: str, entity, relation, modulus, queries, en
                                      _ptr(n_greater), _ptr(n_equal), int(accumulate), _ptr(ws), ws_bytes, _stream()),
                    "kge_eval_rank")
     return true_score, n_greater, n_equal
+
+
+def eval_rank_shard(desc: ModelDesc, mode: str, entity_shard, shard_row0: int, relation, modulus, queries, query_rows,
+                    entity_lo: int, entity_hi: int, filter_indptr=None, filter_idx=None, out=None,
+                    accumulate: bool = False):
+    """kge_eval_rank_shard: `entity_shard` holds rows [shard_row0, shard_row0 + len) of the global table,
+    `query_rows` [Q,2,De] the (head, tail) rows of the queries.  -> (true_score, n_greater, n_equal) of the shard."""
+    lib = _lib.load()
+    m = mode_id(mode)
+    entity_shard = _need_cuda("entity_shard", entity_shard, torch.float32)
+    relation = _need_cuda("relation_embedding", relation, torch.float32)
+    queries = _need_cuda("queries", queries, torch.int64)
+    query_rows = _need_cuda("query_rows", query_rows, torch.float32)
+    Q = queries.shape[0]
+    if query_rows.numel() != Q * 2 * desc.entity_dim:
+        raise ValueError("query_rows must be [Q,2,entity_dim]")
+    dev = entity_shard.device
+    if filter_indptr is not None:
+        filter_indptr = _need_cuda("filter_indptr", filter_indptr, torch.int64)
+        filter_idx = _need_cuda("filter_idx", filter_idx, torch.int64)
+        nflt = filter_idx.numel()
+    else:
+        nflt = 0
+    if out is None:
+        true_score = torch.empty(Q, dtype=torch.float32, device=dev)
+        n_greater = torch.zeros(Q, dtype=torch.int64, device=dev)
+        n_equal = torch.zeros(Q, dtype=torch.int64, device=dev)
+    else:
+        true_score, n_greater, n_equal = out
+    if Q == 0:
+        return true_score, n_greater, n_equal
+    ws_bytes = workspace_bytes(_lib.WS_EVAL, desc, Q, nflt)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    # an empty shard still passes a valid (never dereferenced) pointer
+    ent_ptr = _ptr(entity_shard) if entity_shard.numel() else _ptr(relation)
+    with torch.cuda.device(dev):
+        _lib.check(lib.kge_eval_rank_shard(C.byref(desc), m, ent_ptr, int(shard_row0), int(entity_shard.shape[0]),
+                                           _ptr(relation), _ptr(modulus), _ptr(queries), _ptr(query_rows), Q,
+                                           int(entity_lo), int(entity_hi), _ptr(filter_indptr), _ptr(filter_idx),
+                                           _ptr(true_score), _ptr(n_greater), _ptr(n_equal), int(accumulate), _ptr(ws),
+                                           ws_bytes, _stream()), "kge_eval_rank_shard")
+    return true_score, n_greater, n_equal

@@ -177,6 +177,23 @@ KGE_API int kge_eval_rank(const kge_model_desc *desc, int mode, const float *ent
                   int64_t *n_equal, int accumulate, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * K5 over a ROW-SHARDED entity table (one process per GPU): `entity_shard` holds only the rows
+ * [shard_row0, shard_row0 + shard_rows) of the table (desc->nentity stays the global E), candidates
+ * [entity_lo, entity_hi) must lie inside the shard, and the rows the queries name travel with them:
+ * query_rows [Q,2,entity_dim] = (head row, tail row) of every query, assembled by the caller (owners fill their
+ * rows, one all-reduce(sum) over zeros elsewhere -- exact).  Every rank computes the same true_score from the same
+ * query_rows with the same kernel, so the integer counters of the shards add up to the single-GPU result.
+ * Replaces the per-GPU body of test_step under the sharding north_star names; reference mechanism: replicas only
+ * (tensorflow_codes/run.py:8-17).
+ */
+KGE_API int kge_eval_rank_shard(const kge_model_desc *desc, int mode, const float *entity_shard, int64_t shard_row0,
+                                int64_t shard_rows, const float *relation, const float *modulus,
+                                const int64_t *queries, const float *query_rows, int64_t Q, int64_t entity_lo,
+                                int64_t entity_hi, const int64_t *filter_indptr, const int64_t *filter_idx,
+                                float *true_score, int64_t *n_greater, int64_t *n_equal, int accumulate, void *ws,
+                                size_t ws_bytes, void *stream);
+
+/*
  * DistMult / ComplEx are dot products over entity_dim coordinates (U4, U5), so kge_eval_rank runs them as
  * tcgen05 GEMM tiles (3xTF32 split operands fed by TMA, fp32 accumulation in TMEM, the same counting epilogue;
  * csrc/kge_eval_mma.cu).  kge_eval_set_tensor_path(0) routes them through the fp32 CUDA-core tiles of the

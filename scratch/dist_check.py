@@ -10,7 +10,7 @@ rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), 1e-3
 torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
 dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
 E, R, H, B, N = 2000, 11, 256, 64, 128
-for name in ("RotatE", "TransE", "InterHT"):
+for name in ("RotatE", "TransE", "InterHT", "ComplEx"):
     om = ko.make_model(name, E, R, H, 12.0, seed=0)
     de, dr, tr = ko.model_flags(name)
     def mk():
@@ -37,5 +37,11 @@ for name in ("RotatE", "TransE", "InterHT"):
     assert np.array_equal(r1, r2) and m1 == m2
     if rank == 0:
         print(name, "sharded eval == single eval, MRR", m2["MRR"], flush=True)
+    # row-sharded TABLE: this rank keeps only its rows; query rows are exchanged, counters all-reduced
+    sm = kd.RowShardedKGEModel.from_full(a)
+    m3 = kb.KGEModel.test_step(sm, true[:100], true, args); r3 = sm.last_eval["ranks"]
+    assert np.array_equal(r1, r3) and m1 == m3, (r1[:10], r3[:10])
+    if rank == 0:
+        print(name, "row-sharded table eval == single eval (rows/rank %d)" % sm.entity_embedding.shape[0], flush=True)
 dist.barrier(); dist.destroy_process_group()
 if rank == 0: print("DIST CHECK OK")

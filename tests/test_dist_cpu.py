@@ -25,6 +25,20 @@ def test_shard_range_covers_everything():
             assert prev == n
 
 
+def test_row_sharded_init_does_not_depend_on_the_sharding():
+    """Block-wise streams: the concatenation of the shards is the same table for every world size."""
+    from customknowledgegraphembedding_b200 import dist as kd
+
+    class M(kd.RowShardedKGEModel):
+        INIT_BLOCK = 7
+    full = M("RotatE", 50, 3, 4, 9.0, True, False, rank_world=(0, 1), seed=2)
+    for world in (2, 3, 8):
+        parts = [M("RotatE", 50, 3, 4, 9.0, True, False, rank_world=(r, world), seed=2) for r in range(world)]
+        assert torch.equal(torch.cat([p.entity_embedding for p in parts]), full.entity_embedding)
+        assert all(torch.equal(p.relation_embedding, full.relation_embedding) for p in parts)
+        assert all(p.nentity == 50 for p in parts)
+
+
 def _oracle_counts(om, queries, mode, indptr, idx, entity_lo, entity_hi):
     """CPU stand-in for kge_eval_rank over [entity_lo, entity_hi): same contract as KGEModel.rank_queries."""
     Q, E = queries.shape[0], om.nentity
@@ -69,6 +83,20 @@ def _worker(rank, world, port, tmp):
     want, ranks = ko.test_step(om, test, true, args, return_ranks=True)
     assert np.array_equal(gm.last_eval["ranks"], ranks), (gm.last_eval["ranks"], ranks)
     assert got == want
+
+    # ---------------- eval over a ROW-SHARDED table: row exchange + sharded counts == unsharded ----------------
+    sm = kd.RowShardedKGEModel.from_full(gm)
+    assert (sm.lo, sm.hi) == kd.shard_range(E, rank, world) and sm.entity_embedding.shape[0] == sm.hi - sm.lo
+    ids = torch.tensor([0, E - 1, 30, 31, 5, 5])
+    assert torch.equal(sm.gather_rows(ids), om.entity_embedding.detach()[ids])   # owners + zeros, summed: exact
+
+    def shard_local(q, qrows, mode, ip, ix):
+        want_rows = om.entity_embedding.detach()[q[:, [0, 2]].reshape(-1)].view(q.shape[0], 2, -1)
+        assert torch.equal(qrows, want_rows)
+        return _oracle_counts(om, q, mode, ip, ix, sm.lo, sm.hi)
+    got_s = kb.KGEModel.test_step(sm, test, true, args,
+                                  rank_fn=lambda q, mode, ip, ix: sm.rank_queries(q, mode, ip, ix, local_fn=shard_local))
+    assert np.array_equal(sm.last_eval["ranks"], ranks) and got_s == want
 
     # ---------------- train: sweep local / gather / apply owned rows / broadcast ----------------
     class Step(kd.DataParallelStep):
