@@ -79,6 +79,9 @@ PROTOTYPES = {
     "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                   C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P, _P,
                                   _P, _SZ, _P]),
+    "kge_train_apply_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
+                                        C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P,
+                                        _P, _P, _SZ, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
     "kge_profile_enable": (C.c_int, [C.c_int]),
     "kge_profile_num_stages": (C.c_int, []),

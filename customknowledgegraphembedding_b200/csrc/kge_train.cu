@@ -293,6 +293,25 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_apply(copy loss)");
 }
 
+int kge_train_apply_shard(const kge_model_desc* desc, int mode, float* entity_shard, int64_t shard_row0,
+                          int64_t shard_rows, float* relation, float* modulus, float* adam_m_shard, float* adam_v_shard,
+                          float* adam_m_relation, float* adam_v_relation, float* adam_m_modulus, float* adam_v_modulus,
+                          const int64_t* positive_all, const int64_t* negative_all, int64_t B_all, int64_t N,
+                          const kge_loss_opts* loss_opts, const kge_adam_opts* adam_opts,
+                          const kge_step_buffers* gathered, int64_t entity_lo, int64_t entity_hi, float* loss3,
+                          float* reg1, void* ws, size_t ws_bytes, void* stream) {
+    if (!desc || !entity_shard || !adam_m_shard || !adam_v_shard) return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if (shard_row0 < 0 || shard_rows < 0 || entity_lo < shard_row0 || entity_hi > shard_row0 + shard_rows)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "row range [%lld, %lld) outside the shard [%lld, %lld)", (long long)entity_lo,
+                    (long long)entity_hi, (long long)shard_row0, (long long)(shard_row0 + shard_rows));
+    // rows are addressed by global id and only [entity_lo, entity_hi) is dereferenced: rebase the three shards
+    const uintptr_t off = (uintptr_t)shard_row0 * (uintptr_t)desc->entity_dim * sizeof(float);
+    auto rebase = [off](float* p) { return reinterpret_cast<float*>(reinterpret_cast<uintptr_t>(p) - off); };
+    return kge_train_apply(desc, mode, rebase(entity_shard), relation, modulus, rebase(adam_m_shard), rebase(adam_v_shard),
+                           adam_m_relation, adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all,
+                           B_all, N, loss_opts, adam_opts, gathered, entity_lo, entity_hi, loss3, reg1, ws, ws_bytes, stream);
+}
+
 int kge_train_step_host(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
                         float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
                         float* adam_m_modulus, float* adam_v_modulus, const int64_t* host_positive, const int64_t* host_negative,

@@ -314,3 +314,97 @@ class RowShardedKGEModel(KGEModel):
         return ops.eval_rank_shard(self._desc(), mode, self.entity_embedding.detach(), self.lo,
                                    self.relation_embedding.detach(), None if mod is None else mod.detach(), queries,
                                    qrows, self.lo, self.hi, indptr, idx)
+
+
+class RowShardedStep(DataParallelStep):
+    """Train step over a ``RowShardedKGEModel``: no rank holds the full entity table or its Adam state.
+
+    Per step (north_star "all-gather of the touched rows ... sparse gradients to the owners"):
+
+    1. the unique entity ids of the LOCAL batch are requested from their owners (all-to-all of id lists, all-to-all of
+       rows) into a compact table ``[U, De]``; the batch is remapped to compact ids;
+    2. ``kge_train_sweep`` on the compact table: scores, loss terms, dL/dq, compact per-positive gradient rows;
+    3. all-gather of the per-positive buffers and of the batches (global ids), exactly as ``DataParallelStep``;
+    4. ``kge_train_apply_shard`` on the rows this rank owns: gradient gather in fixed order + dense Adam in place.
+
+    The update is that of ONE step on the global batch, bit-identical to ``DataParallelStep`` on replicated tables
+    (the sweep reads the same row values; the apply is the same kernel on a rebased pointer).
+    """
+
+    def __init__(self, model, optimizer, group=None):
+        if not isinstance(model, RowShardedKGEModel):
+            raise TypeError("RowShardedStep needs a RowShardedKGEModel")
+        super().__init__(model, optimizer, group)
+        self.rank, self.world = model.rank, model.world
+        self.lo, self.hi = model.lo, model.hi
+        self.last_exchange = {}
+
+    # ---- 1: rows of the local batch from their owners ------------------------------------------------------
+    def fetch_rows(self, ids_sorted: torch.Tensor) -> torch.Tensor:
+        """``ids_sorted``: sorted unique global ids this rank needs -> their rows ``[U, De]`` (same order)."""
+        m = self.model
+        ent = m.entity_embedding.detach()
+        dev = ids_sorted.device
+        if self.world == 1 or not dist.is_initialized():
+            return ent[ids_sorted - self.lo]
+        rows_per = (m.nentity + self.world - 1) // self.world
+        bounds = torch.arange(1, self.world, device=dev, dtype=torch.int64) * rows_per
+        cut = torch.searchsorted(ids_sorted, bounds)  # owners are contiguous id ranges and the ids are sorted
+        req_counts = torch.diff(torch.cat([cut.new_zeros(1), cut, cut.new_full((1,), ids_sorted.numel())]))
+        got_counts = torch.empty_like(req_counts)
+        dist.all_to_all_single(got_counts, req_counts, group=self.group)
+        req_l, got_l = req_counts.tolist(), got_counts.tolist()  # host sync: the split sizes of the next two calls
+        asked = torch.empty(sum(got_l), dtype=torch.int64, device=dev)
+        dist.all_to_all_single(asked, ids_sorted, got_l, req_l, group=self.group)
+        served = ent[asked - self.lo]  # every asked id is ours
+        rows = torch.empty((ids_sorted.numel(), m.entity_dim), dtype=torch.float32, device=dev)
+        dist.all_to_all_single(rows, served, req_l, got_l, group=self.group)
+        self.last_exchange = {"rows_requested": int(ids_sorted.numel()), "rows_served": int(asked.numel())}
+        return rows
+
+    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
+        m = self.model
+        B, N = neg.shape
+        ids = torch.cat([pos[:, 0], pos[:, 2], neg.reshape(-1)])
+        uniq, inv = torch.unique(ids, sorted=True, return_inverse=True)
+        compact = self.fetch_rows(uniq).contiguous()
+        cpos = torch.stack([inv[:B], pos[:, 1], inv[B:2 * B]], dim=1).contiguous()
+        cneg = inv[2 * B:].view(B, N).contiguous()
+        self._run_sweep(mode, compact, cpos, cneg, w, wsum, B_total, loss_opts)
+
+    def _run_sweep(self, mode, compact, cpos, cneg, w, wsum, B_total, loss_opts):
+        m = self.model
+        B, N = cneg.shape
+        desc = m._desc()
+        desc.nentity = compact.shape[0]
+        bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        with torch.cuda.device(compact.device):
+            _lib.check(_lib.load().kge_train_sweep(
+                C.byref(desc), ops.mode_id(mode), ops._ptr(compact), ops._ptr(m.relation_embedding),
+                ops._ptr(m._modulus()), ops._ptr(cpos), ops._ptr(cneg), ops._ptr(w), B, N, C.byref(loss_opts),
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._stream()), "kge_train_sweep")
+
+    # ---- 4: owners gather gradients and apply Adam on their shard ---------------------------------------------
+    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out):
+        m, opt = self.model, self.optimizer
+        B_all, N = neg_all.shape
+        ent, rel, mod = m.entity_embedding, m.relation_embedding, m._modulus()
+        st_e, st_r = opt.state[ent], opt.state[rel]
+        st_m = opt.state[mod] if mod is not None else None
+        desc = m._desc()
+        need = ops.workspace_bytes(_lib.WS_TRAIN_APPLY, desc, B_all, N)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=ent.device)
+        bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
+        P = ops._ptr
+        with torch.cuda.device(ent.device):
+            _lib.check(_lib.load().kge_train_apply_shard(
+                C.byref(desc), ops.mode_id(mode), P(ent), self.lo, ent.shape[0], P(rel), P(mod), P(st_e["exp_avg"]),
+                P(st_e["exp_avg_sq"]), P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
+                P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
+                C.byref(adam), C.byref(bufs), self.lo, self.hi, P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws),
+                self._ws.numel(), ops._stream()), "kge_train_apply_shard")
+
+    def _share_rows(self):
+        """Rows stay with their owners: nothing to broadcast."""
+        return

@@ -265,6 +265,22 @@ KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity,
                             float *reg1, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * kge_train_apply over a ROW-SHARDED entity table: `entity_shard`, `adam_m_shard`, `adam_v_shard` hold only the rows
+ * [shard_row0, shard_row0 + shard_rows) (desc->nentity stays the global E; ids in positive_all / negative_all are
+ * global); [entity_lo, entity_hi) must lie inside the shard.  With kge_train_sweep run on a compact table of the
+ * rows this rank's batch touches (fetched from their owners, ids remapped) this is the row-sharded train step of
+ * no rank ever holds the full table or its Adam state.
+ */
+KGE_API int kge_train_apply_shard(const kge_model_desc *desc, int mode, float *entity_shard, int64_t shard_row0,
+                                  int64_t shard_rows, float *relation, float *modulus, float *adam_m_shard,
+                                  float *adam_v_shard, float *adam_m_relation, float *adam_v_relation,
+                                  float *adam_m_modulus, float *adam_v_modulus, const int64_t *positive_all,
+                                  const int64_t *negative_all, int64_t B_all, int64_t N,
+                                  const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
+                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi,
+                                  float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/*
  * Measurement hooks (bench.py): when enabled, kge_train_step* brackets each of its stages with CUDA
  * events on the caller's stream.  kge_profile_read synchronises those events and returns, per stage, the
  * summed device time in ms and the number of kernel launches since the last reset.  Stage names:

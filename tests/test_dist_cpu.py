@@ -98,6 +98,15 @@ def _worker(rank, world, port, tmp):
                                   rank_fn=lambda q, mode, ip, ix: sm.rank_queries(q, mode, ip, ix, local_fn=shard_local))
     assert np.array_equal(sm.last_eval["ranks"], ranks) and got_s == want
 
+    # ---------------- row-sharded train step: the id / row all-to-all (each rank asks for different rows) ----------
+    rstep = kd.RowShardedStep(sm, torch.optim.Adam(filter(lambda p: p.requires_grad, sm.parameters()), lr=1e-2))
+    want_ids = torch.unique(torch.from_numpy(np.random.RandomState(50 + rank).randint(0, E, 40 + 7 * rank)))
+    assert torch.equal(rstep.fetch_rows(want_ids), om.entity_embedding.detach()[want_ids])
+    assert rstep.last_exchange["rows_requested"] == want_ids.numel()
+    only_low = torch.arange(0, 5)  # every rank asks rank 0 only; rank 1 serves nothing
+    assert torch.equal(rstep.fetch_rows(only_low), om.entity_embedding.detach()[only_low])
+    assert torch.equal(rstep.fetch_rows(torch.zeros(0, dtype=torch.int64)), torch.zeros(0, sm.entity_dim))
+
     # ---------------- train: sweep local / gather / apply owned rows / broadcast ----------------
     class Step(kd.DataParallelStep):
         def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):

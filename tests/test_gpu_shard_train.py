@@ -1,0 +1,99 @@
+"""GPU: the ROW-SHARDED train step (RowShardedStep: compact-table sweep + kge_train_apply_shard) reproduces the
+single-GPU step bit for bit.  Ranks are emulated on one GPU by running their pieces one after the other (the
+NCCL run over real ranks is scratch/dist_check.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import kge_oracle as ko
+
+pytestmark = pytest.mark.gpu
+GAMMA = {"TransE": 12.0, "DistMult": 12.0, "ComplEx": 12.0, "RotatE": 9.0, "pRotatE": 9.0, "InterHT": 24.0}
+
+
+def _model(name, E, R, H, seed):
+    import customknowledgegraphembedding_b200 as kb
+    om = ko.make_model(name, E, R, H, GAMMA[name], seed=seed)
+    de, dr, tr = ko.model_flags(name)
+    gm = kb.KGEModel(name, E, R, H, GAMMA[name], de, dr, tr)
+    gm.load_state_dict(om.state_dict())
+    return gm.cuda()
+
+
+def _adam(m, lr):
+    return torch.optim.Adam(filter(lambda p: p.requires_grad, m.parameters()), lr=lr)
+
+
+@pytest.mark.parametrize("name", ko.MODEL_NAMES)
+def test_world1_sharded_step_equals_plain_step(name):
+    """One rank owning every row: exercises the unique / remap / compact-table sweep and the shard apply."""
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import dist as kd
+    E, R, H, B, N, lr = 300, 5, 64, 16, 24, 1e-3
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=0.5, cuda=True)
+    ref = _model(name, E, R, H, seed=2)
+    ref_opt = _adam(ref, lr)
+    sm = kd.RowShardedKGEModel.from_full(_model(name, E, R, H, seed=2), rank_world=(0, 1))
+    step = kd.RowShardedStep(sm, _adam(sm, lr))
+    for s in range(3):
+        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=s)
+        batch = (pos.cuda(), neg.cuda(), w.cuda(), mode)
+        want = kb.KGEModel.train_step(ref, ref_opt, iter([batch]), args)
+        got = step.train_step(iter([batch]), args)
+        assert got["loss"] == want["loss"], (s, got, want)
+        assert torch.equal(sm.entity_embedding, ref.entity_embedding), s
+        assert torch.equal(sm.relation_embedding, ref.relation_embedding), s
+
+
+@pytest.mark.parametrize("name", ["RotatE", "TransE", "InterHT", "pRotatE"])
+@pytest.mark.parametrize("world", [2, 3])
+def test_emulated_ranks_equal_plain_step(name, world):
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import dist as kd
+    E, R, H, B, N, lr = 211, 5, 32, 12, 20, 1e-3
+    half = B // world
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
+    ref = _model(name, E, R, H, seed=5)
+    ref_opt = _adam(ref, lr)
+    full0 = _model(name, E, R, H, seed=5)
+    shards = [kd.RowShardedKGEModel.from_full(full0, rank_world=(r, world)) for r in range(world)]
+    steps = [kd.RowShardedStep(s, _adam(s, lr)) for s in shards]
+    loss_opts = kd.LossOpts(1, 0, 1, 0, 1.0, 0.0)
+    for it in range(3):
+        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=10 + it)
+        pos, neg, w = pos.cuda(), neg.cuda(), w.cuda()
+        want = kb.KGEModel.train_step(ref, ref_opt, iter([(pos, neg, w, mode)]), args)
+        table = torch.cat([s.entity_embedding.detach() for s in shards])  # what the owners would serve
+        wsum = w.sum().reshape(1)
+        gathered = {}
+        for r, st in enumerate(steps):
+            sl = slice(r * half, (r + 1) * half)
+            st.fetch_rows = lambda ids, table=table: table[ids]  # the all-to-all, emulated
+            st.world = 1
+            st._shape = None
+            st._ensure(half, N, pos.device)
+            st._sweep(mode, pos[sl].contiguous(), neg[sl].contiguous(), w[sl].contiguous(), wsum, B, loss_opts)
+            for k, v in st._local.items():
+                gathered.setdefault(k, []).append(v.clone())
+        gathered = {k: torch.cat(v) for k, v in gathered.items()}
+        losses = []
+        for r, st in enumerate(steps):
+            st._gathered = gathered
+            m, opt = st.model, st.optimizer
+            for p in (m.entity_embedding, m.relation_embedding) + ((m.modulus,) if name == "pRotatE" else ()):
+                m._adam_state(opt, p)["step"] += 1
+            adam = kd.AdamOpts(lr, 0.9, 0.999, 1e-8, it + 1, 0)
+            out = torch.zeros(4, device="cuda")
+            st._apply(mode, pos, neg, loss_opts, adam, out)
+            losses.append(out[2].item())
+        # identical arithmetic except the weight sum (torch reduction vs in-kernel reduction order): same bound as
+        # tests/test_gpu_dist.py; every rank must agree with every other rank exactly
+        assert all(l == losses[0] for l in losses)
+        np.testing.assert_allclose(losses[0], want["loss"], rtol=2e-6)
+        now = torch.cat([s.entity_embedding.detach() for s in shards])
+        assert float((now - ref.entity_embedding.detach()).abs().max()) <= 2e-3 * lr * (it + 1), it
+        for s in shards:
+            assert torch.equal(s.relation_embedding, shards[0].relation_embedding)
+            assert float((s.relation_embedding - ref.relation_embedding).abs().max()) <= 2e-3 * lr * (it + 1)
+            if name == "pRotatE":
+                assert torch.equal(s.modulus, shards[0].modulus)
