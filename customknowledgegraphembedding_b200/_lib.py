@@ -70,6 +70,7 @@ PROTOTYPES = {
     "kge_eval_rank_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P,
                                       C.c_int, _P, _SZ, _P]),
     "kge_eval_set_tensor_path": (C.c_int, [C.c_int]),
+    "kge_train_set_sweep_variant": (C.c_int, [C.c_int]),
     "kge_train_step": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                  C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _P, _SZ, _P]),
     "kge_train_step_host": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,

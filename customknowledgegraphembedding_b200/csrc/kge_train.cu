@@ -293,6 +293,11 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_apply(copy loss)");
 }
 
+int kge_train_set_sweep_variant(int variant) {
+    train_set_sweep_variant(variant);
+    return KGE_OK;
+}
+
 int kge_train_apply_shard(const kge_model_desc* desc, int mode, float* entity_shard, int64_t shard_row0,
                           int64_t shard_rows, float* relation, float* modulus, float* adam_m_shard, float* adam_v_shard,
                           float* adam_m_relation, float* adam_v_relation, float* adam_m_modulus, float* adam_v_modulus,

@@ -4,6 +4,7 @@
 
 namespace kge {
 size_t train_step_workspace_bytes(const Params& P, int64_t B, int64_t N, bool host_batch);
+void train_set_sweep_variant(int v);  // 1 = warp-per-row split sweep where it applies (default), 0 = row groups per CTA
 
 // second-generation step (kge_train_fused.cu)
 size_t fused_step_workspace_bytes(const Params& P, int64_t B, int64_t N);

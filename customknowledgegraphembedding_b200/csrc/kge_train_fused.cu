@@ -76,6 +76,13 @@ struct SweepArgs {
     int* counts;         // NULL: uses are counted later (multi-rank apply phase)
     const float* wsum;   // NULL: sum the B local weights; else device scalar with the global sum
     int B_total;         // positives of the global batch (uniform weights: coef = 1 / B_total)
+    // Split sweep (F1w, train_sweep_rows_kernel): part 0 = everything in this kernel (row groups of RPI rows);
+    // 1 = stage Q[b] and return; 2 = the candidate rows were swept by F1w: merge its partial dL/dq, finish the
+    // softmax statistics from S, then the positive score and the chain rule as usual.
+    int part;
+    int parts;           // items per positive of F1w
+    const float* PA;     // [B*parts][QP*H] partial dL/dq, relative to the item's own running max
+    const float* PM;     // [B*parts][2]    (running max, pRotatE modulus partial)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -111,7 +118,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         block_reduce_vals<1>(part, red);
         coef = __ldg(A.w + b) / part[0];
     }
-    if (tid == 0 && A.counts != nullptr) {  // every use of an entity row is counted for the bucket build
+    if (tid == 0 && A.counts != nullptr && A.part != 1) {  // every use of an entity row is counted for the bucket build
         atomicAdd(A.counts + h, 1);
         atomicAdd(A.counts + t, 1);
     }
@@ -158,6 +165,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
             }
     }
 
+    if (A.part == 1) return;  // staging pass of the split sweep: Q[b] is all F1w needs
+
     // ---- the sweep -------------------------------------------------------------------------------
     float acc[QP][CH][4];
 #pragma unroll
@@ -176,7 +185,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
 #pragma unroll
     for (int rr = 0; rr < RPI; ++rr) cid[rr] = (rr < N) ? (int)__ldg(A.neg + b * N + rr) : 0;
 
-    for (int n0 = 0; n0 < N; n0 += RPI) {
+    const int n_sweep = (A.part == 0) ? N : 0;
+    for (int n0 = 0; n0 < n_sweep; n0 += RPI) {
         float c[RPI][CP][CH][4];
         float sg[(MODEL == KGE_INTERHT) ? RPI : 1][CH][4];
 #pragma unroll
@@ -288,6 +298,49 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                     else dq_accumulate<MODEL, false>(aa, dd, s1, wgt, kc);
 #pragma unroll
                     for (int p = 0; p < QP; ++p) acc[p][j][i] = aa[p];
+                }
+        }
+    }
+
+    if (A.part == 2) {
+        // ---- merge of the split sweep: scores S[b,:] and the per-item partials are in global memory --------
+        float m = -INFINITY;
+        if (A.adv)
+            for (int p = 0; p < A.parts; ++p) m = fmaxf(m, __ldg(A.PM + 2 * (b * A.parts + p)));
+        float zl[2] = {0.f, 0.f};
+        for (int n = tid; n < N; n += T) {
+            const float s = A.S[b * N + n];
+            const float ls = log_sigmoid(-s);
+            if (A.adv) {
+                const float e = expf(s * A.alpha - m);
+                zl[0] += e;
+                zl[1] += e * ls;
+            } else {
+                zl[1] += ls;
+            }
+        }
+        block_reduce_vals<2>(zl, red);
+        m_run = m;
+        z_run = zl[0];
+        l_run = zl[1];
+        g_run = 0.f;
+        for (int p = 0; p < A.parts; ++p) {  // fixed order: bit-reproducible
+            const long long item = b * A.parts + p;
+            const float mp = __ldg(A.PM + 2 * item);
+            const float f = A.adv ? ((mp == -INFINITY) ? 0.f : expf(mp - m)) : 1.0f;
+            g_run = fmaf(__ldg(A.PM + 2 * item + 1), f, g_run);
+#pragma unroll
+            for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+                for (int j = 0; j < CH; ++j) {
+                    const int k0 = 4 * (tid + j * T);
+                    if (k0 < H) {
+                        const float4 v = __ldg(reinterpret_cast<const float4*>(A.PA + (item * QP + pl) * H + k0));
+                        acc[pl][j][0] = fmaf(v.x, f, acc[pl][j][0]);
+                        acc[pl][j][1] = fmaf(v.y, f, acc[pl][j][1]);
+                        acc[pl][j][2] = fmaf(v.z, f, acc[pl][j][2]);
+                        acc[pl][j][3] = fmaf(v.w, f, acc[pl][j][3]);
+                    }
                 }
         }
     }
@@ -479,6 +532,154 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         A.terms[2 * b] = coef * log_sigmoid(s_pos);
         A.terms[2 * b + 1] = coef * negterm;
         if (MODEL == KGE_PROTATE) A.GM[b] = -(scale_b * gsum + dpos * ptot[0]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// F1w: the candidate sweep, one WARP per row (split sweep, parts 1 + F1w + 2)
+//
+// Work item = (positive b, part p): rows [p*rpp, (p+1)*rpp) of b's candidates.  A warp owns an item: lane l owns
+// the coordinates 4*(l + 32*j), j < CH, of every row, so a row sum is ONE warp reduction -- no block barrier, no
+// shared-memory round trip, and the online-softmax recurrence advances once per row inside the warp instead of
+// once per row group in every warp of a CTA.  q_b comes from Q[b] (staged by part 1) through shared memory, the
+// dL/dq accumulator stays in registers relative to the item's own running max and is written once per item
+// (PA / PM); part 2 merges the items of a positive in fixed order.  Items are handed out by an atomic counter
+// (8 items per positive: 8192 items for 1776 resident warps), results do not depend on who ran which item.
+// The next row is prefetched into L2 while the current one is processed.
+// ------------------------------------------------------------------------------------------------
+struct RowsArgs {
+    const float* ent;
+    const int64_t* neg;
+    const float* Q;
+    const float* modulus;
+    float* S;
+    float* PA;
+    float* PM;
+    int* counter;
+    int B, N, parts, rpp, adv;
+    float alpha;
+};
+
+template <int MODEL, int CH, bool HEAD>
+__global__ void __launch_bounds__(128)
+train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
+    constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
+    extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4* myq = f1w_q + warp * (QP * CH * 32);
+    const int H = P.H, N = A.N;
+    if (MODEL == KGE_PROTATE) kc.modulus = __ldg(A.modulus);
+    const int total = A.B * A.parts;
+    const int row_lines = (P.De * 4 + 127) / 128;
+    const float cn[2] = {0.f, 0.f};
+
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = atomicAdd(A.counter, 1);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= total) break;
+        const long long b = item / A.parts;
+        const int n0 = (item % A.parts) * A.rpp, n1 = min(N, n0 + A.rpp);
+
+        __syncwarp();  // the previous item's reads of myq are done
+#pragma unroll
+        for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const int k0 = 4 * (lane + 32 * j);
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);  // padding coordinates: q = 0 and c = 0 give a zero term
+                if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(A.Q + (b * QP + pl) * H + k0));
+                myq[(pl * CH + j) * 32 + lane] = v;
+            }
+        __syncwarp();
+
+        float acc[QP][CH][4];
+#pragma unroll
+        for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[pl][j][i] = 0.f;
+        float m_run = -INFINITY, g_run = 0.f;
+
+        long long id = (n0 < n1) ? __ldg(A.neg + b * N + n0) : 0;
+        for (int n = n0; n < n1; ++n) {
+            const float* row = A.ent + id * (long long)P.De;
+            float c[CP][CH][4];
+#pragma unroll
+            for (int pl = 0; pl < CP; ++pl)
+#pragma unroll
+                for (int j = 0; j < CH; ++j) {
+                    const int k0 = 4 * (lane + 32 * j);
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
+                    c[pl][j][0] = v.x; c[pl][j][1] = v.y; c[pl][j][2] = v.z; c[pl][j][3] = v.w;
+                }
+            if (n + 1 < n1) {  // next id, and its row on the way into L2
+                id = __ldg(A.neg + b * N + n + 1);
+                const char* nxt = reinterpret_cast<const char*>(A.ent + id * (long long)P.De);
+                for (int l = lane; l < row_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + 128 * l));
+            }
+            float part = 0.f;
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const float4 q0 = myq[(0 * CH + j) * 32 + lane];
+                const float4 q1 = (QP > 1) ? myq[((QP > 1 ? 1 : 0) * CH + j) * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float q0a[4] = {q0.x, q0.y, q0.z, q0.w}, q1a[4] = {q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float qq[3] = {q0a[i], q1a[i], 0.f};
+                    float cc[2] = {c[0][j][i], (CP > 1) ? c[CP - 1][j][i] : 0.f};
+                    float s1 = 0.f;
+                    part += fwd_coord<MODEL, HEAD>(qq, cc, kc, cn, s1);
+                    c[0][j][i] = cc[0];
+                    if (CP > 1) c[CP - 1][j][i] = cc[1];
+                }
+            }
+            const float tot = warp_sum(part);
+            const float s = score_from_sum<MODEL>(tot, kc);
+            if (lane == 0) A.S[b * N + n] = s;
+            float wgt = sigmoidf(s);
+            if (A.adv) {
+                const float a = s * A.alpha;
+                if (a > m_run) {  // warp-uniform; rare once the running max has settled
+                    const float sc = (m_run == -INFINITY) ? 0.f : expf(m_run - a);
+                    m_run = a;
+                    g_run *= sc;
+#pragma unroll
+                    for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+                        for (int j = 0; j < CH; ++j)
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) acc[pl][j][i] *= sc;
+                }
+                wgt *= expf(a - m_run);
+            }
+            if (MODEL == KGE_PROTATE) g_run = fmaf(wgt, tot, g_run);
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float aa[3] = {acc[0][j][i], (QP > 1) ? acc[QP > 1 ? 1 : 0][j][i] : 0.f, 0.f};
+                    const float dd[2] = {c[0][j][i], (CP > 1) ? c[CP - 1][j][i] : 0.f};
+                    dq_accumulate<MODEL, HEAD>(aa, dd, 0.f, wgt, kc);
+                    acc[0][j][i] = aa[0];
+                    if (QP > 1) acc[QP > 1 ? 1 : 0][j][i] = aa[1];
+                }
+        }
+#pragma unroll
+        for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+                const int k0 = 4 * (lane + 32 * j);
+                if (k0 < H)
+                    *reinterpret_cast<float4*>(A.PA + ((long long)item * QP + pl) * H + k0) =
+                        make_float4(acc[pl][j][0], acc[pl][j][1], acc[pl][j][2], acc[pl][j][3]);
+            }
+        if (lane == 0) {
+            A.PM[2 * (long long)item] = m_run;
+            A.PM[2 * (long long)item + 1] = g_run;
+        }
     }
 }
 
@@ -731,8 +932,18 @@ static inline size_t fz_align(size_t x) { return (x + 255) & ~(size_t)255; }
 struct FusedWs {
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms, *small, *l3_ws;
     int *counts, *offsets, *cursor, *items, *items_sorted, *items_b, *block_sums;
+    float *PA, *PM;      // split sweep: per-item partial dL/dq and (running max, modulus partial)
+    int* item_counter;
     size_t total;
 };
+
+// split sweep (F1w): items per positive and rows per item
+static inline int f1w_parts(int64_t N) { return (int)std::max<int64_t>(1, std::min<int64_t>(8, (N + 31) / 32)); }
+static int g_sweep_variant = 1;  // 1 = warp per row (F1w) where it applies, 0 = row groups per CTA
+void train_set_sweep_variant(int v) { g_sweep_variant = v ? 1 : 0; }
+static inline bool f1w_applies(const Params& P) {
+    return g_sweep_variant == 1 && P.model != KGE_INTERHT && P.H % 4 == 0 && P.H <= 1024;
+}
 
 static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
     FusedWs w{};
@@ -760,6 +971,9 @@ static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
     w.items_sorted = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
     w.items_b = (int*)take((size_t)(B * N + 2 * B) * sizeof(int));
     w.block_sums = (int*)take((size_t)((P.E + 1024) / 1024 + 2) * sizeof(int));
+    w.PA = (float*)take((size_t)B * f1w_parts(N) * qdim * sizeof(float));
+    w.PM = (float*)take((size_t)B * f1w_parts(N) * 2 * sizeof(float));
+    w.item_counter = (int*)take(64);
     w.total = off;
     return w;
 }
@@ -803,6 +1017,38 @@ struct FusedCall {
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
 };
 
+template <int MODEL, int CHW, bool HEAD>
+static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc, const RowsArgs& R, cudaStream_t st) {
+    constexpr size_t smem = (size_t)4 * model_planes(MODEL) * CHW * 32 * sizeof(float4);
+    static int grid = 0;  // persistent: every CTA the device can hold
+    if (grid == 0) {
+        if (smem > 48 * 1024)
+            cudaFuncSetAttribute(train_sweep_rows_kernel<MODEL, CHW, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        int per_sm = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, train_sweep_rows_kernel<MODEL, CHW, HEAD>, 128, smem);
+        if (e != cudaSuccess) return e;
+        grid = std::max(1, per_sm) * sm_count();
+    }
+    const int items = R.B * R.parts;
+    train_sweep_rows_kernel<MODEL, CHW, HEAD><<<std::min(grid, (items + 3) / 4), 128, smem, st>>>(P, kc, R);
+    return cudaGetLastError();
+}
+
+template <int MODEL>
+static cudaError_t launch_sweep_rows(const Params& P, const CoordConsts& kc, bool head, const RowsArgs& R, cudaStream_t st) {
+    if constexpr (MODEL == KGE_INTERHT) {
+        return cudaErrorInvalidValue;
+    } else {
+#define KGE_ROWS(CHW)                                                                       \
+    return head ? launch_sweep_rows_inst<MODEL, CHW, true>(P, kc, R, st)                    \
+                : launch_sweep_rows_inst<MODEL, CHW, false>(P, kc, R, st)
+        if (P.H <= 256) { KGE_ROWS(2); }
+        if (P.H <= 512) { KGE_ROWS(4); }
+        KGE_ROWS(8);
+#undef KGE_ROWS
+    }
+}
+
 template <int MODEL, int CH, int RPI>
 static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
                                 float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
@@ -819,7 +1065,25 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
                     lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
                     fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
-        train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+        if (fc.phase == 0 && f1w_applies(P)) {
+            if constexpr (MODEL != KGE_INTERHT) {
+                // split sweep: stage Q | one warp per candidate row | merge + positive score + chain rule
+                A.part = 1;
+                train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+                if ((e = cudaMemsetAsync(ws.item_counter, 0, sizeof(int), st)) != cudaSuccess) return e;
+                const int parts = f1w_parts(N);
+                RowsArgs R{ent, fc.neg, fc.Q, modulus, fc.S, ws.PA, ws.PM, ws.item_counter, (int)fc.B, (int)N, parts,
+                           (int)((N + parts - 1) / parts), lo.negative_adversarial_sampling, lo.adversarial_temperature};
+                if ((e = launch_sweep_rows<MODEL>(P, kc, head != 0, R, st)) != cudaSuccess) return e;
+                A.part = 2;
+                A.parts = parts;
+                A.PA = ws.PA;
+                A.PM = ws.PM;
+                train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+            }
+        } else {
+            train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+        }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (fc.phase == 1) return cudaSuccess;
     }

@@ -231,6 +231,14 @@ KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *ent
                         float *host_loss4, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * Candidate sweep of the fused step: variant 1 (default) = split sweep, one warp per candidate row with the
+ * per-item partial dL/dq merged in fixed order (TransE, DistMult, ComplEx, RotatE, pRotatE with H <= 1024, H % 4 == 0);
+ * variant 0 = one CTA per positive over row groups (all models; what the split sweep falls back to).  Process-wide;
+ * both are bit-reproducible run to run, they differ from each other in summation order only.
+ */
+KGE_API int kge_train_set_sweep_variant(int variant);
+
+/*
  * Multi-GPU split of the step (one process per GPU; the caller does the NCCL plumbing between the two calls).
  * The step shards twice: positives are data-parallel in the SWEEP, entity rows are owner-parallel in the APPLY.
  *

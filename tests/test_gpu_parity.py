@@ -287,3 +287,41 @@ def test_errors_like_reference():
     m = kb.KGEModel("TransE", 4, 2, 4, 1.0).cuda()
     with pytest.raises(ValueError):
         m(torch.zeros(1, 3, dtype=torch.int64).cuda(), "bad-mode")
+
+
+@pytest.mark.parametrize("name", ["TransE", "DistMult", "ComplEx", "RotatE", "pRotatE"])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_sweep_variants(name, variant):
+    """Both candidate sweeps of the fused step against the oracle: 1 = warp per row (split sweep, the default where
+    it applies), 0 = row groups per CTA (what InterHT / H > 1024 use).  Same tolerances as above."""
+    from customknowledgegraphembedding_b200 import _lib
+    lib = _lib.load()
+    lib.kge_train_set_sweep_variant(variant)
+    try:
+        test_train_step_matches_oracle(name, False, 0)
+        test_fused_step_shapes(name, 1000, 256, "tail-batch")
+        test_fused_step_shapes(name, 500, 37, "head-batch")
+        test_fused_step_shapes(name, 12, 70, "head-batch")   # several items per positive with a ragged last item
+    finally:
+        lib.kge_train_set_sweep_variant(1)
+
+
+def test_sweep_variants_agree():
+    """The two sweeps differ in summation order only: same loss to 2e-6, same gradient (Adam's first moment after
+    one step is 0.1 * g) to 5e-5 of its largest entry."""
+    from customknowledgegraphembedding_b200 import _lib
+    lib = _lib.load()
+    E, R, H, B, N = 500, 6, 1000, 40, 256
+    losses, grads = [], []
+    for variant in (0, 1):
+        lib.kge_train_set_sweep_variant(variant)
+        try:
+            _, gm = _pair("RotatE", E, R, H, seed=4)
+            opt = torch.optim.Adam(filter(lambda p: p.requires_grad, gm.parameters()), lr=1e-3)
+            args = ko.Args(negative_adversarial_sampling=True, cuda=True)
+            losses.append(type(gm).train_step(gm, opt, iter([ko.synthetic_batch(E, R, B, N, seed=0)]), args)["loss"])
+        finally:
+            lib.kge_train_set_sweep_variant(1)
+        grads.append(opt.state[gm.entity_embedding]["exp_avg"].clone())
+    np.testing.assert_allclose(losses[0], losses[1], rtol=2e-6)
+    assert float((grads[0] - grads[1]).abs().max()) <= 5e-5 * float(grads[0].abs().max())
