@@ -11,12 +11,12 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # kge_model_id / kge_mode / kge_ws_kind
 MODEL_IDS = {"TransE": 0, "DistMult": 1, "ComplEx": 2, "RotatE": 3, "pRotatE": 4, "InterHT": 5}
 MODE_IDS = {"single": 0, "head-batch": 1, "tail-batch": 2}
-WS_BACKWARD, WS_LOSS, WS_EVAL, WS_TRAIN_STEP, WS_TRAIN_STEP_HOST, WS_TRAIN_APPLY = range(6)
+WS_BACKWARD, WS_LOSS, WS_EVAL, WS_TRAIN_STEP, WS_TRAIN_STEP_HOST, WS_TRAIN_APPLY, WS_TRAIN_SWEEP = range(7)
 
 KGE_OK = 0
 KGE_ERR_INVALID_ARGUMENT = -1
@@ -76,7 +76,7 @@ PROTOTYPES = {
     "kge_train_step_host": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                       C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _SZ, _P]),
     "kge_train_sweep": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
-                                  C.POINTER(StepBuffers), _P]),
+                                  C.POINTER(StepBuffers), _P, _SZ, _P]),
     "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                   C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P, _P,
                                   _P, _SZ, _P]),

@@ -256,6 +256,7 @@ size_t kge_workspace_bytes(int kind, const kge_model_desc* desc, int64_t B, int6
         case KGE_WS_TRAIN_STEP: return train_step_workspace_bytes(P, B, N, false);
         case KGE_WS_TRAIN_STEP_HOST: return train_step_workspace_bytes(P, B, N, true);
         case KGE_WS_TRAIN_APPLY: return fused_step_workspace_bytes(P, B, N);
+        case KGE_WS_TRAIN_SWEEP: return train_sweep_workspace_bytes(P, B, N);
     }
     return 0;
 }

@@ -66,6 +66,30 @@ __device__ __forceinline__ float accum(float acc, float q0, float q1, float q2, 
     }
 }
 
+// Two candidates per instruction on the packed fp32 pipe (fma.rn.f32x2 / FFMA2; a scalar 3-register FFMA issues at
+// half rate on sm_100, which is what bounded the tile kernel below the SFU ceiling).  Each component goes through
+// exactly the roundings of accum<> above (x - y == fma(y, -1, x); __f*2_rn round per component like __f*_rn), so
+// the tile stays bit-consistent with the true-score and filter passes.
+template <int MODEL>
+__host__ __device__ constexpr bool packed_accum() { return MODEL == KGE_ROTATE || MODEL == KGE_TRANSE; }
+
+template <int MODEL, bool HEAD>
+__device__ __forceinline__ float2 accum2(float2 acc, float q0, float q1, float2 c0, float2 c1) {
+    const float2 neg1 = make_float2(-1.f, -1.f);
+    const float2 qq0 = make_float2(q0, q0);
+    if constexpr (MODEL == KGE_TRANSE) {
+        float2 v = HEAD ? __fadd2_rn(c0, qq0) : __ffma2_rn(c0, neg1, qq0);
+        v.x = fabsf(v.x);
+        v.y = fabsf(v.y);
+        return __fadd2_rn(acc, v);
+    } else {  // RotatE
+        const float2 qq1 = make_float2(q1, q1);
+        const float2 vr = __ffma2_rn(c0, neg1, qq0), vi = __ffma2_rn(c1, neg1, qq1);
+        const float2 n2 = __ffma2_rn(vr, vr, __fmul2_rn(vi, vi));
+        return __fadd2_rn(acc, make_float2(fast_sqrt(n2.x), fast_sqrt(n2.y)));
+    }
+}
+
 template <int MODEL>
 __device__ __forceinline__ float finalize(float acc, const EvalConsts& c) {
     if constexpr (MODEL == KGE_DISTMULT || MODEL == KGE_COMPLEX) return acc;
@@ -321,11 +345,11 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
 
     // compute role: 8 queries x 8 entities, split 4 + 4 so that LDS.128 is conflict-free
     const int ty = tid >> 4, tx = tid & 15;
-    float acc[8][8];
+    float2 acc[8][4];  // [query][candidate pair]
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < 4; ++j) acc[i][j] = make_float2(0.f, 0.f);
 
     const int nchunks = (H + kKC - 1) / kKC;
     fetch(0);
@@ -356,10 +380,19 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
 #pragma unroll
             for (int i = 0; i < 8; ++i)
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    acc[i][j] = accum<MODEL, HEAD>(acc[i][j], qv[0][i], (QP > 1) ? qv[QP > 1 ? 1 : 0][i] : 0.f,
-                                                   (QP > 2) ? qv[QP > 2 ? 2 : 0][i] : 0.f, ev[0][j],
-                                                   (CP > 1) ? ev[CP - 1][j] : 0.f);
+                for (int j = 0; j < 4; ++j) {
+                    const float q0 = qv[0][i], q1 = (QP > 1) ? qv[QP > 1 ? 1 : 0][i] : 0.f;
+                    if constexpr (packed_accum<MODEL>()) {
+                        acc[i][j] = accum2<MODEL, HEAD>(acc[i][j], q0, q1, make_float2(ev[0][2 * j], ev[0][2 * j + 1]),
+                                                        (CP > 1) ? make_float2(ev[CP - 1][2 * j], ev[CP - 1][2 * j + 1])
+                                                                 : make_float2(0.f, 0.f));
+                    } else {
+                        const float q2 = (QP > 2) ? qv[QP > 2 ? 2 : 0][i] : 0.f;
+                        acc[i][j].x = accum<MODEL, HEAD>(acc[i][j].x, q0, q1, q2, ev[0][2 * j], (CP > 1) ? ev[CP - 1][2 * j] : 0.f);
+                        acc[i][j].y = accum<MODEL, HEAD>(acc[i][j].y, q0, q1, q2, ev[0][2 * j + 1],
+                                                         (CP > 1) ? ev[CP - 1][2 * j + 1] : 0.f);
+                    }
+                }
         }
         if (ch + 1 < nchunks) {
             stash(buf ^ 1, (ch + 1) * kKC);  // the other buffer was last read in iteration ch-1
@@ -378,7 +411,7 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const long long e = e0 + ((j < 4) ? (tx * 4 + j) : (64 + tx * 4 + j - 4));
-            const float s = finalize<MODEL>(acc[i][j], c);
+            const float s = finalize<MODEL>((j & 1) ? acc[i][j >> 1].y : acc[i][j >> 1].x, c);
             const bool ok = qok && e < e_hi && e != te;
             gt += (ok && s > t) ? 1 : 0;
             eq += (ok && s == t) ? 1 : 0;

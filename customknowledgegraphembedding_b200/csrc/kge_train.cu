@@ -246,7 +246,8 @@ int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* r
 int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
                     const float* modulus, const int64_t* positive, const int64_t* negative,
                     const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
-                    const float* wsum, int64_t B_total, const kge_step_buffers* out, void* stream) {
+                    const float* wsum, int64_t B_total, const kge_step_buffers* out, void* ws, size_t ws_bytes,
+                    void* stream) {
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -261,7 +262,7 @@ int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, c
     if (!fused_step_applicable(P, *loss_opts, B_total, N, entity, relation))
         return fail(KGE_ERR_UNSUPPORTED, "kge_train_sweep: the fused step does not apply to this configuration");
     cudaError_t e = launch_train_sweep(P, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
-                                       *loss_opts, wsum, B_total, *out, (cudaStream_t)stream);
+                                       *loss_opts, wsum, B_total, *out, ws, ws_bytes, (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_sweep");
 }
 

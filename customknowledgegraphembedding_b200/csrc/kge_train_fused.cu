@@ -571,6 +571,7 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
     if (MODEL == KGE_PROTATE) kc.modulus = __ldg(A.modulus);
     const int total = A.B * A.parts;
     const int row_lines = (P.De * 4 + 127) / 128;
+    const int jfull = H / 128;  // chunks whose 32 lanes all hold live coordinates
     const float cn[2] = {0.f, 0.f};
 
     for (;;) {
@@ -611,8 +612,13 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
 #pragma unroll
                 for (int j = 0; j < CH; ++j) {
                     const int k0 = 4 * (lane + 32 * j);
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
+                    float4 v;
+                    if (j < jfull) {  // warp-uniform: every lane of this chunk is inside the row
+                        v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
+                    } else {
+                        v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
+                    }
                     c[pl][j][0] = v.x; c[pl][j][1] = v.y; c[pl][j][2] = v.z; c[pl][j][3] = v.w;
                 }
             if (n + 1 < n1) {  // next id, and its row on the way into L2
@@ -621,6 +627,33 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
                 for (int l = lane; l < row_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + 128 * l));
             }
             float part = 0.f;
+            if constexpr (MODEL == KGE_ROTATE) {
+                // RotatE on packed fp32 (fma.rn.f32x2 / FFMA2: two coordinates per instruction): v = q - c,
+                // |v|, direction v / |v| left in c for the accumulation below.  rsqrt(max(n2, tiny)) gives
+                // direction 0 and norm 0 at v = 0 (torch: d|v|/dv = 0 there) without a select.
+                const float2 neg1 = make_float2(-1.f, -1.f);
+                float2 part2 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < CH; ++j) {
+                    const float4 q0 = myq[(0 * CH + j) * 32 + lane];
+                    const float4 q1 = myq[(1 * CH + j) * 32 + lane];
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const float2 qr = h2 ? make_float2(q0.z, q0.w) : make_float2(q0.x, q0.y);
+                        const float2 qi = h2 ? make_float2(q1.z, q1.w) : make_float2(q1.x, q1.y);
+                        const float2 cr = make_float2(c[0][j][2 * h2], c[0][j][2 * h2 + 1]);
+                        const float2 ci = make_float2(c[1][j][2 * h2], c[1][j][2 * h2 + 1]);
+                        const float2 vr = __ffma2_rn(cr, neg1, qr), vi = __ffma2_rn(ci, neg1, qi);
+                        const float2 n2 = __ffma2_rn(vr, vr, __fmul2_rn(vi, vi));
+                        const float2 rs = make_float2(fast_rsqrt(fmaxf(n2.x, 1e-37f)), fast_rsqrt(fmaxf(n2.y, 1e-37f)));
+                        const float2 dr = __fmul2_rn(vr, rs), di = __fmul2_rn(vi, rs);
+                        part2 = __ffma2_rn(n2, rs, part2);
+                        c[0][j][2 * h2] = dr.x; c[0][j][2 * h2 + 1] = dr.y;
+                        c[1][j][2 * h2] = di.x; c[1][j][2 * h2 + 1] = di.y;
+                    }
+                }
+                part = part2.x + part2.y;
+            } else
 #pragma unroll
             for (int j = 0; j < CH; ++j) {
                 const float4 q0 = myq[(0 * CH + j) * 32 + lane];
@@ -656,6 +689,20 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
                 wgt *= expf(a - m_run);
             }
             if (MODEL == KGE_PROTATE) g_run = fmaf(wgt, tot, g_run);
+            if constexpr (MODEL == KGE_ROTATE) {
+                const float2 nw = make_float2(-wgt, -wgt);  // ds/dq = -direction
+#pragma unroll
+                for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int h2 = 0; h2 < 2; ++h2) {
+                            const float2 a2 = __ffma2_rn(make_float2(c[pl][j][2 * h2], c[pl][j][2 * h2 + 1]), nw,
+                                                         make_float2(acc[pl][j][2 * h2], acc[pl][j][2 * h2 + 1]));
+                            acc[pl][j][2 * h2] = a2.x;
+                            acc[pl][j][2 * h2 + 1] = a2.y;
+                        }
+            } else
 #pragma unroll
             for (int j = 0; j < CH; ++j)
 #pragma unroll
@@ -979,6 +1026,10 @@ static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
 }
 
 size_t fused_step_workspace_bytes(const Params& P, int64_t B, int64_t N) { return fused_carve(P, B, N, nullptr).total; }
+size_t train_sweep_workspace_bytes(const Params& P, int64_t B, int64_t N) {
+    const size_t qdim = (size_t)model_planes(P.model) * P.H;
+    return fz_align((size_t)B * f1w_parts(N) * qdim * sizeof(float)) + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)) + 512;
+}
 
 bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, int64_t N, const void* ent,
                            const void* rel) {
@@ -1065,7 +1116,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
                     lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
                     fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
-        if (fc.phase == 0 && f1w_applies(P)) {
+        if (fc.phase != 2 && ws.PA != nullptr && f1w_applies(P)) {
             if constexpr (MODEL != KGE_INTERHT) {
                 // split sweep: stage Q | one warp per candidate row | merge + positive score + chain rule
                 A.part = 1;
@@ -1189,8 +1240,16 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
 cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
                                const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
-                               cudaStream_t st) {
-    FusedWs ws{};  // the sweep alone needs no workspace
+                               void* wsp, size_t ws_bytes, cudaStream_t st) {
+    // the sweep alone needs a workspace only for the split (warp-per-row) variant: per-item partials + item counter
+    FusedWs ws{};
+    if (wsp != nullptr && ws_bytes >= train_sweep_workspace_bytes(P, B, N)) {
+        char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(wsp) + 255) & ~(uintptr_t)255);
+        const size_t qdim = (size_t)model_planes(P.model) * P.H;
+        ws.PA = (float*)base;
+        ws.PM = (float*)(base + fz_align((size_t)B * f1w_parts(N) * qdim * sizeof(float)));
+        ws.item_counter = (int*)((char*)ws.PM + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)));
+    }
     FusedCall fc{1, pos, neg, w, B, wsum, B_total, nullptr, nullptr, 0, 0, 0, o.S, o.Q, o.GH, o.GT, o.GR, o.GM, o.stats, o.terms};
     kge_adam_opts ao{0.f, 0.9f, 0.999f, 1e-8f, 1, 0};
     return fused_dispatch(P, mode, const_cast<float*>(ent), const_cast<float*>(rel), const_cast<float*>(modulus), nullptr,

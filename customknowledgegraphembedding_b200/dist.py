@@ -117,11 +117,21 @@ class DataParallelStep:
         m = self.model
         B, N = neg.shape
         bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        sws = self._sweep_ws(m._desc(), B, N, pos.device)
         with torch.cuda.device(pos.device):
             _lib.check(_lib.load().kge_train_sweep(
                 C.byref(m._desc()), ops.mode_id(mode), ops._ptr(m.entity_embedding), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(pos), ops._ptr(neg), ops._ptr(w), B, N, C.byref(loss_opts),
-                ops._ptr(wsum), B_total, C.byref(bufs), ops._stream()), "kge_train_sweep")
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), ops._stream()), "kge_train_sweep")
+
+    def _sweep_ws(self, desc, B, N, dev):
+        """Workspace of the split (warp-per-row) sweep: per-item partial dL/dq + item counter."""
+        need = ops.workspace_bytes(_lib.WS_TRAIN_SWEEP, desc, B, N)
+        ws = getattr(self, "_sws", None)
+        if ws is None or ws.numel() < need or ws.device != dev:
+            ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            self._sws = ws
+        return ws
 
     def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out):
         m, opt = self.model, self.optimizer
@@ -378,11 +388,12 @@ class RowShardedStep(DataParallelStep):
         desc = m._desc()
         desc.nentity = compact.shape[0]
         bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        sws = self._sweep_ws(desc, B, N, compact.device)
         with torch.cuda.device(compact.device):
             _lib.check(_lib.load().kge_train_sweep(
                 C.byref(desc), ops.mode_id(mode), ops._ptr(compact), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(cpos), ops._ptr(cneg), ops._ptr(w), B, N, C.byref(loss_opts),
-                ops._ptr(wsum), B_total, C.byref(bufs), ops._stream()), "kge_train_sweep")
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), ops._stream()), "kge_train_sweep")
 
     # ---- 4: owners gather gradients and apply Adam on their shard ---------------------------------------------
     def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out):

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 1
+#define KGE_B200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -262,7 +262,8 @@ typedef struct {
 KGE_API int kge_train_sweep(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
                             const float *modulus, const int64_t *positive, const int64_t *negative,
                             const float *subsampling_weight, int64_t B, int64_t N, const kge_loss_opts *loss_opts,
-                            const float *wsum, int64_t B_total, const kge_step_buffers *out, void *stream);
+                            const float *wsum, int64_t B_total, const kge_step_buffers *out, void *ws, size_t ws_bytes,
+                            void *stream);
 
 KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
                             float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
@@ -305,7 +306,8 @@ typedef enum {
     KGE_WS_EVAL = 2,
     KGE_WS_TRAIN_STEP = 3,
     KGE_WS_TRAIN_STEP_HOST = 4,
-    KGE_WS_TRAIN_APPLY = 5 /* kge_train_apply: pass B_all as B */
+    KGE_WS_TRAIN_APPLY = 5, /* kge_train_apply: pass B_all as B */
+    KGE_WS_TRAIN_SWEEP = 6  /* kge_train_sweep: per-item partials of the split sweep (ws may be NULL: row-group sweep) */
 } kge_ws_kind;
 
 /* Bytes of workspace the call of that kind needs for (desc, B, N) -- for KGE_WS_EVAL pass Q as B and the

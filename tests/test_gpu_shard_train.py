@@ -80,7 +80,7 @@ def test_emulated_ranks_equal_plain_step(name, world):
         gathered = {k: torch.cat(v) for k, v in gathered.items()}
         losses = []
         for r, st in enumerate(steps):
-            st._gathered = gathered
+            st._gathered = {k: v.clone() for k, v in gathered.items()}  # the apply turns S into dL/ds in place
             m, opt = st.model, st.optimizer
             for p in (m.entity_embedding, m.relation_embedding) + ((m.modulus,) if name == "pRotatE" else ()):
                 m._adam_state(opt, p)["step"] += 1
