@@ -267,6 +267,7 @@ def run_ours(a):
                 last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
     ms_e2e = timed(e2e_steps)
     # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
+    smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
     ev = eval_bench(model, w, dev, timed, rank, world)
     ev_gemm = eval_gemm_bench(dev, timed, world)
     ev_10m = eval_10m_bench(dev, timed, world) if not a.no_eval10m else {"skipped": "--no-eval10m"}
@@ -313,6 +314,7 @@ def run_ours(a):
                               "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12}},
         "stages_ms_per_step": {k: v[0] / K for k, v in stages.items()},
         "profiled_region_ms_per_step": ms_prof / K,
+        "gpu_sampler": smp,
         "eval": ev,
         "eval_gemm": ev_gemm,
         "eval_10m": ev_10m,
@@ -377,6 +379,38 @@ def eval_bench(model, w, dev, timed, rank, world=1):
             "e2e": {"value": 2 * nq / (ms_api * 1e-3), "unit": "queries/s", "ms": ms_api,
                     "note": "KGEModel.test_step from Python triple lists: CSR filter build on host, H2D, D2H of ranks"},
             "mrr_random_init": metrics.get("MRR")}
+
+
+def sampler_bench(model, opt, group, w, dev, timed, K):
+    """the batch produced on the GPU (kge_sample_negatives + gathers) instead of copied from the host:
+    sampler alone, and the train step fed by it.  272,115 synthetic training triples (FB15k-237's train size)."""
+    import numpy as np
+    import torch
+    from customknowledgegraphembedding_b200.sampler import TrainTripleIndex, BidirectionalGpuIterator
+    rng = np.random.RandomState(21)
+    T = 272115
+    triples = np.stack([rng.randint(0, w["nentity"], T), rng.randint(0, w["nrelation"], T), rng.randint(0, w["nentity"], T)], 1)
+    idx = TrainTripleIndex(triples, w["nentity"], w["nrelation"], device=dev)
+    it = BidirectionalGpuIterator(idx, w["negatives"], w["batch"], seed=3)
+    for _ in range(3):
+        next(it)
+
+    def only_sampler():
+        for _ in range(K):
+            next(it)
+    ms_s = timed(only_sampler)
+
+    def fed_steps():
+        for _ in range(K):
+            p, ng, sw, m = next(it)
+            model._fused_step(opt, group, p, ng, sw, m, True, w["adversarial_temperature"], False, 0.0)
+    fed_steps()
+    ms_t = timed(fed_steps)
+    units = w["batch"] * w["negatives"]
+    return {"sampler_only": {"value": units * K / (ms_s * 1e-3), "unit": "negatives/s", "ms_per_batch": ms_s / K},
+            "train_fed_by_gpu_sampler": {"value": units * K / (ms_t * 1e-3), "unit": "triples*neg/s", "ms_per_step": ms_t / K,
+                                         "h2d_bytes_per_step": 0},
+            "train_triples": T}
 
 
 def eval_10m_bench(dev, timed, world=1, nq=256):

@@ -241,6 +241,19 @@ int kge_eval_rank_shard(const kge_model_desc* desc, int mode, const float* entit
                           ws_bytes, stream);
 }
 
+int kge_sample_negatives(const int64_t* positive, int64_t B, int64_t N, int mode, int64_t nentity,
+                         const int64_t* true_sorted, int64_t ntrue, uint64_t seed, uint64_t first_index, uint32_t step,
+                         int64_t* negative, void* stream) {
+    if (mode != KGE_MODE_HEAD_BATCH && mode != KGE_MODE_TAIL_BATCH)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "Training batch mode %d not supported", mode);
+    if (B < 0 || N < 0 || nentity <= 0 || ntrue < 0) return fail(KGE_ERR_INVALID_ARGUMENT, "bad sizes");
+    if (B == 0 || N == 0) return KGE_OK;
+    if (!positive || !negative || (ntrue > 0 && !true_sorted)) return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    cudaError_t e = launch_sample_negatives(positive, B, N, mode == KGE_MODE_HEAD_BATCH, nentity, true_sorted, ntrue, seed,
+                                            first_index, step, negative, (cudaStream_t)stream);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_sample_negatives");
+}
+
 int kge_eval_set_tensor_path(int on) {
     eval_set_tensor_path(on);
     return KGE_OK;

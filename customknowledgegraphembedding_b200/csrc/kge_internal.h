@@ -78,4 +78,9 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
                                  float* true_score, unsigned long long* n_greater, unsigned long long* n_equal,
                                  int accumulate, void* ws, size_t ws_bytes, cudaStream_t st);
 
+// N1 (kge_sampler.cu)
+cudaError_t launch_sample_negatives(const int64_t* positive, int64_t B, int64_t N, int head, int64_t E,
+                                    const int64_t* true_sorted, int64_t ntrue, uint64_t seed, uint64_t first_index,
+                                    uint32_t step, int64_t* negative, cudaStream_t st);
+
 }  // namespace kge

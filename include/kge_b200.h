@@ -290,6 +290,20 @@ KGE_API int kge_train_apply_shard(const kge_model_desc *desc, int mode, float *e
                                   float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
 
 /*
+ * N1  on-GPU negative sampler.  Replaces TrainDataset.__getitem__ of the PyTorch codes (U11; TF twin
+ * compress_data/main.py:64-90): for every positive (h, r, t) draw N corrupted heads (HEAD_BATCH) or tails
+ * (TAIL_BATCH) uniformly among the entities that do not form a known training triple.
+ *   true_sorted [ntrue]: sorted int64 composites (r * nentity + fixed) * nentity + candidate of the training triples,
+ *     fixed = tail and candidate = head for HEAD_BATCH, fixed = head and candidate = tail for TAIL_BATCH.
+ *   (seed, step, first_index + b, slot) fully determine a draw (Philox4x32-10): first_index is the position of
+ *     positive[0] in the caller's sample stream, so a batch does not depend on how it is split over ranks.
+ *   negative [B,N] int64 (device, overwritten).
+ */
+KGE_API int kge_sample_negatives(const int64_t *positive, int64_t B, int64_t N, int mode, int64_t nentity,
+                                 const int64_t *true_sorted, int64_t ntrue, uint64_t seed, uint64_t first_index,
+                                 uint32_t step, int64_t *negative, void *stream);
+
+/*
  * Measurement hooks (bench.py): when enabled, kge_train_step* brackets each of its stages with CUDA
  * events on the caller's stream.  kge_profile_read synchronises those events and returns, per stage, the
  * summed device time in ms and the number of kernel launches since the last reset.  Stage names:

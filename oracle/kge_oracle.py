@@ -499,3 +499,97 @@ def to_double(model: OracleKGEModel) -> OracleKGEModel:
         if hasattr(model, "modulus"):
             twin.modulus.copy_(model.modulus.double())
     return twin
+
+
+# --------------------------------------------------------------------------------------------------
+# U11: the producer of the train batch -- TrainDataset / BidirectionalOneShotIterator of the PyTorch codes
+# (absent submodule; SURVEY 8(a) U11 -- restated from the published algorithm; the TF twin builds the same
+# generators at /root/reference/compress_data/main.py:64-90 with mode 0 = head-batch, 1 = tail-batch).
+# --------------------------------------------------------------------------------------------------
+def count_frequency(triples, start: int = 4):
+    """Frequency of the partial triples (head, relation) and (tail, -relation-1), counts start at `start`."""
+    count = {}
+    for head, relation, tail in triples:
+        count[(head, relation)] = count.get((head, relation), start - 1) + 1
+        count[(tail, -relation - 1)] = count.get((tail, -relation - 1), start - 1) + 1
+    return count
+
+
+def get_true_head_and_tail(triples):
+    """true_head[(relation, tail)] / true_tail[(head, relation)] as unique numpy arrays (order of np.array(set))."""
+    true_head, true_tail = {}, {}
+    for head, relation, tail in triples:
+        true_tail.setdefault((head, relation), []).append(tail)
+        true_head.setdefault((relation, tail), []).append(head)
+    true_head = {k: np.array(list(set(v))) for k, v in true_head.items()}
+    true_tail = {k: np.array(list(set(v))) for k, v in true_tail.items()}
+    return true_head, true_tail
+
+
+def subsampling_weight_of(triple, count):
+    head, relation, tail = triple
+    w = count[(head, relation)] + count[(tail, -relation - 1)]
+    return torch.sqrt(1 / torch.Tensor([w]))  # fp32: 1/w rounded, then sqrt
+
+
+def train_dataset_item(triple, mode: str, nentity: int, negative_sample_size: int, count, true_head, true_tail,
+                       rng: "np.random.RandomState"):
+    """One `TrainDataset.__getitem__`: draw 2N uniform ids at a time, drop the true heads / tails (np.in1d),
+    until N negatives are collected.  -> (positive [3] i64, negative [N] i64, weight [1] f32, mode)."""
+    head, relation, tail = triple
+    weight = subsampling_weight_of(triple, count)
+    negative_sample_list, size = [], 0
+    while size < negative_sample_size:
+        negative_sample = rng.randint(nentity, size=negative_sample_size * 2)
+        if mode == "head-batch":
+            mask = np.in1d(negative_sample, true_head[(relation, tail)], assume_unique=True, invert=True)
+        elif mode == "tail-batch":
+            mask = np.in1d(negative_sample, true_tail[(head, relation)], assume_unique=True, invert=True)
+        else:
+            raise ValueError("Training batch mode %s not supported" % mode)
+        negative_sample = negative_sample[mask]
+        negative_sample_list.append(negative_sample)
+        size += negative_sample.size
+    negative_sample = np.concatenate(negative_sample_list)[:negative_sample_size]
+    return torch.LongTensor(triple), torch.LongTensor(negative_sample), weight, mode
+
+
+# --------------------------------------------------------------------------------------------------
+# Checker for the on-GPU sampler (csrc/kge_sampler.cu): Philox4x32-10 (Salmon et al., SC'11; the known-answer
+# vectors of Random123's kat_vectors are checked in tests/test_oracle_golden.py) and the kernel's draw scheme.
+# --------------------------------------------------------------------------------------------------
+def philox4x32_10(counter, key):
+    """counter: 4 uint32, key: 2 uint32 -> 4 uint32 (python ints)."""
+    M0, M1, W0, W1, MASK = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85, 0xFFFFFFFF
+    c0, c1, c2, c3 = [int(x) & MASK for x in counter]
+    k0, k1 = [int(x) & MASK for x in key]
+    for _ in range(10):
+        p0, p1 = M0 * c0, M1 * c2
+        c0, c1, c2, c3 = (p1 >> 32) ^ c1 ^ k0, p1 & MASK, (p0 >> 32) ^ c3 ^ k1, p0 & MASK
+        k0, k1 = (k0 + W0) & MASK, (k1 + W1) & MASK
+    return c0, c1, c2, c3
+
+
+def sample_negatives_reference(positive, negative_sample_size, mode, nentity, train_triples, seed, step, first_index=0):
+    """Pure-Python restatement of kge_sample_negatives: same counters, same acceptance rule -> identical ids."""
+    true = set((int(h), int(r), int(t)) for h, r, t in train_triples)
+    E = int(nentity)
+    out = np.zeros((len(positive), negative_sample_size), dtype=np.int64)
+    for b, (h, r, t) in enumerate(np.asarray(positive).tolist()):
+        gidx = first_index + b
+        for slot in range(negative_sample_size):
+            e, done = 0, False
+            for attempt in range(256):
+                p = philox4x32_10((gidx & 0xFFFFFFFF, slot, attempt, step & 0xFFFFFFFF),
+                                  (seed & 0xFFFFFFFF, ((seed >> 32) ^ (gidx >> 32)) & 0xFFFFFFFF))
+                for half in range(2):
+                    x = (p[2 * half + 1] << 32) | p[2 * half]
+                    e = (x * E) >> 64
+                    known = ((e, r, t) in true) if mode == "head-batch" else ((h, r, e) in true)
+                    if not known:
+                        done = True
+                        break
+                if done:
+                    break
+            out[b, slot] = e
+    return out
