@@ -70,6 +70,11 @@ PROTOTYPES = {
     "kge_eval_rank_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P,
                                       C.c_int, _P, _SZ, _P]),
     "kge_sample_negatives": (C.c_int, [_P, _I64, _I64, C.c_int, _I64, _P, _I64, C.c_uint64, C.c_uint64, C.c_uint32, _P, _P]),
+    "kge_crc32c": (C.c_uint32, [_P, _SZ]),
+    "kge_tfrecord_next": (C.c_int, [_P, _SZ, _SZ, C.POINTER(_SZ), C.POINTER(_SZ), C.POINTER(_SZ), C.c_int]),
+    "kge_tfrecord_frame": (_SZ, [_P, _SZ, _P]),
+    "kge_record_parse_example": (C.c_int, [_P, _SZ, _P, _SZ, _P, _SZ, _P, _SZ, _P, _SZ, C.POINTER(_SZ)]),
+    "kge_record_build_example": (_SZ, [_P, _SZ, _P, _SZ, _P, _SZ, _P, _SZ, _P, _SZ]),
     "kge_eval_set_tensor_path": (C.c_int, [C.c_int]),
     "kge_train_set_sweep_variant": (C.c_int, [C.c_int]),
     "kge_train_step": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,

@@ -304,6 +304,30 @@ KGE_API int kge_sample_negatives(const int64_t *positive, int64_t B, int64_t N, 
                                  uint32_t step, int64_t *negative, void *stream);
 
 /*
+ * N2  the batch wire format without TensorFlow (host code).  The reference stores one tf.train.Example per batch in
+ * TFRecord shards: writer compress_data/utils.py:35-42 + compress_data/main.py:97-125, reader
+ * tensorflow_codes/run.py:40-66 (tf.data.TFRecordDataset + tf.io.parse_single_example).
+ *   kge_tfrecord_next        one frame of a shard held in memory: 0 = ok, 1 = end of file, negative = error
+ *                            (truncated, or CRC-32C mismatch when verify_crc != 0)
+ *   kge_tfrecord_frame       data -> header | data | footer (out needs data_len + 16 bytes); returns bytes written
+ *   kge_record_parse_example serialized Example -> positive_sample, negative_sample (int64), subsampling_weight
+ *                            (float), mode (int64); counts[4] = values found per feature; any map order, packed or
+ *                            unpacked lists; a feature larger than its buffer is an error
+ *   kge_record_build_example the inverse (create_example): map in sorted key order, packed lists; out == NULL
+ *                            returns the size; 0 when cap is too small
+ */
+KGE_API uint32_t kge_crc32c(const void *data, size_t n);
+KGE_API int kge_tfrecord_next(const uint8_t *file, size_t len, size_t offset, size_t *data_offset, size_t *data_len,
+                              size_t *next_offset, int verify_crc);
+KGE_API size_t kge_tfrecord_frame(const uint8_t *data, size_t data_len, uint8_t *out);
+KGE_API int kge_record_parse_example(const uint8_t *buf, size_t len, int64_t *positive, size_t cap_positive,
+                                     int64_t *negative, size_t cap_negative, float *weight, size_t cap_weight,
+                                     int64_t *mode, size_t cap_mode, size_t *counts);
+KGE_API size_t kge_record_build_example(const int64_t *positive, size_t n_positive, const int64_t *negative,
+                                        size_t n_negative, const float *weight, size_t n_weight, const int64_t *mode,
+                                        size_t n_mode, uint8_t *out, size_t cap);
+
+/*
  * Measurement hooks (bench.py): when enabled, kge_train_step* brackets each of its stages with CUDA
  * events on the caller's stream.  kge_profile_read synchronises those events and returns, per stage, the
  * summed device time in ms and the number of kernel launches since the last reset.  Stage names:
