@@ -319,9 +319,20 @@ class KGEModel(nn.Module):
         head-batch then tail-batch queries (same query order and metric arithmetic as upstream).
         ``rank_fn(queries, mode, filter_indptr, filter_idx)`` replaces the local K5 call (dist.test_step)."""
         model.eval()
-        if getattr(args, "countries", False):
-            raise NotImplementedError("--countries AUC-PR evaluation is outside the B200 hot path (SURVEY 8(f) N4)")
         dev = model.entity_embedding.device
+        if getattr(args, "countries", False):
+            # Countries S* datasets are evaluated with AUC-PR, which is calculated using scikit-learn (upstream branch):
+            # every test triple is scored against the regions as candidate tails -- K1 in 'single' mode.
+            from sklearn.metrics import average_precision_score
+            sample, y_true = [], []
+            for head, relation, tail in test_triples:
+                for candidate_region in args.regions:
+                    y_true.append(1 if candidate_region == tail else 0)
+                    sample.append((head, relation, candidate_region))
+            sample = torch.LongTensor(sample).to(dev)
+            with torch.no_grad():
+                y_score = model(sample).squeeze(1).cpu().numpy()
+            return {"auc_pr": average_precision_score(np.array(y_true), y_score)}
         if dev.type != "cuda" and rank_fn is None:
             raise RuntimeError("KGEModel.test_step: model is on %s; move it to a CUDA device (no CPU fallback)" % dev)
         if rank_fn is None:

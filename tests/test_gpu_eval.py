@@ -144,3 +144,22 @@ def test_exact_ties_are_reported():
     q = torch.tensor([[1, 0, 2], [3, 1, 4]], dtype=torch.int64)
     _, ng, ne = m.rank_queries(q, "head-batch")
     assert ng.tolist() == [0, 0] and ne.tolist() == [E - 1, E - 1]
+
+
+def test_countries_auc_pr():
+    """--countries branch of test_step: AUC-PR over the region candidates (scikit-learn), scores from K1."""
+    from sklearn.metrics import average_precision_score
+    E, R, H = 60, 2, 16
+    om, gm = _pair("RotatE", E, R, H, seed=6)
+    regions = [3, 11, 27, 40, 59]
+    rng = np.random.RandomState(1)
+    test = [(int(rng.randint(0, E)), int(rng.randint(0, R)), regions[int(rng.randint(0, 5))]) for _ in range(24)]
+    args = ko.Args(nentity=E, nrelation=R)
+    args.countries, args.regions = True, regions
+    got = type(gm).test_step(gm, test, test, args)
+    sample = torch.LongTensor([(h, r, c) for h, r, t in test for c in regions])
+    y_true = np.array([1 if c == t else 0 for h, r, t in test for c in regions])
+    with torch.no_grad():
+        y_score = om(sample).squeeze(1).numpy()
+    want = average_precision_score(y_true, y_score)
+    assert set(got) == {"auc_pr"} and abs(got["auc_pr"] - want) < 1e-6
