@@ -267,10 +267,14 @@ def run_ours(a):
                 last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
     ms_e2e = timed(e2e_steps)
     # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
-    smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
-    ev = eval_bench(model, w, dev, timed, rank, world)
-    ev_gemm = eval_gemm_bench(dev, timed, world)
-    ev_10m = eval_10m_bench(dev, timed, world) if not a.no_eval10m else {"skipped": "--no-eval10m"}
+    if a.train_only:
+        smp = ev = ev_gemm = None
+        ev_10m = {"skipped": "--train-only"}
+    else:
+        smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
+        ev = eval_bench(model, w, dev, timed, rank, world)
+        ev_gemm = eval_gemm_bench(dev, timed, world)
+        ev_10m = eval_10m_bench(dev, timed, world) if not a.no_eval10m else {"skipped": "--no-eval10m"}
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -527,6 +531,7 @@ def main():
     ap.add_argument("--deterministic", action="store_true", help="use the fixed-order backward variant")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eval10m", action="store_true", help="skip the 10M-entity sharded eval section (80 GB table)")
+    ap.add_argument("--train-only", action="store_true", help="tuning loops: only the headline train step sections")
     a = ap.parse_args()
     if a.impl == "reference":
         if a.steps > 8:

@@ -16,11 +16,13 @@ static const char* const kStageNames[ST_COUNT] = {
     "l3_reg", "adam(entity)", "adam(relation+modulus)",
     "fused_sweep(scores+loss+dL/dq)", "buckets(scan+fill+sort)", "dscore+loss_final", "entity_gather+adam",
     "relation_gather+adam"};
-// kernels launched per stage (memsets are not kernels)
-static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1, 1, 5, 2, 1, 2};
+// kernels launched per stage (memsets are not kernels); a scope whose count depends on the path taken overrides it
+// through ProfScope::launches
+static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1, 1, 5, 2, 1, 1};
 
 struct ProfRec {
     int stage;
+    int launches;
     cudaEvent_t a, b;
 };
 extern bool g_prof_on;
@@ -47,10 +49,12 @@ struct ProfScope {
     ProfScope(int stage, cudaStream_t s) : st(s), on(g_prof_on) {
         if (!on) return;
         rec.stage = stage;
+        rec.launches = kStageLaunches[stage];
         rec.a = prof_event();
         rec.b = prof_event();
         cudaEventRecord(rec.a, st);
     }
+    void launches(int n) { rec.launches = n; }
     ~ProfScope() {
         if (!on) return;
         cudaEventRecord(rec.b, st);

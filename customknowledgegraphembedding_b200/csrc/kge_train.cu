@@ -201,7 +201,7 @@ int kge_profile_read(float* ms_sum, int64_t* launches, int reset) {
         float ms = 0.f;
         cudaEventElapsedTime(&ms, r.a, r.b);
         g_prof_ms[r.stage] += ms;
-        g_prof_launches[r.stage] += kStageLaunches[r.stage];
+        g_prof_launches[r.stage] += r.launches;
         g_prof_pool.push_back(r.a);
         g_prof_pool.push_back(r.b);
     }
