@@ -28,6 +28,7 @@
 #include "kge_coord.cuh"
 #include "kge_internal.h"
 #include "kge_prof.h"
+#include "kge_ptx.cuh"
 #include "kge_train.h"
 
 namespace kge {
@@ -566,17 +567,29 @@ struct RowsArgs {
     float alpha;
 };
 
-template <int MODEL, int CH, bool HEAD>
+// Candidate rows reach the warp through a warp-private ring of R shared-memory slots filled by 1-D bulk copies (TMA,
+// one instruction per 8 KB row, completion on an mbarrier): the copy of row n + R starts as soon as row n has been
+// lifted into registers, so it overlaps the reduction and the accumulation pass of rows n .. n + R - 1.
+template <int MODEL, int CH, bool HEAD, int R>
 __global__ void __launch_bounds__(128)
 train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
-    extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32]
+    extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32] | [warp][R][slot_bytes] | [warp][R] mbarriers
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float4* myq = f1w_q + warp * (QP * CH * 32);
+    const uint32_t row_bytes = (uint32_t)P.De * 4u, slot_bytes = (row_bytes + 127u) & ~127u;
+    const uint32_t ring_s = smem_u32(f1w_q + 4 * (QP * CH * 32)) + warp * R * slot_bytes;
+    const uint32_t bars_s = smem_u32(f1w_q + 4 * (QP * CH * 32)) + 4 * R * slot_bytes + warp * R * 8;
+    if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) mbar_init(bars_s + 8 * r, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    uint32_t issued = 0, consumed = 0;  // rows of this warp so far: slot = count % R, parity = (count / R) & 1
     const int H = P.H, N = A.N;
     if (MODEL == KGE_PROTATE) kc.modulus = __ldg(A.modulus);
     const int total = A.B * A.parts;
-    const int row_lines = (P.De * 4 + 127) / 128;
     const int jfull = H / 128;  // chunks whose 32 lanes all hold live coordinates
     const float cn[2] = {0.f, 0.f};
 
@@ -609,28 +622,39 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
                 for (int i = 0; i < 4; ++i) acc[pl][j][i] = 0.f;
         float m_run = -INFINITY, g_run = 0.f;
 
-        long long id = (n0 < n1) ? __ldg(A.neg + b * N + n0) : 0;
+        auto issue_row = [&](long long rid) {  // lane 0 only
+            const uint32_t slot = issued % R, bar = bars_s + 8 * slot;
+            mbar_arrive_expect_tx(bar, row_bytes);
+            bulk_g2s(ring_s + slot * slot_bytes, A.ent + rid * (long long)P.De, row_bytes, bar);
+        };
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (n0 + r < n1) {
+                const long long rid = __ldg(A.neg + b * N + n0 + r);
+                if (lane == 0) issue_row(rid);
+                ++issued;
+            }
         for (int n = n0; n < n1; ++n) {
-            const float* row = A.ent + id * (long long)P.De;
+            // id of the row that will take this slot next; its latency hides behind the wait below
+            const long long id_ahead = (n + R < n1) ? __ldg(A.neg + b * N + n + R) : 0;
+            const uint32_t slot = consumed % R;
+            mbar_wait(bars_s + 8 * slot, (consumed / R) & 1u);
+            ++consumed;
+            const uint32_t row_s = ring_s + slot * slot_bytes + 16u * lane;
             float c[CP][CH][4];
 #pragma unroll
             for (int pl = 0; pl < CP; ++pl)
 #pragma unroll
                 for (int j = 0; j < CH; ++j) {
                     const int k0 = 4 * (lane + 32 * j);
-                    float4 v;
-                    if (j < jfull) {  // warp-uniform: every lane of this chunk is inside the row
-                        v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
-                    } else {
-                        v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(row + pl * H + k0));
-                    }
-                    c[pl][j][0] = v.x; c[pl][j][1] = v.y; c[pl][j][2] = v.z; c[pl][j][3] = v.w;
+                    c[pl][j][0] = c[pl][j][1] = c[pl][j][2] = c[pl][j][3] = 0.f;
+                    if (j < jfull || k0 < H)  // j < jfull is warp-uniform: every lane of the chunk is inside the row
+                        lds128(c[pl][j], row_s + (uint32_t)(pl * H + 128 * j) * 4u);
                 }
-            if (n + 1 < n1) {  // next id, and its row on the way into L2
-                id = __ldg(A.neg + b * N + n + 1);
-                const char* nxt = reinterpret_cast<const char*>(A.ent + id * (long long)P.De);
-                for (int l = lane; l < row_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + 128 * l));
+            __syncwarp();  // every lane has lifted its part of the slot
+            if (n + R < n1) {
+                if (lane == 0) issue_row(id_ahead);
+                ++issued;
             }
             float part = 0.f;
             if constexpr (MODEL == KGE_ROTATE) {
@@ -838,9 +862,6 @@ constexpr int kRing = 4;
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void lds128(float (&x)[4], uint32_t smem_src) {
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "r"(smem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -1202,20 +1223,26 @@ struct FusedCall {
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
 };
 
-template <int MODEL, int CHW, bool HEAD>
-static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc, const RowsArgs& R, cudaStream_t st) {
-    constexpr size_t smem = (size_t)4 * model_planes(MODEL) * CHW * 32 * sizeof(float4);
+template <int MODEL, int CHW, bool HEAD, int R>
+static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc, const RowsArgs& A, cudaStream_t st) {
+    auto kernel = train_sweep_rows_kernel<MODEL, CHW, HEAD, R>;
+    // per warp: the staged q planes, R row slots (128-byte aligned) and their mbarriers
+    const size_t slot_bytes = ((size_t)P.De * 4 + 127) & ~(size_t)127;
+    const size_t smem = (size_t)4 * model_planes(MODEL) * CHW * 32 * sizeof(float4) + 4 * R * slot_bytes + 4 * R * 8;
+    static size_t grid_for = 0;
     static int grid = 0;  // persistent: every CTA the device can hold
-    if (grid == 0) {
-        if (smem > 48 * 1024)
-            cudaFuncSetAttribute(train_sweep_rows_kernel<MODEL, CHW, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (grid_for != smem) {
+        cudaError_t e;
+        if (smem > 40 * 1024 &&
+            (e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+            return e;
         int per_sm = 0;
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, train_sweep_rows_kernel<MODEL, CHW, HEAD>, 128, smem);
-        if (e != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 128, smem)) != cudaSuccess) return e;
         grid = std::max(1, per_sm) * sm_count();
+        grid_for = smem;
     }
-    const int items = R.B * R.parts;
-    train_sweep_rows_kernel<MODEL, CHW, HEAD><<<std::min(grid, (items + 3) / 4), 128, smem, st>>>(P, kc, R);
+    const int items = A.B * A.parts;
+    kernel<<<std::min(grid, (items + 3) / 4), 128, smem, st>>>(P, kc, A);
     return cudaGetLastError();
 }
 
@@ -1224,9 +1251,13 @@ static cudaError_t launch_sweep_rows(const Params& P, const CoordConsts& kc, boo
     if constexpr (MODEL == KGE_INTERHT) {
         return cudaErrorInvalidValue;
     } else {
-#define KGE_ROWS(CHW)                                                                       \
-    return head ? launch_sweep_rows_inst<MODEL, CHW, true>(P, kc, R, st)                    \
-                : launch_sweep_rows_inst<MODEL, CHW, false>(P, kc, R, st)
+        static const int ring_env = getenv("KGE_SWEEP_RING") ? atoi(getenv("KGE_SWEEP_RING")) : 1;
+#define KGE_ROWS(CHW)                                                                                                   \
+    if (ring_env == 2)                                                                                                  \
+        return head ? launch_sweep_rows_inst<MODEL, CHW, true, 2>(P, kc, R, st)                                         \
+                    : launch_sweep_rows_inst<MODEL, CHW, false, 2>(P, kc, R, st);                                       \
+    return head ? launch_sweep_rows_inst<MODEL, CHW, true, 1>(P, kc, R, st)                                             \
+                : launch_sweep_rows_inst<MODEL, CHW, false, 1>(P, kc, R, st)
         if (P.H <= 256) { KGE_ROWS(2); }
         if (P.H <= 512) { KGE_ROWS(4); }
         KGE_ROWS(8);
