@@ -92,7 +92,9 @@ struct SweepArgs {
 // ------------------------------------------------------------------------------------------------
 // F1
 // ------------------------------------------------------------------------------------------------
-template <int MODEL, int CH, int RPI>
+// PART (SweepArgs.part) is a template parameter so that the staging and merge passes of the split sweep do not carry
+// the register footprint of the row-group sweep they skip.
+template <int MODEL, int CH, int RPI, int PART>
 __global__ void __launch_bounds__(256)
 train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL), RP = rel_planes_of(MODEL);
@@ -122,7 +124,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         block_reduce_vals<1>(part, red);
         coef = __ldg(A.w + b) / part[0];
     }
-    if (tid == 0 && A.counts != nullptr && A.part != 1) {  // every use of an entity row is counted for the bucket build
+    if (tid == 0 && A.counts != nullptr && PART != 1) {  // every use of an entity row is counted for the bucket build
         atomicAdd(A.counts + h, 1);
         atomicAdd(A.counts + t, 1);
     }
@@ -169,7 +171,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
             }
     }
 
-    if (A.part == 1) {  // staging pass of the split sweep: Q[b] is all F1w needs
+    if constexpr (PART == 1) {  // staging pass of the split sweep: Q[b] is all F1w needs
         if (blockIdx.x == 0 && threadIdx.x == 0) *A.item_counter = 0;
         return;
     }
@@ -192,7 +194,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
 #pragma unroll
     for (int rr = 0; rr < RPI; ++rr) cid[rr] = (rr < N) ? (int)__ldg(A.neg + b * N + rr) : 0;
 
-    const int n_sweep = (A.part == 0) ? N : 0;
+    const int n_sweep = (PART == 0) ? N : 0;
     for (int n0 = 0; n0 < n_sweep; n0 += RPI) {
         float c[RPI][CP][CH][4];
         float sg[(MODEL == KGE_INTERHT) ? RPI : 1][CH][4];
@@ -309,7 +311,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         }
     }
 
-    if (A.part == 2) {
+    if (PART == 2) {
         // ---- merge of the split sweep: scores S[b,:] and the per-item partials are in global memory --------
         float m = -INFINITY;
         if (A.adv)
@@ -571,7 +573,7 @@ struct RowsArgs {
 // one instruction per 8 KB row, completion on an mbarrier): the copy of row n + R starts as soon as row n has been
 // lifted into registers, so it overlaps the reduction and the accumulation pass of rows n .. n + R - 1.
 template <int MODEL, int CH, bool HEAD, int R>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 3)
 train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
     extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32] | [warp][R][slot_bytes] | [warp][R] mbarriers
@@ -1251,11 +1253,8 @@ static cudaError_t launch_sweep_rows(const Params& P, const CoordConsts& kc, boo
     if constexpr (MODEL == KGE_INTERHT) {
         return cudaErrorInvalidValue;
     } else {
-        static const int ring_env = getenv("KGE_SWEEP_RING") ? atoi(getenv("KGE_SWEEP_RING")) : 1;
+        // R = 1: 16 KB per warp keeps 12 warps on an SM; R = 2 (8 warps) measured slower (0.367 vs 0.311 ms)
 #define KGE_ROWS(CHW)                                                                                                   \
-    if (ring_env == 2)                                                                                                  \
-        return head ? launch_sweep_rows_inst<MODEL, CHW, true, 2>(P, kc, R, st)                                         \
-                    : launch_sweep_rows_inst<MODEL, CHW, false, 2>(P, kc, R, st);                                       \
     return head ? launch_sweep_rows_inst<MODEL, CHW, true, 1>(P, kc, R, st)                                             \
                 : launch_sweep_rows_inst<MODEL, CHW, false, 1>(P, kc, R, st)
         if (P.H <= 256) { KGE_ROWS(2); }
@@ -1320,7 +1319,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 ps.launches(3);
                 A.part = 1;
                 A.item_counter = ws.item_counter;
-                train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+                train_sweep_kernel<MODEL, CH, RPI, 1><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
                 const int parts = f1w_parts(N);
                 RowsArgs R{ent, fc.neg, fc.Q, modulus, fc.S, ws.PA, ws.PM, ws.item_counter, (int)fc.B, (int)N, parts,
                            (int)((N + parts - 1) / parts), lo.negative_adversarial_sampling, lo.adversarial_temperature};
@@ -1329,10 +1328,10 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 A.parts = parts;
                 A.PA = ws.PA;
                 A.PM = ws.PM;
-                train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+                train_sweep_kernel<MODEL, CH, RPI, 2><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
             }
         } else {
-            train_sweep_kernel<MODEL, CH, RPI><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+            train_sweep_kernel<MODEL, CH, RPI, 0><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (fc.phase == 1) return cudaSuccess;
