@@ -13,6 +13,7 @@
 //
 // Same result as the atomic variant up to float reassociation, and bit-identical run to run.
 #include "kge_internal.h"
+#include "kge_ptx.cuh"
 #include "kge_score.cuh"
 
 namespace kge {
@@ -121,6 +122,7 @@ __device__ __forceinline__ long long item_entity(int item, int mode, const int64
 
 __global__ void det_histogram_kernel(int mode, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg,
                                      long long BN, long long B, int* counts) {
+    pdl_enter();
     const long long total = BN + 2 * B;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
         atomicAdd(counts + item_entity((int)i, mode, pos, neg, BN, B), 1);
@@ -128,6 +130,7 @@ __global__ void det_histogram_kernel(int mode, const int64_t* __restrict__ pos, 
 
 // exclusive scan of counts[0..n) -> offsets[0..n], three phases, 1024 elements per block
 __global__ void __launch_bounds__(256) scan_block_kernel(const int* __restrict__ in, int* out, int* block_sums, long long n) {
+    pdl_enter();
     __shared__ int warp_tot[8];
     const long long base = (long long)blockIdx.x * kScanBlock + threadIdx.x * 4;
     int v[4];
@@ -155,6 +158,7 @@ __global__ void __launch_bounds__(256) scan_block_kernel(const int* __restrict__
 }
 
 __global__ void scan_sums_kernel(int* block_sums, int nblocks) {  // single thread block, sequential carry
+    pdl_enter();
     __shared__ int carry;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
@@ -183,6 +187,7 @@ __global__ void scan_sums_kernel(int* block_sums, int nblocks) {  // single thre
 }
 
 __global__ void scan_add_kernel(int* out, const int* __restrict__ block_sums, long long n, int* cursor) {
+    pdl_enter();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         const int v = out[i] + block_sums[i / kScanBlock];
@@ -195,6 +200,7 @@ __global__ void scan_add_kernel(int* out, const int* __restrict__ block_sums, lo
 
 __global__ void det_fill_kernel(int mode, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg,
                                 long long BN, long long B, int* cursor, int* items) {
+    pdl_enter();
     const long long total = BN + 2 * B;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int slot = atomicAdd(cursor + item_entity((int)i, mode, pos, neg, BN, B), 1);
@@ -288,8 +294,7 @@ cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, l
                              cudaStream_t st) {
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
-    det_histogram_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, counts);
-    return cudaGetLastError();
+    return launch_pdl(det_histogram_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, counts);
 }
 
 // exclusive scan of counts -> offsets (+ a copy in cursor), then scatter every use into its bucket
@@ -298,11 +303,12 @@ cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, l
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
     const int nblocks = (int)((E + kScanBlock - 1) / kScanBlock);
-    scan_block_kernel<<<nblocks, 256, 0, st>>>(counts, offsets, block_sums, E);
-    scan_sums_kernel<<<1, 1024, 0, st>>>(block_sums, nblocks);
-    scan_add_kernel<<<(unsigned)((E + 1 + 255) / 256), 256, 0, st>>>(offsets, block_sums, E, cursor);
-    det_fill_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, cursor, items);
-    return cudaGetLastError();
+    cudaError_t e;
+    if ((e = launch_pdl(scan_block_kernel, dim3(nblocks), dim3(256), 0, st, counts, offsets, block_sums, E)) != cudaSuccess) return e;
+    if ((e = launch_pdl(scan_sums_kernel, dim3(1), dim3(1024), 0, st, block_sums, nblocks)) != cudaSuccess) return e;
+    if ((e = launch_pdl(scan_add_kernel, dim3((unsigned)((E + 1 + 255) / 256)), dim3(256), 0, st, offsets, block_sums, E, cursor)) != cudaSuccess)
+        return e;
+    return launch_pdl(det_fill_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, cursor, items);
 }
 
 template <int MODEL>

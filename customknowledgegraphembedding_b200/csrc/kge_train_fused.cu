@@ -97,6 +97,7 @@ struct SweepArgs {
 template <int MODEL, int CH, int RPI, int PART>
 __global__ void __launch_bounds__(256)
 train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
+    pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL), RP = rel_planes_of(MODEL);
     __shared__ float red[4 * 32 * 2];      // block reductions: up to 8 values x 32 warps
     __shared__ float red2[2][RPI * 32];    // row-sum partials of the sweep, double-buffered by row group
@@ -575,6 +576,7 @@ struct RowsArgs {
 template <int MODEL, int CH, bool HEAD, int R>
 __global__ void __launch_bounds__(128, 3)
 train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
+    pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
     extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32] | [warp][R][slot_bytes] | [warp][R] mbarriers
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -768,6 +770,7 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
 __global__ void __launch_bounds__(256)
 bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, int* __restrict__ out,
                    int* __restrict__ out_b, long long E, int N) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -786,6 +789,7 @@ bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, 
 // F2b: S[b,n] <- dL/ds[b,n] = scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s))
 __global__ void __launch_bounds__(256)
 dscore_kernel(float* __restrict__ S, const float* __restrict__ stats, long long BN, int N, int adv, float alpha) {
+    pdl_enter();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < BN; i += (long long)gridDim.x * blockDim.x) {
         const long long b = i / N;
         const float s = S[i];
@@ -875,6 +879,7 @@ template <int MODEL, int CH, bool HEAD, int TMAX>
 __global__ void __launch_bounds__(TMAX, TMAX == 128 ? 6 : 2)
 train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ modulus, EntityArgs A, AdamScalars ad,
                          float l3) {
+    pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
     __shared__ float red[2 * 32];
     __shared__ float use_g[kUseChunk];
@@ -1067,6 +1072,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
 __global__ void __launch_bounds__(256)
 train_relation_adam_kernel(int Dr, const int64_t* __restrict__ pos, int B, const float* __restrict__ GR, float* rel,
                            float* m, float* v, AdamScalars ad, float l3, int* scratch) {
+    pdl_enter();
     // warp 0 lists the positives that use relation r, in ascending b (ballot + popc keeps the order)
     extern __shared__ int match[];  // up to B entries
     __shared__ int nmatch;
@@ -1098,6 +1104,7 @@ train_relation_adam_kernel(int Dr, const int64_t* __restrict__ pos, int B, const
 
 __global__ void __launch_bounds__(256)
 train_modulus_adam_kernel(const float* __restrict__ GM, int B, float* modulus, float* m, float* v, AdamScalars ad) {
+    pdl_enter();
     __shared__ float red[32];
     float acc = 0.f;
     for (int b = threadIdx.x; b < B; b += blockDim.x) acc += GM[b];
@@ -1113,6 +1120,7 @@ train_modulus_adam_kernel(const float* __restrict__ GM, int B, float* modulus, f
 
 // loss terms [B][2] (pos, neg) -> loss3, fixed order
 __global__ void __launch_bounds__(256) loss_final2_kernel(const float* __restrict__ terms, int B, float* loss3) {
+    pdl_enter();
     __shared__ float red[32];
     float p = 0.f, n = 0.f;
     for (int i = threadIdx.x; i < B; i += blockDim.x) {
@@ -1199,6 +1207,7 @@ bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, 
 }
 
 __global__ void fused_finalize_reg_kernel(float* small, float lambda) {
+    pdl_enter();
     const float reg = lambda * (small[4] + small[5]);
     small[3] = reg;
     small[2] += reg;
@@ -1244,8 +1253,7 @@ static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc
         grid_for = smem;
     }
     const int items = A.B * A.parts;
-    kernel<<<std::min(grid, (items + 3) / 4), 128, smem, st>>>(P, kc, A);
-    return cudaGetLastError();
+    return launch_pdl(kernel, dim3(std::min(grid, (items + 3) / 4)), dim3(128), smem, st, P, kc, A);
 }
 
 template <int MODEL>
@@ -1282,8 +1290,7 @@ static cudaError_t launch_entity_inst(const Params& P, const CoordConsts& kc, co
         resident_for = ethreads;
     }
     const int blocks = (int)std::min<long long>(A.e_hi - A.e_lo, (long long)std::max(1, resident_cached) * sm_count());
-    kernel<<<blocks, ethreads, ring_bytes, st>>>(P, kc, modulus, A, ad, l3);
-    return cudaGetLastError();
+    return launch_pdl(kernel, dim3(blocks), dim3(ethreads), ring_bytes, st, P, kc, modulus, A, ad, l3);
 }
 
 template <int MODEL, int ECH>
@@ -1310,6 +1317,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     if (fc.phase != 2) {
         ProfScope ps(ST_SWEEP, st);
         if (fc.phase == 0 && (e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
+        if (fc.phase == 0 && (e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
         SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
                     lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
                     fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
@@ -1319,7 +1327,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 ps.launches(3);
                 A.part = 1;
                 A.item_counter = ws.item_counter;
-                train_sweep_kernel<MODEL, CH, RPI, 1><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+                if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 1>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
                 const int parts = f1w_parts(N);
                 RowsArgs R{ent, fc.neg, fc.Q, modulus, fc.S, ws.PA, ws.PM, ws.item_counter, (int)fc.B, (int)N, parts,
                            (int)((N + parts - 1) / parts), lo.negative_adversarial_sampling, lo.adversarial_temperature};
@@ -1328,10 +1336,10 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 A.parts = parts;
                 A.PA = ws.PA;
                 A.PM = ws.PM;
-                train_sweep_kernel<MODEL, CH, RPI, 2><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+                if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 2>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
             }
         } else {
-            train_sweep_kernel<MODEL, CH, RPI, 0><<<(unsigned)fc.B, threads, 0, st>>>(P, kc, head, A);
+            if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (fc.phase == 1) return cudaSuccess;
@@ -1340,7 +1348,9 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     const long long BN = B * N;
     {
         ProfScope ps(ST_BUCKETS, st);
-        if ((e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
+        // (ws.small was cleared before the sweep when this call runs one: the sweep's last kernel is then followed
+        //  directly by the scan, kernel to kernel)
+        if (fc.phase == 2 && (e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
         if (fc.phase == 2) {
             if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
             if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, st)) != cudaSuccess) return e;
@@ -1349,15 +1359,15 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                                   ws.block_sums, st)) != cudaSuccess)
             return e;
         const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
-        bucket_sort_kernel<<<sb, 256, 0, st>>>(ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N);
+        if ((e = launch_pdl(bucket_sort_kernel, dim3(sb), dim3(256), 0, st, ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N)) != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     {
         ProfScope ps(ST_DSCORE, st);
         const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
-        dscore_kernel<<<db, 256, 0, st>>>(fc.S, fc.stats, BN, (int)N, lo.negative_adversarial_sampling,
-                                          lo.adversarial_temperature);
-        loss_final2_kernel<<<1, 256, 0, st>>>(fc.terms, (int)B, ws.small);
+        if ((e = launch_pdl(dscore_kernel, dim3(db), dim3(256), 0, st, fc.S, fc.stats, BN, (int)N,
+                            lo.negative_adversarial_sampling, lo.adversarial_temperature)) != cudaSuccess) return e;
+        if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(256), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     float l3 = 0.f;
@@ -1381,8 +1391,8 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     {
         // relation rows and the modulus are replicated: every rank applies the same fixed-order update
         ProfScope ps(ST_RELATION, st);
-        train_relation_adam_kernel<<<(unsigned)P.R, 256, (size_t)B * sizeof(int), st>>>(P.Dr, fc.pos_all, (int)B, fc.GR, rel,
-                                                                                         m_rel, v_rel, ad, l3, nullptr);
+        if ((e = launch_pdl(train_relation_adam_kernel, dim3((unsigned)P.R), dim3(256), (size_t)B * sizeof(int), st, P.Dr,
+                            fc.pos_all, (int)B, fc.GR, rel, m_rel, v_rel, ad, l3, nullptr)) != cudaSuccess) return e;
         if (MODEL == KGE_PROTATE) train_modulus_adam_kernel<<<1, 256, 0, st>>>(fc.GM, (int)B, modulus, m_mod, v_mod, ad);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
