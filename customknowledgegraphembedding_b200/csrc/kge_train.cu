@@ -238,8 +238,13 @@ int kge_train_step(const kge_model_desc* desc, int mode, float* entity, float* r
                            adam_v_relation, adam_m_modulus, adam_v_modulus, positive, negative, subsampling_weight, B, N, *loss_opts,
                            *adam_opts, deterministic, w, st, &small);
     if (rc) return rc;
-    cudaError_t e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
-    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    cudaError_t e;
+    if (reg1 == loss3 + 3) {  // one contiguous float[4]: a single copy
+        e = cudaMemcpyAsync(loss3, small, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    } else {
+        e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    }
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_step(copy loss)");
 }
 
@@ -289,8 +294,12 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
                                        adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
                                        *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, ws, ws_bytes, &small, st);
     if (e != cudaSuccess) return fail_cuda(e, "kge_train_apply");
-    e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
-    if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    if (reg1 == loss3 + 3) {
+        e = cudaMemcpyAsync(loss3, small, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    } else {
+        e = cudaMemcpyAsync(loss3, small, 3 * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess && reg1) e = cudaMemcpyAsync(reg1, small + 3, sizeof(float), cudaMemcpyDeviceToDevice, st);
+    }
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_apply(copy loss)");
 }
 

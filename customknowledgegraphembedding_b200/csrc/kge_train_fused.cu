@@ -801,6 +801,47 @@ dscore_kernel(float* __restrict__ S, const float* __restrict__ stats, long long 
 // ------------------------------------------------------------------------------------------------
 // F3: entity-major gradient gather fused with Adam
 // ------------------------------------------------------------------------------------------------
+// One relation row: dL/d(row) = sum of GR[b] over the positives b that use it, in ascending b; then Adam.  Called by a
+// whole CTA (any size); match / nmatch are shared-memory scratch (relation_scratch_ints(B) ints, one int).
+__host__ __device__ inline int relation_scratch_ints(int B) { return B + (B + 31) / 32; }
+__device__ __forceinline__ void relation_row_update(long long r, int Dr, const int64_t* __restrict__ pos, int B,
+                                                    const float* __restrict__ GR, float* rel, float* m, float* v,
+                                                    const AdamScalars& ad, float l3, int* match, int* nmatch) {
+    // every warp tests 32 positives at a time (independent loads) and leaves one bitmap word per group; warp 0 then
+    // expands the bitmap into the list of matching positives in ascending b (popc keeps the order)
+    unsigned* bits = reinterpret_cast<unsigned*>(match + B);
+    const int words = (B + 31) / 32, lane = threadIdx.x & 31;
+    for (int w = threadIdx.x >> 5; w < words; w += blockDim.x >> 5) {
+        const int b = 32 * w + lane;
+        const bool hit = (b < B) && (pos[3 * (long long)b + 1] == r);
+        const unsigned mask = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) bits[w] = mask;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int count = 0;
+        for (int w = 0; w < words; ++w) {
+            const unsigned mask = bits[w];
+            if ((mask >> lane) & 1u) match[count + __popc(mask & ((1u << lane) - 1u))] = 32 * w + lane;
+            count += __popc(mask);
+        }
+        if (lane == 0) *nmatch = count;
+    }
+    __syncthreads();
+    const int nm = *nmatch;
+    for (int k = threadIdx.x; k < Dr; k += blockDim.x) {
+        float g = 0.f;
+        for (int j = 0; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
+        const long long i = r * Dr + k;
+        float pp = rel[i], mm = m[i], vv = v[i];
+        adam_update(pp, g, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+        rel[i] = pp;
+        m[i] = mm;
+        v[i] = vv;
+    }
+    __syncthreads();  // match / nmatch may be rewritten by the caller's next row
+}
+
 struct EntityArgs {
     float* ent;
     float* m;
@@ -1073,33 +1114,9 @@ __global__ void __launch_bounds__(256)
 train_relation_adam_kernel(int Dr, const int64_t* __restrict__ pos, int B, const float* __restrict__ GR, float* rel,
                            float* m, float* v, AdamScalars ad, float l3, int* scratch) {
     pdl_enter();
-    // warp 0 lists the positives that use relation r, in ascending b (ballot + popc keeps the order)
     extern __shared__ int match[];  // up to B entries
     __shared__ int nmatch;
-    const long long r = blockIdx.x;
-    if (threadIdx.x < 32) {
-        int count = 0;
-        for (int base = 0; base < B; base += 32) {
-            const int b = base + threadIdx.x;
-            const bool hit = (b < B) && (pos[3 * (long long)b + 1] == r);
-            const unsigned mask = __ballot_sync(0xffffffffu, hit);
-            if (hit) match[count + __popc(mask & ((1u << threadIdx.x) - 1u))] = b;
-            count += __popc(mask);
-        }
-        if (threadIdx.x == 0) nmatch = count;
-    }
-    __syncthreads();
-    const int nm = nmatch;
-    for (int k = threadIdx.x; k < Dr; k += blockDim.x) {
-        float g = 0.f;
-        for (int j = 0; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
-        const long long i = r * Dr + k;
-        float pp = rel[i], mm = m[i], vv = v[i];
-        adam_update(pp, g, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
-        rel[i] = pp;
-        m[i] = mm;
-        v[i] = vv;
-    }
+    relation_row_update(blockIdx.x, Dr, pos, B, GR, rel, m, v, ad, l3, match, &nmatch);
 }
 
 __global__ void __launch_bounds__(256)
@@ -1384,15 +1401,18 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
                      fc.e_lo, fc.e_hi};
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
-        e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, ad, l3, st);
-        if (e != cudaSuccess) return e;
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, ad, l3, st)) != cudaSuccess) return e;
     }
     {
-        // relation rows and the modulus are replicated: every rank applies the same fixed-order update
+        // relation rows and the modulus are replicated: every rank applies the same fixed-order update.  (Folding the
+        // relation rows into the tail of the entity kernel was tried: the extra code slowed that kernel by more than
+        // the launch it saves.)
         ProfScope ps(ST_RELATION, st);
-        if ((e = launch_pdl(train_relation_adam_kernel, dim3((unsigned)P.R), dim3(256), (size_t)B * sizeof(int), st, P.Dr,
-                            fc.pos_all, (int)B, fc.GR, rel, m_rel, v_rel, ad, l3, nullptr)) != cudaSuccess) return e;
+        ps.launches(MODEL == KGE_PROTATE ? 2 : 1);
+        if ((e = launch_pdl(train_relation_adam_kernel, dim3((unsigned)P.R), dim3(256),
+                            (size_t)relation_scratch_ints((int)B) * sizeof(int), st, P.Dr, fc.pos_all, (int)B, fc.GR, rel,
+                            m_rel, v_rel, ad, l3, nullptr)) != cudaSuccess)
+            return e;
         if (MODEL == KGE_PROTATE) train_modulus_adam_kernel<<<1, 256, 0, st>>>(fc.GM, (int)B, modulus, m_mod, v_mod, ad);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }

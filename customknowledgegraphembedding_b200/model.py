@@ -230,7 +230,7 @@ class KGEModel(nn.Module):
             neg = ops._need_cuda("negative_sample", negative_sample, torch.int64)
             w = None if uni else ops._need_cuda("subsampling_weight", subsampling_weight.to(dev), torch.float32)
             ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
-            out = torch.zeros(4, dtype=torch.float32, device=dev)
+            out = torch.empty(4, dtype=torch.float32, device=dev)  # [pos, neg, loss, reg]: all four are written
             _lib.check(lib.kge_train_step(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(pos), P(neg), P(w),
                 B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out),
