@@ -90,13 +90,26 @@ class KGEModel(nn.Module):
         self.deterministic = False  # fixed-order backward (exact-check runs)
         self.interht_eps = 0.0      # 0: tf.linalg.normalize; 1e-12: F.normalize
         self._ws: Dict[tuple, torch.Tensor] = {}
+        self._scalars: Dict[str, tuple] = {}
         self._filter_cache = None
         self.last_eval = {}
 
     # ------------------------------------------------------------------------------------
+    def _scalar(self, name: str) -> float:
+        """gamma / embedding_range as Python floats without a device sync per call: `.item()` on a CUDA parameter
+        waits for everything queued on the stream, which would serialise the host and the GPU every step.  The cached
+        value is refreshed when the parameter is replaced (`.to(device)`) or written in place (`load_state_dict`)."""
+        p = getattr(self, name)
+        key = (id(p), p.data_ptr(), p._version)
+        hit = self._scalars.get(name)
+        if hit is None or hit[0] != key:
+            hit = (key, float(p.item()))
+            self._scalars[name] = hit
+        return hit[1]
+
     def _desc(self):
         return ops.make_desc(self.model_name, self.nentity, self.nrelation, self.hidden_dim, self.entity_dim,
-                             self.relation_dim, self.gamma.item(), self.embedding_range.item(), self.interht_eps)
+                             self.relation_dim, self._scalar("gamma"), self._scalar("embedding_range"), self.interht_eps)
 
     def _modulus(self) -> Optional[torch.Tensor]:
         return self.modulus if self.model_name == "pRotatE" else None
