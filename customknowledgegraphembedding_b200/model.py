@@ -10,6 +10,8 @@ memory, streams and the autograd graph edge.  There is no CPU path: a model left
 """
 from __future__ import annotations
 
+import contextlib
+
 import ctypes as C
 import logging
 from typing import Dict, Optional
@@ -91,6 +93,7 @@ class KGEModel(nn.Module):
         self.interht_eps = 0.0      # 0: tf.linalg.normalize; 1e-12: F.normalize
         self._ws: Dict[tuple, torch.Tensor] = {}
         self._scalars: Dict[str, tuple] = {}
+        self._plan_key, self._plan_ok = None, False
         self._filter_cache = None
         self.last_eval = {}
 
@@ -157,11 +160,13 @@ class KGEModel(nn.Module):
         g = optimizer.param_groups[0]
         if g.get("amsgrad") or g.get("weight_decay", 0) != 0 or g.get("maximize") or g.get("differentiable"):
             return None
-        mine = [p for p in self.parameters() if p.requires_grad]
-        theirs = [p for p in g["params"] if p.requires_grad]  # Adam skips parameters that never get a gradient
-        if len(theirs) != len(mine) or any(a is not b for a, b in zip(sorted(theirs, key=id), sorted(mine, key=id))):
-            return None
-        return g
+        key = (id(optimizer), id(g), len(g["params"]))  # the parameter-identity walk is done once per optimizer
+        if self._plan_key != key:
+            mine = [p for p in self.parameters() if p.requires_grad]
+            theirs = [p for p in g["params"] if p.requires_grad]  # Adam skips parameters that never get a gradient
+            same = len(theirs) == len(mine) and all(a is b for a, b in zip(sorted(theirs, key=id), sorted(mine, key=id)))
+            self._plan_key, self._plan_ok = key, same
+        return g if self._plan_ok else None
 
     @staticmethod
     def _adam_state(optimizer, p):
@@ -222,7 +227,8 @@ class KGEModel(nn.Module):
         P = ops._ptr
         common_state = (P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]), P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]),
                         P(st_m["exp_avg"]) if st_m else None, P(st_m["exp_avg_sq"]) if st_m else None)
-        with torch.cuda.device(dev):
+        # (the device guard costs ~10 us of host time: only taken when the model is not on the current device)
+        with (torch.cuda.device(dev) if torch.cuda.current_device() != dev.index else contextlib.nullcontext()):
             stream = ops._stream()
             if host_batch:
                 pos = positive_sample.contiguous()
