@@ -231,6 +231,15 @@ def test_fused_step_shapes(name, H, N, mode):
         gm.load_state_dict(om.state_dict())  # re-sync for the next configuration
 
 
+@pytest.mark.parametrize("name", ["RotatE", "ComplEx", "DistMult", "TransE", "pRotatE"])
+@pytest.mark.parametrize("H,N,mode", [(1000, 700, "head-batch"), (256, 1, "tail-batch"), (64, 300, "head-batch"),
+                                      (1000, 3, "tail-batch"), (512, 129, "tail-batch")])
+def test_split_sweep_part_shapes(name, H, N, mode):
+    """The warp-per-row sweep at its part boundaries: N > 256 (more than 32 rows per part), N = 1 and N = 3 (fewer
+    parts than warps), N = 129 (first size with 8 parts), every row-slot size (H <= 256 / 512 / 1024)."""
+    test_fused_step_shapes(name, H, N, mode)
+
+
 def test_fused_step_is_bit_reproducible():
     E, R, H, B, N = 400, 6, 128, 64, 96
     results = []
