@@ -277,6 +277,20 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
                     const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
                     const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
                     int64_t entity_hi, float* loss3, float* reg1, void* ws, size_t ws_bytes, void* stream) {
+    return kge_train_apply_parts(desc, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                                 adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
+                                 loss_opts, adam_opts, gathered, entity_lo, entity_hi, KGE_APPLY_ALL, loss3, reg1, ws,
+                                 ws_bytes, stream);
+}
+
+int kge_train_apply_parts(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
+                          float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
+                          float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
+                          const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
+                          const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
+                          int64_t entity_hi, int parts, float* loss3, float* reg1, void* ws, size_t ws_bytes,
+                          void* stream) {
+    if (parts <= 0 || (parts & ~KGE_APPLY_ALL)) return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be a non-empty subset of KGE_APPLY_*");
     Params P;
     int rc = check_train_args(desc, &P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                               adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all,
@@ -292,8 +306,9 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
     float* small = nullptr;
     cudaError_t e = launch_train_apply(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                                        adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
-                                       *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, ws, ws_bytes, &small, st);
+                                       *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, parts, ws, ws_bytes, &small, st);
     if (e != cudaSuccess) return fail_cuda(e, "kge_train_apply");
+    if (!(parts & KGE_APPLY_PREPARE)) return KGE_OK;  // the loss belongs to the piece that computes it
     if (reg1 == loss3 + 3) {
         e = cudaMemcpyAsync(loss3, small, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st);
     } else {

@@ -24,5 +24,5 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, void* ws, size_t ws_bytes, float** out_small, cudaStream_t st);
+                               int64_t e_hi, int parts, void* ws, size_t ws_bytes, float** out_small, cudaStream_t st);
 }

@@ -1249,6 +1249,9 @@ struct FusedCall {
     long long e_lo, e_hi;
     // per-positive buffers (sweep: written for the local batch; apply: read for the global batch)
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
+    // apply in pieces (kge_train_apply_parts): 1 = buckets + dL/ds + loss, 2 = entity rows [e_lo, e_hi), 4 = relation
+    // rows + modulus.  One piece-1 call, any number of piece-2 calls over disjoint ranges, one piece-4 call.
+    int parts = 7;
 };
 
 template <int MODEL, int CHW, bool HEAD, int R>
@@ -1363,47 +1366,48 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     }
     const int64_t B = fc.B_all;
     const long long BN = B * N;
-    {
-        ProfScope ps(ST_BUCKETS, st);
-        // (ws.small was cleared before the sweep when this call runs one: the sweep's last kernel is then followed
-        //  directly by the scan, kernel to kernel)
-        if (fc.phase == 2 && (e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
-        if (fc.phase == 2) {
-            if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
-            if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, st)) != cudaSuccess) return e;
+    const float l3 = lo.regularization;
+    if (fc.parts & 1) {
+        {
+            ProfScope ps(ST_BUCKETS, st);
+            // (ws.small was cleared before the sweep when this call runs one: the sweep's last kernel is then followed
+            //  directly by the scan, kernel to kernel)
+            if (fc.phase == 2 && (e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
+            if (fc.phase == 2) {
+                if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
+                if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, st)) != cudaSuccess) return e;
+            }
+            if ((e = launch_scan_fill(mode, fc.pos_all, fc.neg_all, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items,
+                                      ws.block_sums, st)) != cudaSuccess)
+                return e;
+            const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
+            if ((e = launch_pdl(bucket_sort_kernel, dim3(sb), dim3(256), 0, st, ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N)) != cudaSuccess) return e;
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
-        if ((e = launch_scan_fill(mode, fc.pos_all, fc.neg_all, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items,
-                                  ws.block_sums, st)) != cudaSuccess)
-            return e;
-        const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
-        if ((e = launch_pdl(bucket_sort_kernel, dim3(sb), dim3(256), 0, st, ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N)) != cudaSuccess) return e;
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        {
+            ProfScope ps(ST_DSCORE, st);
+            const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
+            if ((e = launch_pdl(dscore_kernel, dim3(db), dim3(256), 0, st, fc.S, fc.stats, BN, (int)N,
+                                lo.negative_adversarial_sampling, lo.adversarial_temperature)) != cudaSuccess) return e;
+            if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(256), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
+        if (lo.regularization != 0.f) {
+            ProfScope ps(ST_REG, st);
+            if ((e = launch_l3_sum_cubes(ent, (int64_t)P.E * P.De, ws.small + 4, ws.l3_ws, st)) != cudaSuccess) return e;
+            if ((e = launch_l3_sum_cubes(rel, (int64_t)P.R * P.Dr, ws.small + 5, ws.l3_ws, st)) != cudaSuccess) return e;
+            fused_finalize_reg_kernel<<<1, 1, 0, st>>>(ws.small, l3);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
     }
-    {
-        ProfScope ps(ST_DSCORE, st);
-        const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
-        if ((e = launch_pdl(dscore_kernel, dim3(db), dim3(256), 0, st, fc.S, fc.stats, BN, (int)N,
-                            lo.negative_adversarial_sampling, lo.adversarial_temperature)) != cudaSuccess) return e;
-        if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(256), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    }
-    float l3 = 0.f;
-    if (lo.regularization != 0.f) {
-        ProfScope ps(ST_REG, st);
-        l3 = lo.regularization;
-        if ((e = launch_l3_sum_cubes(ent, (int64_t)P.E * P.De, ws.small + 4, ws.l3_ws, st)) != cudaSuccess) return e;
-        if ((e = launch_l3_sum_cubes(rel, (int64_t)P.R * P.Dr, ws.small + 5, ws.l3_ws, st)) != cudaSuccess) return e;
-        fused_finalize_reg_kernel<<<1, 1, 0, st>>>(ws.small, l3);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    }
-    if (fc.e_hi > fc.e_lo) {
+    if ((fc.parts & 2) && fc.e_hi > fc.e_lo) {
         ProfScope ps(ST_ENTITY, st);
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
                      fc.e_lo, fc.e_hi};
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
         if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, ad, l3, st)) != cudaSuccess) return e;
     }
-    {
+    if (fc.parts & 4) {
         // relation rows and the modulus are replicated: every rank applies the same fixed-order update.  (Folding the
         // relation rows into the tail of the entity kernel was tried: the extra code slowed that kernel by more than
         // the launch it saves.)
@@ -1489,12 +1493,12 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, void* wsp, size_t ws_bytes, float** out_small, cudaStream_t st) {
+                               int64_t e_hi, int parts, void* wsp, size_t ws_bytes, float** out_small, cudaStream_t st) {
     if (ws_bytes < fused_step_workspace_bytes(P, B_all, N)) return cudaErrorInvalidValue;
     const FusedWs ws = fused_carve(P, B_all, N, wsp);
     *out_small = ws.small;
     FusedCall fc{2, nullptr, nullptr, nullptr, 0, nullptr, B_all, pos_all, neg_all, B_all, e_lo, e_hi,
-                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms};
+                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, parts};
     return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
                           ws, st);
 }

@@ -20,6 +20,7 @@ is testable on CPU over ``gloo`` with stand-ins (tests/test_dist_cpu.py).
 from __future__ import annotations
 
 import contextlib
+import os
 import ctypes as C
 from typing import Dict, Optional
 
@@ -43,13 +44,14 @@ def _world(group=None):
     return dist.get_rank(group), dist.get_world_size(group)
 
 
-def _coalesced(group, device):
-    """Batch several NCCL calls into one group launch when torch exposes the coalescing manager."""
+def _coalesced(group, device, async_ops=False):
+    """Batch several NCCL calls into one group launch when torch exposes the coalescing manager.  With
+    ``async_ops`` the context yields a handle whose ``wait()`` makes the current stream wait for the batch."""
     cm = getattr(dist, "_coalescing_manager", None)
     if cm is None or device.type != "cuda":
         return contextlib.nullcontext()
     try:
-        return cm(group=group, device=device, async_ops=False)
+        return cm(group=group, device=device, async_ops=async_ops)
     except TypeError:  # signature differs in this torch: fall back to one launch per call
         return contextlib.nullcontext()
 
@@ -94,6 +96,8 @@ class DataParallelStep:
         self._gathered: Dict[str, torch.Tensor] = {}
         self._ws: Optional[torch.Tensor] = None
         self._shape = None
+        # pieces of the owned row range whose broadcast overlaps the next piece's update (1 = apply, then broadcast)
+        self.overlap_chunks = int(os.environ.get("KGE_DP_OVERLAP_CHUNKS", "1"))
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -133,7 +137,8 @@ class DataParallelStep:
             self._sws = ws
         return ws
 
-    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out):
+    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None):
+        """kge_train_apply_parts on the rows ``[lo, hi)`` (default: everything this rank owns, all parts)."""
         m, opt = self.model, self.optimizer
         B_all, N = neg_all.shape
         ent, rel, mod = m.entity_embedding, m.relation_embedding, m._modulus()
@@ -146,12 +151,43 @@ class DataParallelStep:
         bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
         P = ops._ptr
         with torch.cuda.device(ent.device):
-            _lib.check(_lib.load().kge_train_apply(
+            _lib.check(_lib.load().kge_train_apply_parts(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
                 P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
                 P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
-                C.byref(adam), C.byref(bufs), self.lo, self.hi, P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws),
-                self._ws.numel(), ops._stream()), "kge_train_apply")
+                C.byref(adam), C.byref(bufs), self.lo if lo is None else lo, self.hi if hi is None else hi, int(parts),
+                P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws), self._ws.numel(), ops._stream()),
+                "kge_train_apply_parts")
+
+    def _apply_overlapped(self, mode, pos_all, neg_all, loss_opts, adam, out):
+        """Owner-parallel apply with the broadcast of the updated rows hidden behind it: the owned range is cut into
+        ``overlap_chunks`` pieces; as soon as the kernel of piece c is queued, every rank's piece c is broadcast
+        asynchronously (NCCL's stream waits for the kernels queued so far, ours goes on with piece c + 1)."""
+        K, world, E = self.overlap_chunks, self.world, self.model.nentity
+        ent = self.model.entity_embedding.data
+
+        def piece(r, c):
+            lo, hi = shard_range(E, r, world)
+            n = hi - lo
+            return lo + (n * c) // K, lo + (n * (c + 1)) // K
+
+        self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_PREPARE)
+        pending = []
+        for c in range(K):
+            lo, hi = piece(self.rank, c)
+            if hi > lo:
+                self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ROWS, lo=lo, hi=hi)
+            with _coalesced(self.group, ent.device, async_ops=True) as cm:
+                for r in range(world):
+                    rlo, rhi = piece(r, c)
+                    if rhi > rlo:
+                        src = dist.get_global_rank(self.group, r) if self.group is not None else r
+                        dist.broadcast(ent[rlo:rhi], src=src, group=self.group)
+            pending.append(cm)
+        self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_FINISH)
+        for cm in pending:
+            if cm is not None:
+                cm.wait()  # the current stream waits for the broadcasts: the next sweep reads every row
 
     # ---- one global step -----------------------------------------------------------------------------
     def train_step(self, train_iterator, args, sync: bool = True):
@@ -197,8 +233,12 @@ class DataParallelStep:
         b1, b2 = group_opts["betas"]
         adam = AdamOpts(float(group_opts["lr"]), float(b1), float(b2), float(group_opts["eps"]), int(states[0]["step"]), 0)
         out = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._apply(mode, pos_all, neg_all, loss_opts, adam, out)
-        self._share_rows()
+        if (self.world > 1 and self.overlap_chunks > 1 and dev.type == "cuda"
+                and type(self)._apply is DataParallelStep._apply and type(self)._share_rows is DataParallelStep._share_rows):
+            self._apply_overlapped(mode, pos_all, neg_all, loss_opts, adam, out)
+        else:
+            self._apply(mode, pos_all, neg_all, loss_opts, adam, out)
+            self._share_rows()
         if not sync:
             return out
         pos_l, neg_l, loss, regv = out.tolist()

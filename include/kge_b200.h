@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 2
+#define KGE_B200_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -272,6 +272,23 @@ KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity,
                             const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
                             const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, float *loss3,
                             float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/* kge_train_apply in pieces, so that the caller can put communication between them (dist.DataParallelStep broadcasts
+ * the rows of one chunk while the next chunk is being updated).  `parts` is a subset of:
+ *   KGE_APPLY_PREPARE  bucket build over the global batch, S <- dL/ds in place, loss3 / reg1 (exactly once, first);
+ *   KGE_APPLY_ROWS     gradient gather + Adam for the entity rows [entity_lo, entity_hi) (any number of calls over
+ *                      disjoint ranges; needs the workspace PREPARE left behind);
+ *   KGE_APPLY_FINISH   relation rows + pRotatE modulus (exactly once, after the last ROWS call: pRotatE's entity
+ *                      gradient reads the modulus of the step's start).
+ * kge_train_apply == parts = KGE_APPLY_ALL.  Replaces the same `apply_gradients` as kge_train_apply (supervisor.py:26). */
+enum { KGE_APPLY_PREPARE = 1, KGE_APPLY_ROWS = 2, KGE_APPLY_FINISH = 4, KGE_APPLY_ALL = 7 };
+KGE_API int kge_train_apply_parts(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
+                                  float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
+                                  float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus,
+                                  const int64_t *positive_all, const int64_t *negative_all, int64_t B_all, int64_t N,
+                                  const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
+                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
+                                  float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
 
 /*
  * kge_train_apply over a ROW-SHARDED entity table: `entity_shard`, `adam_m_shard`, `adam_v_shard` hold only the rows

@@ -95,3 +95,51 @@ def test_emulated_ranks_equal_plain_step(name, world):
             assert torch.equal(s.relation_embedding, ref.relation_embedding)
             if name == "pRotatE":
                 assert torch.equal(s.modulus, ref.modulus)
+
+
+@pytest.mark.parametrize("name", ["RotatE", "pRotatE", "InterHT", "ComplEx"])
+def test_apply_in_pieces_equals_one_apply(name):
+    """kge_train_apply_parts: PREPARE, the owned rows in three ROWS calls, FINISH == kge_train_apply, bit for bit
+    (pRotatE: the entity gradient must see the modulus of the step's start, so FINISH comes last)."""
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import _lib, dist as kd
+    E, R, H, B, N, lr = 157, 4, 32, 10, 21, 1e-3
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
+    ref, cut = _model(name, E, R, H, seed=9), _model(name, E, R, H, seed=9)
+    ref_opt, cut_opt = _adam(ref, lr), _adam(cut, lr)
+
+    class Pieces(kd.DataParallelStep):
+        def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None):
+            base = super()._apply
+            base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_PREPARE)
+            for a, b in ((0, 50), (50, 51), (51, E)):
+                base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ROWS, lo=a, hi=b)
+            base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_FINISH)
+
+    step = Pieces(cut, cut_opt)
+    for s in range(3):
+        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=20 + s)
+        batch = (pos.cuda(), neg.cuda(), w.cuda(), mode)
+        want = kb.KGEModel.train_step(ref, ref_opt, iter([batch]), args)
+        got = step.train_step(iter([batch]), args)
+        assert got["loss"] == want["loss"], (s, got, want)
+        assert torch.equal(cut.entity_embedding, ref.entity_embedding), s
+        assert torch.equal(cut.relation_embedding, ref.relation_embedding), s
+        if name == "pRotatE":
+            assert torch.equal(cut.modulus, ref.modulus), s
+
+
+def test_apply_parts_argument_checks():
+    from customknowledgegraphembedding_b200 import _lib, dist as kd
+    E, R, H, B, N = 40, 3, 16, 4, 6
+    m = _model("RotatE", E, R, H, seed=1)
+    step = kd.DataParallelStep(m, _adam(m, 1e-3))
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
+    pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=3)
+    step.train_step(iter([(pos.cuda(), neg.cuda(), w.cuda(), mode)]), args)  # builds the buffers
+    from customknowledgegraphembedding_b200._lib import AdamOpts, LossOpts
+    out = torch.zeros(4, device="cuda")
+    for bad in (0, 8, -1):
+        with pytest.raises(ValueError):
+            step._apply(mode, pos.cuda(), neg.cuda(), LossOpts(1, 0, 1, 0, 1.0, 0.0), AdamOpts(1e-3, 0.9, 0.999, 1e-8, 2, 0),
+                        out, parts=bad)
