@@ -120,12 +120,16 @@ __device__ __forceinline__ long long item_entity(int item, int mode, const int64
     return (j < B) ? pos[3 * j + 0] : pos[3 * (j - B) + 2];
 }
 
+// only uses of the entity rows [e_lo, e_hi) are counted / filed: a rank that owns a row range builds the buckets of
+// that range alone (the per-bucket sort is quadratic in the bucket length, which grows with the global batch)
 __global__ void det_histogram_kernel(int mode, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg,
-                                     long long BN, long long B, int* counts) {
+                                     long long BN, long long B, int* counts, long long e_lo, long long e_hi) {
     pdl_enter();
     const long long total = BN + 2 * B;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
-        atomicAdd(counts + item_entity((int)i, mode, pos, neg, BN, B), 1);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int e = item_entity((int)i, mode, pos, neg, BN, B);
+        if (e >= e_lo && e < e_hi) atomicAdd(counts + e, 1);
+    }
 }
 
 // exclusive scan of counts[0..n) -> offsets[0..n], three phases, 1024 elements per block
@@ -199,12 +203,12 @@ __global__ void scan_add_kernel(int* out, const int* __restrict__ block_sums, lo
 }
 
 __global__ void det_fill_kernel(int mode, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg,
-                                long long BN, long long B, int* cursor, int* items) {
+                                long long BN, long long B, int* cursor, int* items, long long e_lo, long long e_hi) {
     pdl_enter();
     const long long total = BN + 2 * B;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int slot = atomicAdd(cursor + item_entity((int)i, mode, pos, neg, BN, B), 1);
-        items[slot] = (int)i;
+        const int e = item_entity((int)i, mode, pos, neg, BN, B);
+        if (e >= e_lo && e < e_hi) items[atomicAdd(cursor + e, 1)] = (int)i;
     }
 }
 
@@ -291,15 +295,16 @@ __global__ void __launch_bounds__(256) det_modulus_kernel(const float* __restric
 }
 
 cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, int* counts,
-                             cudaStream_t st) {
+                             long long e_lo, long long e_hi, cudaStream_t st) {
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
-    return launch_pdl(det_histogram_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, counts);
+    return launch_pdl(det_histogram_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, counts, e_lo, e_hi);
 }
 
 // exclusive scan of counts -> offsets (+ a copy in cursor), then scatter every use into its bucket
 cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
-                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st) {
+                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, long long e_lo,
+                             long long e_hi, cudaStream_t st) {
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
     const int nblocks = (int)((E + kScanBlock - 1) / kScanBlock);
@@ -308,7 +313,7 @@ cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, l
     if ((e = launch_pdl(scan_sums_kernel, dim3(1), dim3(1024), 0, st, block_sums, nblocks)) != cudaSuccess) return e;
     if ((e = launch_pdl(scan_add_kernel, dim3((unsigned)((E + 1 + 255) / 256)), dim3(256), 0, st, offsets, block_sums, E, cursor)) != cudaSuccess)
         return e;
-    return launch_pdl(det_fill_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, cursor, items);
+    return launch_pdl(det_fill_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, cursor, items, e_lo, e_hi);
 }
 
 template <int MODEL>
@@ -341,12 +346,12 @@ static cudaError_t launch_det_model(const Params& P, int mode, const float* ent,
     if (e != cudaSuccess) return e;
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
-    det_histogram_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, w.counts);
+    det_histogram_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, w.counts, 0, P.E);
     const int nblocks = (int)((P.E + kScanBlock - 1) / kScanBlock);
     scan_block_kernel<<<nblocks, 256, 0, st>>>(w.counts, w.offsets, w.block_sums, P.E);
     scan_sums_kernel<<<1, 1024, 0, st>>>(w.block_sums, nblocks);
     scan_add_kernel<<<(unsigned)((P.E + 1 + 255) / 256), 256, 0, st>>>(w.offsets, w.block_sums, P.E, w.cursor);
-    det_fill_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, w.cursor, w.items);
+    det_fill_kernel<<<hb, 256, 0, st>>>(mode, pos, neg, BN, B, w.cursor, w.items, 0, P.E);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     // C

@@ -40,9 +40,10 @@ cudaError_t launch_score_backward_det(const Params& P, int mode, const float* en
                                       float* grad_modulus, void* ws, size_t ws_bytes, cudaStream_t st);
 
 cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, int* counts,
-                             cudaStream_t st);
+                             long long e_lo, long long e_hi, cudaStream_t st);
 cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, long long BN, long long B, long long E,
-                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, cudaStream_t st);
+                             int* counts, int* offsets, int* cursor, int* items, int* block_sums, long long e_lo,
+                             long long e_hi, cudaStream_t st);
 
 // K2
 cudaError_t launch_loss_final(const float* terms, int64_t B, float* loss3, cudaStream_t st);

@@ -1370,15 +1370,17 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     if (fc.parts & 1) {
         {
             ProfScope ps(ST_BUCKETS, st);
+            // apply-only calls build the buckets of the rows [e_lo, e_hi) alone; a full step counted every use in F1
+            const long long b_lo = (fc.phase == 2) ? fc.e_lo : 0, b_hi = (fc.phase == 2) ? fc.e_hi : P.E;
             // (ws.small was cleared before the sweep when this call runs one: the sweep's last kernel is then followed
             //  directly by the scan, kernel to kernel)
             if (fc.phase == 2 && (e = cudaMemsetAsync(ws.small, 0, 16 * sizeof(float), st)) != cudaSuccess) return e;
             if (fc.phase == 2) {
                 if ((e = cudaMemsetAsync(ws.counts, 0, (size_t)(P.E + 1) * sizeof(int), st)) != cudaSuccess) return e;
-                if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, st)) != cudaSuccess) return e;
+                if ((e = launch_histogram(mode, fc.pos_all, fc.neg_all, BN, B, ws.counts, b_lo, b_hi, st)) != cudaSuccess) return e;
             }
             if ((e = launch_scan_fill(mode, fc.pos_all, fc.neg_all, BN, B, P.E, ws.counts, ws.offsets, ws.cursor, ws.items,
-                                      ws.block_sums, st)) != cudaSuccess)
+                                      ws.block_sums, b_lo, b_hi, st)) != cudaSuccess)
                 return e;
             const int sb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
             if ((e = launch_pdl(bucket_sort_kernel, dim3(sb), dim3(256), 0, st, ws.offsets, ws.items, ws.items_sorted, ws.items_b, P.E, (int)N)) != cudaSuccess) return e;

@@ -275,7 +275,8 @@ KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity,
 
 /* kge_train_apply in pieces, so that the caller can put communication between them (dist.DataParallelStep broadcasts
  * the rows of one chunk while the next chunk is being updated).  `parts` is a subset of:
- *   KGE_APPLY_PREPARE  bucket build over the global batch, S <- dL/ds in place, loss3 / reg1 (exactly once, first);
+ *   KGE_APPLY_PREPARE  bucket build for the rows [entity_lo, entity_hi) (must cover every later ROWS range), S <- dL/ds
+ *                      in place, loss3 / reg1 (exactly once, first);
  *   KGE_APPLY_ROWS     gradient gather + Adam for the entity rows [entity_lo, entity_hi) (any number of calls over
  *                      disjoint ranges; needs the workspace PREPARE left behind);
  *   KGE_APPLY_FINISH   relation rows + pRotatE modulus (exactly once, after the last ROWS call: pRotatE's entity
