@@ -318,6 +318,22 @@ int kge_train_apply_parts(const kge_model_desc* desc, int mode, float* entity, f
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_apply(copy loss)");
 }
 
+int kge_train_exchange(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B, int64_t N,
+                       const kge_step_buffers* local, int rank, int world, const kge_step_buffers* peer_gathered,
+                       int64_t* const* peer_positive, int64_t* const* peer_negative, void* stream) {
+    Params P;
+    int rc = make_params(desc, &P);
+    if (rc) return rc;
+    if (!positive || !negative || !local || !peer_gathered || !peer_positive || !peer_negative)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if (B < 0 || N < 1) return fail(KGE_ERR_INVALID_ARGUMENT, "bad batch shape");
+    if (world < 1 || world > 16 || rank < 0 || rank >= world)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "rank %d / world %d (at most 16 peers)", rank, world);
+    cudaError_t e = launch_exchange(P, positive, negative, B, N, *local, rank, world, peer_gathered, peer_positive,
+                                    peer_negative, (cudaStream_t)stream);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_exchange");
+}
+
 int kge_train_set_sweep_variant(int variant) {
     train_set_sweep_variant(variant);
     return KGE_OK;

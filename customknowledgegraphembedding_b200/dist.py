@@ -98,6 +98,9 @@ class DataParallelStep:
         self._shape = None
         # pieces of the owned row range whose broadcast overlaps the next piece's update (1 = apply, then broadcast)
         self.overlap_chunks = int(os.environ.get("KGE_DP_OVERLAP_CHUNKS", "1"))
+        # per-positive buffers exchanged by peer stores (symmetric memory) instead of an NCCL all-gather
+        self.peer_exchange = os.environ.get("KGE_DP_PEER_EXCHANGE", "1") != "0"
+        self._peer = None
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -111,10 +114,51 @@ class DataParallelStep:
             return
         sizes = self._row_sizes(N)
         self._local = {k: torch.empty(B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
-        self._gathered = {k: torch.empty(self.world * B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
-        self._gathered["pos"] = torch.empty((self.world * B, 3), dtype=torch.int64, device=dev)
-        self._gathered["neg"] = torch.empty((self.world * B, N), dtype=torch.int64, device=dev)
+        self._peer = None
+        if self.world > 1 and dev.type == "cuda" and self.peer_exchange:
+            self._peer = self._peer_buffers(B, N, dev, sizes)
+        if self._peer is None:
+            self._gathered = {k: torch.empty(self.world * B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
+            self._gathered["pos"] = torch.empty((self.world * B, 3), dtype=torch.int64, device=dev)
+            self._gathered["neg"] = torch.empty((self.world * B, N), dtype=torch.int64, device=dev)
         self._shape = (B, N, dev)
+
+    def _peer_buffers(self, B, N, dev, sizes):
+        """The gathered buffers carved from ONE symmetric-memory block, so that every rank can store into every other
+        rank's copy (kge_train_exchange).  Returns the peer pointer tables, or None when this torch has no symmetric
+        memory (the NCCL all-gather is used then).  Collective: every rank takes the same branch."""
+        try:
+            import torch.distributed._symmetric_memory as symm
+        except ImportError:
+            return None
+        G = self.world
+        items = [(k, G * B * sizes[k] * 4, torch.float32, None) for k in _BUFFERS]
+        items += [("pos", G * B * 3 * 8, torch.int64, (G * B, 3)), ("neg", G * B * N * 8, torch.int64, (G * B, N))]
+        offsets, total = {}, 0
+        for k, nbytes, _, _ in items:
+            offsets[k] = total
+            total += (nbytes + 255) & ~255
+        block = symm.empty(total, dtype=torch.uint8, device=dev)
+        hdl = symm.rendezvous(block, self.group if self.group is not None else dist.group.WORLD)
+        self._gathered = {}
+        for k, nbytes, dt, shape in items:
+            t = block[offsets[k]:offsets[k] + nbytes].view(dt)
+            self._gathered[k] = t.view(shape) if shape is not None else t
+        bases = [int(p) for p in hdl.buffer_ptrs]
+        tables = (StepBuffers * G)(*[StepBuffers(*[C.c_void_p(b + offsets[k]) for k in _BUFFERS]) for b in bases])
+        pos_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["pos"]) for b in bases])
+        neg_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["neg"]) for b in bases])
+        return {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs}
+
+    def _exchange(self, pos, neg):
+        """kge_train_exchange + the barrier that orders every rank's apply after every rank's stores."""
+        B, N = neg.shape
+        local = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        with torch.cuda.device(pos.device):
+            _lib.check(_lib.load().kge_train_exchange(
+                C.byref(self.model._desc()), ops._ptr(pos), ops._ptr(neg), B, N, C.byref(local), self.rank, self.world,
+                self._peer["tables"], self._peer["pos"], self._peer["neg"], ops._stream()), "kge_train_exchange")
+            self._peer["hdl"].barrier()
 
     # ---- the two kernel calls (overridable: tests/test_dist_cpu.py) ------------------------------------
     def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
@@ -214,7 +258,10 @@ class DataParallelStep:
         if self.world > 1:
             dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
         self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
-        if self.world > 1:
+        if self.world > 1 and self._peer is not None:
+            self._exchange(pos, neg)  # peer stores over NVLink: GH / GT rows go to their owners only
+            pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
+        elif self.world > 1:
             with _coalesced(self.group, dev):
                 dist.all_gather_into_tensor(self._gathered["pos"], pos, group=self.group)
                 dist.all_gather_into_tensor(self._gathered["neg"], neg, group=self.group)

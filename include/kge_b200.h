@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 3
+#define KGE_B200_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -290,6 +290,20 @@ KGE_API int kge_train_apply_parts(const kge_model_desc *desc, int mode, float *e
                                   const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
                                   const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
                                   float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * Between kge_train_sweep and kge_train_apply: the exchange of the per-positive buffers over NVLink peer memory,
+ * in place of an all-gather.  One kernel stores, for each of the B local positives (global slot rank * B + b), the
+ * ids, S, Q, GR, GM, stats, terms into EVERY rank's gathered buffers and GH[b] / GT[b] only into the buffers of the
+ * rank that owns the head / tail entity (row ranges of ceil(E / world) rows, as dist.shard_range).  `peer_gathered`,
+ * `peer_positive`, `peer_negative` are HOST arrays of `world` entries holding device pointers valid on this GPU
+ * (symmetric-memory peer mappings; entry `rank` is the local buffer).  The caller puts a barrier across the ranks on
+ * the stream before kge_train_apply.  Replaces the dense gradient all-reduce of the replicas (supervisor.py:26-30).
+ */
+KGE_API int kge_train_exchange(const kge_model_desc *desc, const int64_t *positive, const int64_t *negative, int64_t B,
+                               int64_t N, const kge_step_buffers *local, int rank, int world,
+                               const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
+                               int64_t *const *peer_negative, void *stream);
 
 /*
  * kge_train_apply over a ROW-SHARDED entity table: `entity_shard`, `adam_m_shard`, `adam_v_shard` hold only the rows

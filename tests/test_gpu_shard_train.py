@@ -143,3 +143,51 @@ def test_apply_parts_argument_checks():
         with pytest.raises(ValueError):
             step._apply(mode, pos.cuda(), neg.cuda(), LossOpts(1, 0, 1, 0, 1.0, 0.0), AdamOpts(1e-3, 0.9, 0.999, 1e-8, 2, 0),
                         out, parts=bad)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_peer_exchange_places_every_row_where_it_is_needed(world):
+    """kge_train_exchange with the ranks emulated on one GPU (every "peer" block is a plain tensor here; over real
+    ranks the same pointers come from symmetric memory -- scratch/dist_check.py): ids, S, Q, GR and the scalars land
+    in every rank's gathered buffers at slot rank * B + b; GH / GT rows only at the owner of the head / tail."""
+    import ctypes as C
+    from customknowledgegraphembedding_b200 import _lib, ops
+    from customknowledgegraphembedding_b200._lib import StepBuffers
+    E, R, H, B, N = 50, 3, 8, 5, 7
+    m = _model("RotatE", E, R, H, seed=1)
+    sizes = {"S": N, "Q": 2 * H, "GH": 2 * H, "GT": 2 * H, "GR": H, "GM": 1, "stats": 2, "terms": 2}
+    names = ("S", "Q", "GH", "GT", "GR", "GM", "stats", "terms")
+    g = torch.Generator().manual_seed(3)
+    local = [{k: torch.randn(B * s, generator=g).cuda() for k, s in sizes.items()} for _ in range(world)]
+    pos = [torch.stack([torch.randint(0, E, (B,), generator=g), torch.randint(0, R, (B,), generator=g),
+                        torch.randint(0, E, (B,), generator=g)], 1).cuda() for _ in range(world)]
+    neg = [torch.randint(0, E, (B, N), generator=g).cuda() for _ in range(world)]
+    SENT = -777.0
+    gathered = [{k: torch.full((world * B * s,), SENT, device="cuda") for k, s in sizes.items()} for _ in range(world)]
+    gpos = [torch.full((world * B, 3), -1, dtype=torch.int64, device="cuda") for _ in range(world)]
+    gneg = [torch.full((world * B, N), -1, dtype=torch.int64, device="cuda") for _ in range(world)]
+    tables = (StepBuffers * world)(*[StepBuffers(*[C.c_void_p(gathered[p][k].data_ptr()) for k in names]) for p in range(world)])
+    ppos = (C.c_void_p * world)(*[C.c_void_p(t.data_ptr()) for t in gpos])
+    pneg = (C.c_void_p * world)(*[C.c_void_p(t.data_ptr()) for t in gneg])
+    lib = _lib.load()
+    for r in range(world):
+        loc = StepBuffers(*[C.c_void_p(local[r][k].data_ptr()) for k in names])
+        _lib.check(lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r, world,
+                                          tables, ppos, pneg, ops._stream()), "kge_train_exchange")
+    torch.cuda.synchronize()
+    rows = (E + world - 1) // world
+    for p in range(world):
+        assert torch.equal(gpos[p], torch.cat(pos)) and torch.equal(gneg[p], torch.cat(neg))
+        for k in ("S", "Q", "GR", "GM", "stats", "terms"):
+            assert torch.equal(gathered[p][k], torch.cat([local[r][k] for r in range(world)])), (p, k)
+        for k, col in (("GH", 0), ("GT", 2)):
+            got = gathered[p][k].view(world * B, -1)
+            want = torch.cat([local[r][k] for r in range(world)]).view(world * B, -1)
+            owner = torch.cat(pos)[:, col] // rows
+            mine = owner == p
+            assert torch.equal(got[mine], want[mine]), (p, k)
+            assert bool((got[~mine] == SENT).all()), (p, k)  # rows nobody here will read were not sent
+    with pytest.raises(ValueError):
+        lib_rc = lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[0]), ops._ptr(neg[0]), B, N, C.byref(loc), world, world,
+                                        tables, ppos, pneg, ops._stream())
+        _lib.check(lib_rc, "kge_train_exchange")
