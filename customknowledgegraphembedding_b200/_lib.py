@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
 
 # kge_model_id / kge_mode / kge_ws_kind
@@ -90,6 +90,9 @@ PROTOTYPES = {
     "kge_train_apply_parts": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                         C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64,
                                         C.c_int, _P, _P, _P, _SZ, _P]),
+    "kge_train_apply_peers": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
+                                        C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64,
+                                        C.c_int, C.c_int, C.POINTER(C.c_void_p), _P, _P, _P, _SZ, _P]),
     "kge_train_exchange": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
                                      C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _P]),
     "kge_train_apply_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,

@@ -842,6 +842,8 @@ __device__ __forceinline__ void relation_row_update(long long r, int Dr, const i
     __syncthreads();  // match / nmatch may be rewritten by the caller's next row
 }
 
+constexpr int kMaxRowPeers = 15;
+
 struct EntityArgs {
     float* ent;
     float* m;
@@ -856,6 +858,10 @@ struct EntityArgs {
     int N;
     long long BN, B;
     long long e_lo, e_hi;  // rows this rank owns
+    // replicas of the table on the other ranks (peer mappings): the updated row is stored there as well, so that the
+    // broadcast of the owned rows rides on the Adam epilogue instead of following it
+    int npeers;
+    float* peer[kMaxRowPeers];
 };
 
 // One use of the row by a negative slot: gc += dL/ds * ds/dc, with q of the using positive.
@@ -1099,9 +1105,12 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
                     adam_update(c[p][j][1], gc[p][j][1], mm.y, vv.y, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
                     adam_update(c[p][j][2], gc[p][j][2], mm.z, vv.z, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
                     adam_update(c[p][j][3], gc[p][j][3], mm.w, vv.w, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
-                    *reinterpret_cast<float4*>(row + p * H + k0) = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
+                    const float4 upd = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
+                    *reinterpret_cast<float4*>(row + p * H + k0) = upd;
                     *reinterpret_cast<float4*>(mrow + p * H + k0) = mm;
                     *reinterpret_cast<float4*>(vrow + p * H + k0) = vv;
+                    for (int q = 0; q < A.npeers; ++q)  // NVLink stores into the other ranks' replicas
+                        *reinterpret_cast<float4*>(A.peer[q] + e * (long long)P.De + p * H + k0) = upd;
                 }
             }
     }
@@ -1252,6 +1261,9 @@ struct FusedCall {
     // apply in pieces (kge_train_apply_parts): 1 = buckets + dL/ds + loss, 2 = entity rows [e_lo, e_hi), 4 = relation
     // rows + modulus.  One piece-1 call, any number of piece-2 calls over disjoint ranges, one piece-4 call.
     int parts = 7;
+    // kge_train_apply_rows_peers: replicas of the entity table on the other ranks
+    int npeers = 0;
+    float* const* peers = nullptr;  // host array of npeers device pointers
 };
 
 template <int MODEL, int CHW, bool HEAD, int R>
@@ -1405,7 +1417,8 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     if ((fc.parts & 2) && fc.e_hi > fc.e_lo) {
         ProfScope ps(ST_ENTITY, st);
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
-                     fc.e_lo, fc.e_hi};
+                     fc.e_lo, fc.e_hi, fc.npeers, {}};
+        for (int q = 0; q < fc.npeers; ++q) A.peer[q] = fc.peers[q];
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
         if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, ad, l3, st)) != cudaSuccess) return e;
     }
@@ -1495,12 +1508,14 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, int parts, void* wsp, size_t ws_bytes, float** out_small, cudaStream_t st) {
+                               int64_t e_hi, int parts, int npeers, float* const* peers, void* wsp, size_t ws_bytes,
+                               float** out_small, cudaStream_t st) {
+    if (npeers < 0 || npeers > kMaxRowPeers) return cudaErrorInvalidValue;
     if (ws_bytes < fused_step_workspace_bytes(P, B_all, N)) return cudaErrorInvalidValue;
     const FusedWs ws = fused_carve(P, B_all, N, wsp);
     *out_small = ws.small;
     FusedCall fc{2, nullptr, nullptr, nullptr, 0, nullptr, B_all, pos_all, neg_all, B_all, e_lo, e_hi,
-                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, parts};
+                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, parts, npeers, peers};
     return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
                           ws, st);
 }

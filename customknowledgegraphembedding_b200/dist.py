@@ -101,6 +101,7 @@ class DataParallelStep:
         # per-positive buffers exchanged by peer stores (symmetric memory) instead of an NCCL all-gather
         self.peer_exchange = os.environ.get("KGE_DP_PEER_EXCHANGE", "1") != "0"
         self._peer = None
+        self._rows_peer = None  # entity table in symmetric memory: updated rows are stored into the other replicas
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -117,6 +118,8 @@ class DataParallelStep:
         self._peer = None
         if self.world > 1 and dev.type == "cuda" and self.peer_exchange:
             self._peer = self._peer_buffers(B, N, dev, sizes)
+            if self._peer is not None and self._rows_peer is None and self.world <= 16:
+                self._rows_peer = self._peer_table()
         if self._peer is None:
             self._gathered = {k: torch.empty(self.world * B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
             self._gathered["pos"] = torch.empty((self.world * B, 3), dtype=torch.int64, device=dev)
@@ -150,6 +153,19 @@ class DataParallelStep:
         neg_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["neg"]) for b in bases])
         return {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs}
 
+    def _peer_table(self):
+        """Move the (replicated) entity table into symmetric memory, once: every rank can then store the rows it
+        owns straight into the other replicas from the Adam epilogue (kge_train_apply_peers)."""
+        import torch.distributed._symmetric_memory as symm
+        ent = self.model.entity_embedding
+        block = symm.empty(ent.numel(), dtype=torch.float32, device=ent.device)
+        block.copy_(ent.data.reshape(-1))
+        hdl = symm.rendezvous(block, self.group if self.group is not None else dist.group.WORLD)
+        ent.data = block.view(ent.shape)
+        bases = [int(p) for p in hdl.buffer_ptrs]
+        others = [bases[r] for r in range(self.world) if r != self.rank]
+        return {"hdl": hdl, "block": block, "ptrs": (C.c_void_p * len(others))(*[C.c_void_p(b) for b in others])}
+
     def _exchange(self, pos, neg):
         """kge_train_exchange + the barrier that orders every rank's apply after every rank's stores."""
         B, N = neg.shape
@@ -181,8 +197,10 @@ class DataParallelStep:
             self._sws = ws
         return ws
 
-    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None):
-        """kge_train_apply_parts on the rows ``[lo, hi)`` (default: everything this rank owns, all parts)."""
+    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None,
+               row_peers=None):
+        """kge_train_apply_peers on the rows ``[lo, hi)`` (default: everything this rank owns, all parts);
+        ``row_peers``: ctypes array of the other ranks' table pointers -- updated rows are stored there too."""
         m, opt = self.model, self.optimizer
         B_all, N = neg_all.shape
         ent, rel, mod = m.entity_embedding, m.relation_embedding, m._modulus()
@@ -195,13 +213,13 @@ class DataParallelStep:
         bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
         P = ops._ptr
         with torch.cuda.device(ent.device):
-            _lib.check(_lib.load().kge_train_apply_parts(
+            _lib.check(_lib.load().kge_train_apply_peers(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
                 P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
                 P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
                 C.byref(adam), C.byref(bufs), self.lo if lo is None else lo, self.hi if hi is None else hi, int(parts),
-                P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws), self._ws.numel(), ops._stream()),
-                "kge_train_apply_parts")
+                0 if row_peers is None else len(row_peers), row_peers, P(out), C.c_void_p(out.data_ptr() + 12),
+                P(self._ws), self._ws.numel(), ops._stream()), "kge_train_apply_peers")
 
     def _apply_overlapped(self, mode, pos_all, neg_all, loss_opts, adam, out):
         """Owner-parallel apply with the broadcast of the updated rows hidden behind it: the owned range is cut into
@@ -280,8 +298,12 @@ class DataParallelStep:
         b1, b2 = group_opts["betas"]
         adam = AdamOpts(float(group_opts["lr"]), float(b1), float(b2), float(group_opts["eps"]), int(states[0]["step"]), 0)
         out = torch.zeros(4, dtype=torch.float32, device=dev)
-        if (self.world > 1 and self.overlap_chunks > 1 and dev.type == "cuda"
-                and type(self)._apply is DataParallelStep._apply and type(self)._share_rows is DataParallelStep._share_rows):
+        plain = type(self)._apply is DataParallelStep._apply and type(self)._share_rows is DataParallelStep._share_rows
+        if self.world > 1 and plain and self._rows_peer is not None and reg == 0.0:
+            # the broadcast of the owned rows rides on the Adam epilogue as NVLink stores; one barrier closes the step
+            self._apply(mode, pos_all, neg_all, loss_opts, adam, out, row_peers=self._rows_peer["ptrs"])
+            self._rows_peer["hdl"].barrier()
+        elif self.world > 1 and self.overlap_chunks > 1 and dev.type == "cuda" and plain:
             self._apply_overlapped(mode, pos_all, neg_all, loss_opts, adam, out)
         else:
             self._apply(mode, pos_all, neg_all, loss_opts, adam, out)

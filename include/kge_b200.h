@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 4
+#define KGE_B200_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -290,6 +290,21 @@ KGE_API int kge_train_apply_parts(const kge_model_desc *desc, int mode, float *e
                                   const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
                                   const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
                                   float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/* kge_train_apply_parts that ALSO stores every updated entity row into `npeers` replicas of the table on other GPUs
+ * (`peer_entity`: HOST array of device pointers to the peers' tables, peer mappings valid on this GPU): the broadcast of
+ * the owned rows that has to follow kge_train_apply under data parallelism rides on the Adam epilogue as NVLink
+ * stores.  The caller puts a barrier across the ranks on the stream before anything reads the replicas.  With a
+ * non-zero `regularization` the L3 sum of PREPARE reads the whole local table, so the caller must keep the ranks from
+ * writing into it before every rank's PREPARE is done (dist.DataParallelStep falls back to a broadcast then). */
+KGE_API int kge_train_apply_peers(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
+                                  float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
+                                  float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus,
+                                  const int64_t *positive_all, const int64_t *negative_all, int64_t B_all, int64_t N,
+                                  const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
+                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
+                                  int npeers, float *const *peer_entity, float *loss3, float *reg1, void *ws,
+                                  size_t ws_bytes, void *stream);
 
 /*
  * Between kge_train_sweep and kge_train_apply: the exchange of the per-positive buffers over NVLink peer memory,

@@ -191,3 +191,32 @@ def test_peer_exchange_places_every_row_where_it_is_needed(world):
         lib_rc = lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[0]), ops._ptr(neg[0]), B, N, C.byref(loc), world, world,
                                         tables, ppos, pneg, ops._stream())
         _lib.check(lib_rc, "kge_train_exchange")
+
+
+def test_updated_rows_are_stored_into_the_replicas():
+    """kge_train_apply_peers: every updated entity row is also written to the peer tables (two extra buffers on the
+    same GPU stand in for the other ranks' replicas); rows outside the applied range stay as they were."""
+    import ctypes as C
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import dist as kd
+    E, R, H, B, N, lr = 90, 4, 16, 8, 11, 1e-3
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
+    m = _model("RotatE", E, R, H, seed=4)
+    before = m.entity_embedding.detach().clone()
+    replicas = [before.clone(), before.clone()]
+    lo, hi = 10, 70
+
+    class Peers(kd.DataParallelStep):
+        def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, **kw):
+            ptrs = (C.c_void_p * 2)(*[C.c_void_p(r.data_ptr()) for r in replicas])
+            super()._apply(mode, pos_all, neg_all, loss_opts, adam, out, lo=lo, hi=hi, row_peers=ptrs)
+
+    step = Peers(m, _adam(m, lr))
+    pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=8)
+    step.train_step(iter([(pos.cuda(), neg.cuda(), w.cuda(), mode)]), args)
+    now = m.entity_embedding.detach()
+    assert not torch.equal(now[lo:hi], before[lo:hi])
+    for r in replicas:
+        assert torch.equal(r[lo:hi], now[lo:hi])
+        assert torch.equal(r[:lo], before[:lo]) and torch.equal(r[hi:], before[hi:])
+    assert torch.equal(now[:lo], before[:lo]) and torch.equal(now[hi:], before[hi:])
