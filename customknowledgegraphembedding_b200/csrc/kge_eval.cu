@@ -7,11 +7,11 @@
 //
 //   1 stage      per query: the candidate-independent planes q (same maths as K1) -> workspace
 //   2 norms      InterHT only: 1/|a_e|, 1/|b_e| per entity
-//   3 true       per query: score of the true entity, accumulated k = 0..H-1 in order
+//   3 true       per query (one warp): score of the true entity, accumulated k = 0..H-1 in order
 //   4 tile       128 queries x 128 entities per CTA, 8x8 scores per thread, coordinates streamed
 //                through shared memory in chunks of 16 (k-major, register-staged double buffer);
 //                epilogue counts score > true / score == true, skipping the true entity itself
-//   5 filter     per filtered (query, entity) pair: undo its contribution to the counters
+//   5 filter     per filtered (query, entity) pair (one warp): undo its contribution to the counters
 //
 // Bit-consistency: 3, 4 and 5 evaluate a pair with the SAME instruction sequence (explicit
 // round-to-nearest intrinsics, no contraction freedom) in the SAME order, so the true entity
@@ -97,23 +97,70 @@ __device__ __forceinline__ float finalize(float acc, const EvalConsts& c) {
     else return __fsub_rn(c.gamma, acc);
 }
 
-// One thread, one (query, entity) pair, coordinates in ascending order: the reference order of K5.
+// One WARP, one (query, entity) pair, coordinates accumulated in ascending order: the reference order of K5 (what a
+// thread of the tile kernel does for each of its 64 pairs).  A single thread walking the two rows is a chain of H
+// dependent-latency global loads (measured 0.25 ms for the true scores and 0.69 ms for the filter entries of 2048
+// queries at H = 1000).  Here the lanes read both rows coalesced and evaluate the per-coordinate term -- the value
+// accum<> adds, which does not depend on the running sum -- into a warp-private shared-memory strip; lane 0 then adds
+// the terms in ascending k with the same __fadd_rn chain.  DistMult / ComplEx accumulate through fma(q, c, acc), whose
+// product is not rounded on its own: for them the strip holds the operands and lane 0 runs the fma chain.
+constexpr int kPairChunk = 1024;  // coordinates per strip pass (bounds shared memory whatever H is)
+constexpr int kPairWarps = 4;
+template <int MODEL>
+__host__ __device__ constexpr int pair_strips() { return MODEL == KGE_DISTMULT ? 2 : (MODEL == KGE_COMPLEX ? 4 : 1); }
+template <int MODEL>
+constexpr size_t pair_smem() { return (size_t)kPairWarps * pair_strips<MODEL>() * kPairChunk * sizeof(float); }
+
 template <int MODEL, bool HEAD>
-__device__ __forceinline__ float pair_score_seq(const float* __restrict__ qrow, const float* __restrict__ erow, int H,
-                                                const EvalConsts& c, float ina, float inb) {
+__device__ __forceinline__ float pair_score_warp(const float* __restrict__ qrow, const float* __restrict__ erow, int H,
+                                                 const EvalConsts& c, float ina, float inb, float* __restrict__ strip) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes(MODEL);
+    const int lane = threadIdx.x & 31;
     float acc = 0.f;
-    for (int k = 0; k < H; ++k) {
-        const float q0 = qrow[k];
-        const float q1 = (QP > 1) ? qrow[H + k] : 0.f;
-        const float q2 = (QP > 2) ? qrow[2 * H + k] : 0.f;
-        const float x0 = __ldg(erow + k);
-        const float x1 = (CP > 1) ? __ldg(erow + H + k) : 0.f;
-        float c0, c1;
-        prep_candidate<MODEL>(c0, c1, x0, x1, c.inv_phase_div, ina, inb);
-        acc = accum<MODEL, HEAD>(acc, q0, q1, q2, c0, c1);
+    for (int k0 = 0; k0 < H; k0 += kPairChunk) {
+        const int n = min(kPairChunk, H - k0);
+        for (int i = lane; i < n; i += 32) {
+            const int k = k0 + i;
+            const float q0 = qrow[k];
+            const float q1 = (QP > 1) ? qrow[H + k] : 0.f;
+            const float q2 = (QP > 2) ? qrow[2 * H + k] : 0.f;
+            const float x0 = __ldg(erow + k);
+            const float x1 = (CP > 1) ? __ldg(erow + H + k) : 0.f;
+            float c0, c1;
+            prep_candidate<MODEL>(c0, c1, x0, x1, c.inv_phase_div, ina, inb);
+            if constexpr (MODEL == KGE_DISTMULT) {
+                strip[i] = q0;
+                strip[kPairChunk + i] = c0;
+            } else if constexpr (MODEL == KGE_COMPLEX) {
+                strip[i] = q0;
+                strip[kPairChunk + i] = c0;
+                strip[2 * kPairChunk + i] = q1;
+                strip[3 * kPairChunk + i] = c1;
+            } else {
+                // accum<>(0, ...) == +0 + term == term for every term these models produce (|x|, sqrt: never -0)
+                strip[i] = accum<MODEL, HEAD>(0.f, q0, q1, q2, c0, c1);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            if constexpr (MODEL == KGE_DISTMULT) {
+                for (int i = 0; i < n; ++i) acc = __fmaf_rn(strip[i], strip[kPairChunk + i], acc);
+            } else if constexpr (MODEL == KGE_COMPLEX) {
+                for (int i = 0; i < n; ++i)
+                    acc = __fmaf_rn(strip[2 * kPairChunk + i], strip[3 * kPairChunk + i],
+                                    __fmaf_rn(strip[i], strip[kPairChunk + i], acc));
+            } else {
+                int i = 0;
+                for (; i + 4 <= n; i += 4) {
+                    const float4 t = *reinterpret_cast<const float4*>(strip + i);
+                    acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, t.x), t.y), t.z), t.w);
+                }
+                for (; i < n; ++i) acc = __fadd_rn(acc, strip[i]);
+            }
+        }
+        __syncwarp();
     }
-    return finalize<MODEL>(acc, c);
+    return __shfl_sync(0xffffffffu, finalize<MODEL>(acc, c), 0);
 }
 
 // ---- 1 stage ---------------------------------------------------------------------------------
@@ -201,66 +248,62 @@ eval_true_norm_kernel(Params P, const float* __restrict__ ent, const float* __re
 }
 
 template <int MODEL, bool HEAD>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(32 * kPairWarps)
 eval_true_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
                  const float* __restrict__ qrows, const float* __restrict__ Qs, const float* __restrict__ tna,
                  const float* __restrict__ tnb, const int64_t* __restrict__ queries, long long Q,
                  float* __restrict__ true_score) {
-    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    extern __shared__ __align__(16) float smem[];
+    float* strip = smem + (size_t)(threadIdx.x >> 5) * pair_strips<MODEL>() * kPairChunk;
+    const long long q = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);  // one warp per query
     if (q >= Q) return;
     if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
     const int qdim = model_planes(MODEL) * P.H;
     const float a = (MODEL == KGE_INTERHT) ? tna[q] : 0.f, b = (MODEL == KGE_INTERHT) ? tnb[q] : 0.f;
-    true_score[q] = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, true_row<HEAD>(P, ent, qrows, queries, q), P.H, c, a, b);
+    const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, true_row<HEAD>(P, ent, qrows, queries, q), P.H, c, a, b, strip);
+    if ((threadIdx.x & 31) == 0) true_score[q] = s;
 }
 
 // ---- 5 filter --------------------------------------------------------------------------------
+// one warp per filter entry (grid-stride; the number of entries lives on the device)
 template <int MODEL, bool HEAD>
-__device__ __forceinline__ void filter_one(long long f, const Params& P, const EvalConsts& c, const float* __restrict__ ent,
-                   const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
-                   const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
-                   const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
-                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal);
-
-template <int MODEL, bool HEAD>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(32 * kPairWarps)
 eval_filter_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
                    const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
                    const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
                    const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
                    const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+    extern __shared__ __align__(16) float smem[];
+    float* strip = smem + (size_t)(threadIdx.x >> 5) * pair_strips<MODEL>() * kPairChunk;
+    const int lane = threadIdx.x & 31;
     const long long total = indptr[Q];
     if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
-    for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x)
-        filter_one<MODEL, HEAD>(f, P, c, ent, Qs, ina, inb, queries, Q, indptr, idx, e_lo, e_hi, true_score, n_greater, n_equal);
-}
-
-template <int MODEL, bool HEAD>
-__device__ __forceinline__ void filter_one(long long f, const Params& P, const EvalConsts& c, const float* __restrict__ ent,
-                   const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
-                   const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
-                   const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
-                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
-    // query owning entry f: last q with indptr[q] <= f
-    long long lo = 0, hi = Q;
-    while (hi - lo > 1) {
-        const long long mid = (lo + hi) >> 1;
-        if (indptr[mid] <= f) lo = mid;
-        else hi = mid;
-    }
-    const long long q = lo;
-    const long long e = idx[f];
-    const long long te = HEAD ? queries[3 * q] : queries[3 * q + 2];
-    if (e == te || e < e_lo || e >= e_hi) return;
-    // a candidate listed twice must be undone once: only its first occurrence in the row acts
-    for (long long j = indptr[q]; j < f; ++j)
-        if (idx[j] == e) return;
     const int qdim = model_planes(MODEL) * P.H;
-    const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
-    const float s = pair_score_seq<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b);
-    const float t = true_score[q];
-    if (s > t) atomicAdd(n_greater + q, ~0ULL);      // -1
-    else if (s == t) atomicAdd(n_equal + q, ~0ULL);  // -1
+    for (long long f = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5); f < total;
+         f += (long long)gridDim.x * kPairWarps) {
+        // query owning entry f: last q with indptr[q] <= f
+        long long lo = 0, hi = Q;
+        while (hi - lo > 1) {
+            const long long mid = (lo + hi) >> 1;
+            if (indptr[mid] <= f) lo = mid;
+            else hi = mid;
+        }
+        const long long q = lo;
+        const long long e = idx[f];
+        const long long te = HEAD ? queries[3 * q] : queries[3 * q + 2];
+        if (e == te || e < e_lo || e >= e_hi) continue;
+        // a candidate listed twice must be undone once: only its first occurrence in the row acts
+        bool dup = false;
+        for (long long j = indptr[q] + lane; j < f; j += 32) dup |= (idx[j] == e);
+        if (__any_sync(0xffffffffu, dup)) continue;
+        const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
+        const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b, strip);
+        if (lane == 0) {
+            const float t = true_score[q];
+            if (s > t) atomicAdd(n_greater + q, ~0ULL);      // -1
+            else if (s == t) atomicAdd(n_equal + q, ~0ULL);  // -1
+        }
+    }
 }
 
 // ---- 4 tile ----------------------------------------------------------------------------------
@@ -473,8 +516,13 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
         }
         eval_true_norm_kernel<HEAD><<<(unsigned)((Q * 32 + 255) / 256), 256, 0, st>>>(P, ent, qrows, queries, Q, tna, tnb);
     }
-    eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + 127) / 128), 128, 0, st>>>(P, c, modulus, ent, qrows, Qs, tna, tnb,
-                                                                             queries, Q, true_score);
+    constexpr size_t smem_pair = pair_smem<MODEL>();
+    if (smem_pair > 48 * 1024) {
+        cudaFuncSetAttribute(eval_true_kernel<MODEL, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pair);
+        cudaFuncSetAttribute(eval_filter_kernel<MODEL, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pair);
+    }
+    eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + kPairWarps - 1) / kPairWarps), 32 * kPairWarps, smem_pair, st>>>(
+        P, c, modulus, ent, qrows, Qs, tna, tnb, queries, Q, true_score);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (e_hi > e_lo) {
         constexpr size_t smem = eval_tile_smem<MODEL>();
@@ -486,8 +534,8 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
     }
     if (indptr != nullptr && idx != nullptr) {
         // the number of filter entries lives on the device (indptr[Q]): grid-stride over it, no host sync
-        eval_filter_kernel<MODEL, HEAD><<<4 * sm_count(), 128, 0, st>>>(P, c, modulus, ent, Qs, ina, inb, queries, Q, indptr,
-                                                                      idx, e_lo, e_hi, true_score, n_greater, n_equal);
+        eval_filter_kernel<MODEL, HEAD><<<8 * sm_count(), 32 * kPairWarps, smem_pair, st>>>(
+            P, c, modulus, ent, Qs, ina, inb, queries, Q, indptr, idx, e_lo, e_hi, true_score, n_greater, n_equal);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     return cudaSuccess;

@@ -14,11 +14,11 @@ enum Stage {
 static const char* const kStageNames[ST_COUNT] = {
     "zero_grad", "score_forward(neg)", "score_forward(pos)", "loss", "score_backward(neg)", "score_backward(pos)",
     "l3_reg", "adam(entity)", "adam(relation+modulus)",
-    "fused_sweep(scores+loss+dL/dq)", "buckets(scan+fill+sort)", "dscore+loss_final", "entity_gather+adam",
+    "fused_sweep(scores+loss+dL/dq)", "buckets(scan+fill+sort)", "loss_final", "entity_gather+adam",
     "relation_gather+adam"};
 // kernels launched per stage (memsets are not kernels); a scope whose count depends on the path taken overrides it
 // through ProfScope::launches
-static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1, 1, 5, 2, 1, 1};
+static const int kStageLaunches[ST_COUNT] = {0, 1, 1, 2, 1, 1, 5, 1, 1, 1, 5, 1, 1, 1};
 
 struct ProfRec {
     int stage;

@@ -30,6 +30,7 @@
 #include "kge_prof.h"
 #include "kge_ptx.cuh"
 #include "kge_train.h"
+#include <type_traits>
 
 namespace kge {
 
@@ -64,6 +65,11 @@ __device__ __forceinline__ void load_coords(float (&x)[CP][CH][4], const float* 
             if (k0 < H) val = __ldg(reinterpret_cast<const float4*>(row + p * plane_stride + k0));
             x[p][j][0] = val.x; x[p][j][1] = val.y; x[p][j][2] = val.z; x[p][j][3] = val.w;
         }
+}
+
+// dL/ds of one negative score: scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s) without -adv)
+__device__ __forceinline__ float dscore_value(float s, float m_b, float scale_b, int adv, float alpha) {
+    return adv ? scale_b * expf(s * alpha - m_b) * sigmoidf(s) : scale_b * sigmoidf(s);
 }
 
 struct SweepArgs {
@@ -368,6 +374,13 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     const float negterm = sh_fin[2] / denom;
     const float scale_b = 0.5f * coef / denom;  // dL/ds_n = scale_b * e_n * sigma(s_n)
     const float gsum = sh_fin[3];
+    // F2b folded in: S[b,:] <- dL/ds.  The raw scores are not read again by anybody; every later consumer (the entity
+    // kernel of this rank, or of the row owners after the exchange) wants the derivative, and here the work stays with
+    // the rank that owns the positive instead of being repeated on the global batch by every rank.
+    for (int n = tid; n < N; n += T) {
+        const long long i = b * N + n;
+        A.S[i] = dscore_value(A.S[i], m_b, scale_b, A.adv, A.alpha);
+    }
     // dL/dq of the negative part
 #pragma unroll
     for (int p = 0; p < QP; ++p)
@@ -786,18 +799,6 @@ bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, 
     }
 }
 
-// F2b: S[b,n] <- dL/ds[b,n] = scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s))
-__global__ void __launch_bounds__(256)
-dscore_kernel(float* __restrict__ S, const float* __restrict__ stats, long long BN, int N, int adv, float alpha) {
-    pdl_enter();
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < BN; i += (long long)gridDim.x * blockDim.x) {
-        const long long b = i / N;
-        const float s = S[i];
-        const float sc = stats[2 * b + 1];
-        S[i] = adv ? sc * expf(s * alpha - stats[2 * b]) * sigmoidf(s) : sc * sigmoidf(s);
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // F3: entity-major gradient gather fused with Adam
 // ------------------------------------------------------------------------------------------------
@@ -831,7 +832,15 @@ __device__ __forceinline__ void relation_row_update(long long r, int Dr, const i
     const int nm = *nmatch;
     for (int k = threadIdx.x; k < Dr; k += blockDim.x) {
         float g = 0.f;
-        for (int j = 0; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
+        int j = 0;
+        for (; j + 8 <= nm; j += 8) {  // eight independent loads in flight; the additions keep the ascending order
+            float x[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) x[u] = GR[(long long)match[j + u] * Dr + k];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) g += x[u];
+        }
+        for (; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
         const long long i = r * Dr + k;
         float pp = rel[i], mm = m[i], vv = v[i];
         adam_update(pp, g, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
@@ -858,11 +867,16 @@ struct EntityArgs {
     int N;
     long long BN, B;
     long long e_lo, e_hi;  // rows this rank owns
-    // replicas of the table on the other ranks (peer mappings): the updated row is stored there as well, so that the
-    // broadcast of the owned rows rides on the Adam epilogue instead of following it
+};
+// replicas of the table on the other ranks (peer mappings): the updated row is stored there as well, so that the
+// broadcast of the owned rows rides on the Adam epilogue instead of following it.  A separate, LAST kernel parameter
+// that is an empty struct in the single-GPU instantiation: with the pointer table inside EntityArgs the parameter
+// block grew by 128 bytes and ptxas' different allocation for the very same loop cost 13 % (0.240 -> 0.269 ms).
+struct EntityPeers {
     int npeers;
     float* peer[kMaxRowPeers];
 };
+struct NoPeers {};
 
 // One use of the row by a negative slot: gc += dL/ds * ds/dc, with q of the using positive.
 template <int MODEL, int CH, bool HEAD>
@@ -922,10 +936,13 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-template <int MODEL, int CH, bool HEAD, int TMAX>
+// PEERS: the multi-GPU instantiation that also stores the updated row into the other ranks' replicas.  It is a template
+// parameter because the mere presence of the (empty) peer loop in the Adam epilogue cost the single-GPU kernel 13 %
+// (0.237 -> 0.269 ms: stores through unknown pointers between the m / v loads of consecutive chunks).
+template <int MODEL, int CH, bool HEAD, int TMAX, bool PEERS>
 __global__ void __launch_bounds__(TMAX, TMAX == 128 ? 6 : 2)
 train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ modulus, EntityArgs A, AdamScalars ad,
-                         float l3) {
+                         float l3, std::conditional_t<PEERS, EntityPeers, NoPeers> X) {
     pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
     __shared__ float red[2 * 32];
@@ -1105,14 +1122,28 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
                     adam_update(c[p][j][1], gc[p][j][1], mm.y, vv.y, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
                     adam_update(c[p][j][2], gc[p][j][2], mm.z, vv.z, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
                     adam_update(c[p][j][3], gc[p][j][3], mm.w, vv.w, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
-                    const float4 upd = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
-                    *reinterpret_cast<float4*>(row + p * H + k0) = upd;
+                    *reinterpret_cast<float4*>(row + p * H + k0) = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
                     *reinterpret_cast<float4*>(mrow + p * H + k0) = mm;
                     *reinterpret_cast<float4*>(vrow + p * H + k0) = vv;
-                    for (int q = 0; q < A.npeers; ++q)  // NVLink stores into the other ranks' replicas
-                        *reinterpret_cast<float4*>(A.peer[q] + e * (long long)P.De + p * H + k0) = upd;
                 }
             }
+        if constexpr (PEERS) {
+            // NVLink stores into the other ranks' replicas, after the local row / m / v traffic has been issued: the
+            // updated row is still in registers
+#pragma unroll
+            for (int q = 0; q < kMaxRowPeers; ++q) {  // constant indices: the pointer table stays in the parameter bank
+                if (q >= X.npeers) break;
+                float* prow = X.peer[q] + e * (long long)P.De;
+#pragma unroll
+                for (int p = 0; p < CP; ++p)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        const int k0 = 4 * (tid + j * T);
+                        if (k0 < H)
+                            *reinterpret_cast<float4*>(prow + p * H + k0) = make_float4(c[p][j][0], c[p][j][1], c[p][j][2], c[p][j][3]);
+                    }
+            }
+        }
     }
 }
 
@@ -1304,11 +1335,11 @@ static cudaError_t launch_sweep_rows(const Params& P, const CoordConsts& kc, boo
     }
 }
 
-template <int MODEL, int ECH, bool HEAD, int TMAX>
+template <int MODEL, int ECH, bool HEAD, int TMAX, bool PEERS>
 static cudaError_t launch_entity_inst(const Params& P, const CoordConsts& kc, const float* modulus, const EntityArgs& A,
-                                      const AdamScalars& ad, float l3, int ethreads, cudaStream_t st) {
+                                      const EntityPeers& X, const AdamScalars& ad, float l3, int ethreads, cudaStream_t st) {
     cudaError_t e;
-    auto kernel = train_entity_adam_kernel<MODEL, ECH, HEAD, TMAX>;
+    auto kernel = train_entity_adam_kernel<MODEL, ECH, HEAD, TMAX, PEERS>;
     const size_t ring_bytes = (MODEL == KGE_INTERHT) ? 0 : (size_t)kRing * model_planes(MODEL) * ECH * ethreads * sizeof(float4);
     static size_t allowed = 0;
     if (ring_bytes > 40 * 1024 && allowed < ring_bytes) {  // static shared memory counts towards the 48 KB default
@@ -1322,18 +1353,20 @@ static cudaError_t launch_entity_inst(const Params& P, const CoordConsts& kc, co
         resident_for = ethreads;
     }
     const int blocks = (int)std::min<long long>(A.e_hi - A.e_lo, (long long)std::max(1, resident_cached) * sm_count());
-    return launch_pdl(kernel, dim3(blocks), dim3(ethreads), ring_bytes, st, P, kc, modulus, A, ad, l3);
+    if constexpr (PEERS) return launch_pdl(kernel, dim3(blocks), dim3(ethreads), ring_bytes, st, P, kc, modulus, A, ad, l3, X);
+    else return launch_pdl(kernel, dim3(blocks), dim3(ethreads), ring_bytes, st, P, kc, modulus, A, ad, l3, NoPeers{});
 }
 
 template <int MODEL, int ECH>
 static cudaError_t launch_entity(const Params& P, const CoordConsts& kc, int head, const float* modulus, const EntityArgs& A,
-                                 const AdamScalars& ad, float l3, cudaStream_t st) {
+                                 const EntityPeers& X, const AdamScalars& ad, float l3, cudaStream_t st) {
     const int ethreads = std::max(32, (((P.H / 4 + ECH - 1) / ECH + 31) / 32) * 32);
-    if (ethreads <= 128)
-        return head ? launch_entity_inst<MODEL, ECH, true, 128>(P, kc, modulus, A, ad, l3, ethreads, st)
-                    : launch_entity_inst<MODEL, ECH, false, 128>(P, kc, modulus, A, ad, l3, ethreads, st);
-    return head ? launch_entity_inst<MODEL, ECH, true, 256>(P, kc, modulus, A, ad, l3, ethreads, st)
-                : launch_entity_inst<MODEL, ECH, false, 256>(P, kc, modulus, A, ad, l3, ethreads, st);
+#define KGE_ENT(HD, TM)                                                                                       \
+    (X.npeers > 0 ? launch_entity_inst<MODEL, ECH, HD, TM, true>(P, kc, modulus, A, X, ad, l3, ethreads, st)   \
+                  : launch_entity_inst<MODEL, ECH, HD, TM, false>(P, kc, modulus, A, X, ad, l3, ethreads, st))
+    if (ethreads <= 128) return head ? KGE_ENT(true, 128) : KGE_ENT(false, 128);
+    return head ? KGE_ENT(true, 256) : KGE_ENT(false, 256);
+#undef KGE_ENT
 }
 
 template <int MODEL, int CH, int RPI>
@@ -1400,9 +1433,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         }
         {
             ProfScope ps(ST_DSCORE, st);
-            const int db = (int)std::min<long long>((BN + 255) / 256, 8LL * sm_count());
-            if ((e = launch_pdl(dscore_kernel, dim3(db), dim3(256), 0, st, fc.S, fc.stats, BN, (int)N,
-                                lo.negative_adversarial_sampling, lo.adversarial_temperature)) != cudaSuccess) return e;
+            // (S already holds dL/ds: the sweep's last pass writes it per positive)
             if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(256), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
@@ -1417,10 +1448,11 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     if ((fc.parts & 2) && fc.e_hi > fc.e_lo) {
         ProfScope ps(ST_ENTITY, st);
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
-                     fc.e_lo, fc.e_hi, fc.npeers, {}};
-        for (int q = 0; q < fc.npeers; ++q) A.peer[q] = fc.peers[q];
+                     fc.e_lo, fc.e_hi};
+        EntityPeers X{fc.npeers, {}};
+        for (int q = 0; q < fc.npeers; ++q) X.peer[q] = fc.peers[q];
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
-        if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, ad, l3, st)) != cudaSuccess) return e;
+        if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, X, ad, l3, st)) != cudaSuccess) return e;
     }
     if (fc.parts & 4) {
         // relation rows and the modulus are replicated: every rank applies the same fixed-order update.  (Folding the

@@ -243,12 +243,12 @@ KGE_API int kge_train_set_sweep_variant(int variant);
  * The step shards twice: positives are data-parallel in the SWEEP, entity rows are owner-parallel in the APPLY.
  *
  *   kge_train_sweep  : scores, loss terms and dL/dq for the B LOCAL positives; writes the per-positive buffers
- *                      (S [B,N] scores, Q [B,planes*H] staged planes, GH/GT [B,De], GR [B,Dr] compact gradient
+ *                      (S [B,N] dL/dscore of the negatives, Q [B,planes*H] staged planes, GH/GT [B,De], GR [B,Dr] compact gradient
  *                      rows, GM [B], stats [B,2], terms [B,2]).  wsum: device scalar = sum of the subsampling
  *                      weights over the GLOBAL batch (all-reduced by the caller; NULL = local sum);
  *                      B_total = positives of the global batch (uniform weighting).
  *   (caller)         : all-gather every buffer, positive and negative over the ranks -> B_all = sum of B.
- *   kge_train_apply  : on the gathered buffers: dL/ds, the per-entity use lists, then for the entity rows
+ *   kge_train_apply  : on the gathered buffers: the per-entity use lists, then for the entity rows
  *                      [entity_lo, entity_hi) this rank owns: gradient gather + Adam (m, v of other rows are not
  *                      touched); relation rows and the pRotatE modulus are replicated and updated identically on
  *                      every rank (fixed summation order).  loss3 / reg1 as in kge_train_step.
@@ -275,8 +275,8 @@ KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity,
 
 /* kge_train_apply in pieces, so that the caller can put communication between them (dist.DataParallelStep broadcasts
  * the rows of one chunk while the next chunk is being updated).  `parts` is a subset of:
- *   KGE_APPLY_PREPARE  bucket build for the rows [entity_lo, entity_hi) (must cover every later ROWS range), S <- dL/ds
- *                      in place, loss3 / reg1 (exactly once, first);
+ *   KGE_APPLY_PREPARE  bucket build for the rows [entity_lo, entity_hi) (must cover every later ROWS range),
+ *                      loss3 / reg1 (exactly once, first);
  *   KGE_APPLY_ROWS     gradient gather + Adam for the entity rows [entity_lo, entity_hi) (any number of calls over
  *                      disjoint ranges; needs the workspace PREPARE left behind);
  *   KGE_APPLY_FINISH   relation rows + pRotatE modulus (exactly once, after the last ROWS call: pRotatE's entity
