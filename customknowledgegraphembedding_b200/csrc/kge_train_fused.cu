@@ -167,15 +167,18 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
 #pragma unroll
                 for (int p = 0; p < QP; ++p) q[p][j][i] = qq[p];
             }
+        {  // (the merge pass rewrites the Q[b] the staging pass wrote: the store leaves the row in L2 for the entity
+           //  kernel that follows -- without it that kernel measured 4 us slower, more than the store costs)
 #pragma unroll
-        for (int p = 0; p < QP; ++p)
+            for (int p = 0; p < QP; ++p)
 #pragma unroll
-            for (int j = 0; j < CH; ++j) {
-                const int k0 = 4 * (tid + j * T);
-                if (k0 < H)
-                    *reinterpret_cast<float4*>(A.Q + (b * QP + p) * H + k0) =
-                        make_float4(q[p][j][0], q[p][j][1], q[p][j][2], q[p][j][3]);
-            }
+                for (int j = 0; j < CH; ++j) {
+                    const int k0 = 4 * (tid + j * T);
+                    if (k0 < H)
+                        *reinterpret_cast<float4*>(A.Q + (b * QP + p) * H + k0) =
+                            make_float4(q[p][j][0], q[p][j][1], q[p][j][2], q[p][j][3]);
+                }
+        }
     }
 
     if constexpr (PART == 1) {  // staging pass of the split sweep: Q[b] is all F1w needs
@@ -340,24 +343,43 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         z_run = zl[0];
         l_run = zl[1];
         g_run = 0.f;
-        for (int p = 0; p < A.parts; ++p) {  // fixed order: bit-reproducible
-            const long long item = b * A.parts + p;
-            const float mp = __ldg(A.PM + 2 * item);
-            const float f = A.adv ? ((mp == -INFINITY) ? 0.f : expf(mp - m)) : 1.0f;
-            g_run = fmaf(__ldg(A.PM + 2 * item + 1), f, g_run);
+        // fixed order: bit-reproducible.  The partials of four items are requested together (they do not depend on
+        // one another: one L2 round trip instead of four), then folded in ascending order.
+        constexpr int MU = (CH == 1) ? 4 : 2;
+        for (int p0 = 0; p0 < A.parts; p0 += MU) {
+            float4 v[MU][QP][CH];
+            float mp[MU], gp[MU];
 #pragma unroll
-            for (int pl = 0; pl < QP; ++pl)
+            for (int u = 0; u < MU; ++u) {
+                const long long item = b * A.parts + min(p0 + u, A.parts - 1);
+                mp[u] = __ldg(A.PM + 2 * item);
+                gp[u] = __ldg(A.PM + 2 * item + 1);
 #pragma unroll
-                for (int j = 0; j < CH; ++j) {
-                    const int k0 = 4 * (tid + j * T);
-                    if (k0 < H) {
-                        const float4 v = __ldg(reinterpret_cast<const float4*>(A.PA + (item * QP + pl) * H + k0));
-                        acc[pl][j][0] = fmaf(v.x, f, acc[pl][j][0]);
-                        acc[pl][j][1] = fmaf(v.y, f, acc[pl][j][1]);
-                        acc[pl][j][2] = fmaf(v.z, f, acc[pl][j][2]);
-                        acc[pl][j][3] = fmaf(v.w, f, acc[pl][j][3]);
+                for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        const int k0 = 4 * (tid + j * T);
+                        v[u][pl][j] = (k0 < H) ? __ldg(reinterpret_cast<const float4*>(A.PA + (item * QP + pl) * H + k0))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
-                }
+            }
+#pragma unroll
+            for (int u = 0; u < MU; ++u) {
+                if (p0 + u >= A.parts) break;
+                const float f = A.adv ? ((mp[u] == -INFINITY) ? 0.f : expf(mp[u] - m)) : 1.0f;
+                g_run = fmaf(gp[u], f, g_run);
+#pragma unroll
+                for (int pl = 0; pl < QP; ++pl)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        if (4 * (tid + j * T) < H) {
+                            acc[pl][j][0] = fmaf(v[u][pl][j].x, f, acc[pl][j][0]);
+                            acc[pl][j][1] = fmaf(v[u][pl][j].y, f, acc[pl][j][1]);
+                            acc[pl][j][2] = fmaf(v[u][pl][j].z, f, acc[pl][j][2]);
+                            acc[pl][j][3] = fmaf(v[u][pl][j].w, f, acc[pl][j][3]);
+                        }
+                    }
+            }
         }
     }
 
