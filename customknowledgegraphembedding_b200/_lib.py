@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
 
 # kge_model_id / kge_mode / kge_ws_kind
@@ -82,6 +82,8 @@ PROTOTYPES = {
                                  C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _P, _SZ, _P]),
     "kge_train_step_host": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                       C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _SZ, _P]),
+    "kge_stage_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _P]),
+    "kge_fetch_floats": (C.c_int, [_P, _P, _I64, _P]),
     "kge_train_sweep": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
                                   C.POINTER(StepBuffers), _P, _SZ, _P]),
     "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,

@@ -350,6 +350,30 @@ int kge_train_exchange(const kge_model_desc* desc, const int64_t* positive, cons
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_exchange");
 }
 
+int kge_stage_batch(const int64_t* host_positive, const int64_t* host_negative, const float* host_subsampling_weight,
+                    int64_t* dev_positive, int64_t* dev_negative, float* dev_subsampling_weight, int64_t B, int64_t N,
+                    void* stream) {
+    if (!host_positive || !host_negative || !dev_positive || !dev_negative) return fail(KGE_ERR_INVALID_ARGUMENT, "NULL pointer");
+    if ((host_subsampling_weight == nullptr) != (dev_subsampling_weight == nullptr))
+        return fail(KGE_ERR_INVALID_ARGUMENT, "subsampling weight: host and device pointers must both be given or both be NULL");
+    if (B < 0 || N < 1) return fail(KGE_ERR_INVALID_ARGUMENT, "bad batch shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemcpyAsync(dev_positive, host_positive, (size_t)B * 3 * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(dev_negative, host_negative, (size_t)B * N * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && host_subsampling_weight)
+        e = cudaMemcpyAsync(dev_subsampling_weight, host_subsampling_weight, (size_t)B * sizeof(float), cudaMemcpyHostToDevice, st);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_stage_batch");
+}
+
+int kge_fetch_floats(float* host_dst, const float* dev_src, int64_t n, void* stream) {
+    if (!host_dst || !dev_src || n < 0) return fail(KGE_ERR_INVALID_ARGUMENT, "bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemcpyAsync(host_dst, dev_src, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_fetch_floats");
+}
+
 int kge_train_set_sweep_variant(int variant) {
     train_set_sweep_variant(variant);
     return KGE_OK;

@@ -96,6 +96,18 @@ class KGEModel(nn.Module):
         self._plan_key, self._plan_ok = None, False
         self._filter_cache = None
         self.last_eval = {}
+        # train_step input lookahead: while the GPU runs step k, batch k+1 is taken from the iterator and copied to the
+        # device on a side stream (see _fused_step).  Set to False for the strictly sequential upstream behaviour.
+        self.input_lookahead = True
+        self._ahead = {}     # id(iterator) -> (iterator, batch, staged device copy or None); holding the iterator pins its id
+        self._stage = None   # copy stream and the pool of staging buffer sets
+        self._loss_dev = self._loss_host = None
+
+    def __getstate__(self):
+        # streams, events, staged batches and workspaces are per-process scratch: never pickled / deep-copied
+        d = self.__dict__.copy()
+        d.update(_ahead={}, _stage=None, _ws={}, _loss_dev=None, _loss_host=None)
+        return d
 
     # ------------------------------------------------------------------------------------
     def _scalar(self, name: str) -> float:
@@ -181,7 +193,11 @@ class KGEModel(nn.Module):
     def train_step(model, optimizer, train_iterator, args):
         """A single train step: apply back-propagation and return the loss log (same keys as upstream)."""
         model.train()
-        positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
+        ahead, staged = model._ahead.pop(id(train_iterator), None) if model._ahead else None, None
+        if ahead is not None:  # taken from this iterator during its previous step
+            (positive_sample, negative_sample, subsampling_weight, mode), staged = ahead[1], ahead[2]
+        else:
+            positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
         if mode not in ("head-batch", "tail-batch"):
             raise ValueError("mode %s not supported" % mode)
         adv = bool(getattr(args, "negative_adversarial_sampling", False))
@@ -198,16 +214,61 @@ class KGEModel(nn.Module):
                                              adv, alpha, uni, reg)
 
         out = model._fused_step(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
-                                adv, alpha, uni, reg)
+                                adv, alpha, uni, reg, staged=staged,
+                                lookahead=train_iterator if model.input_lookahead else None)
         pos_l, neg_l, loss, regv = out.tolist() if isinstance(out, torch.Tensor) else (float(x) for x in out)
         log = {"regularization": regv} if reg != 0.0 else {}
         log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
         return log
 
+    # ---- input lookahead -------------------------------------------------------------------------
+    def _stage_host_batch(self, lib, positive_sample, negative_sample, subsampling_weight, uni, dev):
+        """H2D copies of one host batch on the copy stream into a free set of staging buffers (kge_stage_batch);
+        returns (pos, neg, w or None, event, host sources).  A set goes back to the pool when the step that read it
+        has had its loss read back (a stream synchronisation): one set per batch in flight plus the one in use."""
+        pos = positive_sample.contiguous()
+        neg = negative_sample.contiguous()
+        if pos.dtype != torch.int64 or neg.dtype != torch.int64:
+            raise TypeError("positive_sample / negative_sample must be int64")
+        w = None if uni else subsampling_weight.to(torch.float32).contiguous()
+        B, N = neg.shape
+        st = self._stage
+        key = (B, N, dev, bool(uni))
+        if st is None or st["dev"] != dev:
+            stream = torch.cuda.Stream(dev)
+            st = self._stage = {"dev": dev, "stream": stream, "stream_ptr": C.c_void_p(stream.cuda_stream), "key": key, "free": []}
+        if st["key"] != key:
+            st["key"], st["free"] = key, []
+        if st["free"]:
+            dpos, dneg, dw, ev = st["free"].pop()
+        else:
+            dpos = torch.empty((B, 3), dtype=torch.int64, device=dev)
+            dneg = torch.empty((B, N), dtype=torch.int64, device=dev)
+            dw = None if uni else torch.empty(B, dtype=torch.float32, device=dev)
+            ev = torch.cuda.Event()
+        _lib.check(lib.kge_stage_batch(C.c_void_p(pos.data_ptr()), C.c_void_p(neg.data_ptr()),
+                                       None if w is None else C.c_void_p(w.data_ptr()), ops._ptr(dpos), ops._ptr(dneg),
+                                       ops._ptr(dw), B, N, st["stream_ptr"]), "kge_stage_batch")
+        ev.record(st["stream"])
+        return dpos, dneg, dw, ev, (pos, neg, w), key  # (the host sources stay alive with the tuple)
+
+    def _take_ahead(self, lib, iterator, uni, dev):
+        """``next(iterator)`` one step early, its H2D copies queued behind nothing but themselves."""
+        try:
+            batch = next(iterator)
+        except StopIteration:
+            return  # an exhausted iterator raises again on the next call's own next(): nothing to remember
+        staged = None
+        if (isinstance(batch[0], torch.Tensor) and not batch[0].is_cuda and batch[3] in ("head-batch", "tail-batch")):
+            staged = self._stage_host_batch(lib, batch[0], batch[1], batch[2], uni, dev)
+        self._ahead[id(iterator)] = (iterator, batch, staged)
+
     def _fused_step(self, optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
-                    adv, alpha, uni, reg, detach_weights=True, keras_adam=False):
+                    adv, alpha, uni, reg, detach_weights=True, keras_adam=False, staged=None, lookahead=None):
         """One call into kge_train_step(_host).  Batch on the host -> copies inside the C call, returns a numpy
-        [pos_loss, neg_loss, loss, reg]; batch on the device -> fully asynchronous, returns a device tensor."""
+        [pos_loss, neg_loss, loss, reg]; batch on the device -> fully asynchronous, returns a device tensor.
+        With ``lookahead`` (the train iterator) the host batch goes through staging buffers instead: the step is queued,
+        the NEXT batch is taken from the iterator and copied on a side stream while the GPU works, then the loss is read."""
         model = self
         lib = _lib.load()
         dev = model.entity_embedding.device
@@ -230,6 +291,26 @@ class KGEModel(nn.Module):
         # (the device guard costs ~10 us of host time: only taken when the model is not on the current device)
         with (torch.cuda.device(dev) if torch.cuda.current_device() != dev.index else contextlib.nullcontext()):
             stream = ops._stream()
+            if host_batch and (staged is not None or lookahead is not None):
+                if staged is None or (staged[2] is None) != bool(uni) or staged[0].device != dev:
+                    staged = model._stage_host_batch(lib, positive_sample, negative_sample, subsampling_weight, uni, dev)
+                dpos, dneg, dw, ev = staged[:4]
+                torch.cuda.current_stream().wait_event(ev)
+                ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
+                if model._loss_dev is None or model._loss_dev.device != dev:
+                    model._loss_dev = torch.empty(4, dtype=torch.float32, device=dev)
+                    model._loss_host = np.empty(4, dtype=np.float32)
+                out_dev, out = model._loss_dev, model._loss_host
+                _lib.check(lib.kge_train_step(
+                    C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(dpos), P(dneg), P(dw),
+                    B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out_dev),
+                    C.c_void_p(out_dev.data_ptr() + 12), P(ws), ws.numel(), stream), "kge_train_step")
+                if lookahead is not None:
+                    model._take_ahead(lib, lookahead, uni, dev)  # host work + H2D of batch k+1 under step k
+                _lib.check(lib.kge_fetch_floats(out.ctypes.data_as(C.c_void_p), P(out_dev), 4, stream), "kge_fetch_floats")
+                if model._stage is not None and model._stage["key"] == staged[5]:
+                    model._stage["free"].append(staged[:4])  # the step is over: its staging set can take a new batch
+                return out
             if host_batch:
                 pos = positive_sample.contiguous()
                 neg = negative_sample.contiguous()

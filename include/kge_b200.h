@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 5
+#define KGE_B200_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -229,6 +229,17 @@ KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *ent
                         const int64_t *host_negative, const float *host_subsampling_weight, int64_t B, int64_t N,
                         const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts, int deterministic,
                         float *host_loss4, void *ws, size_t ws_bytes, void *stream);
+
+/* The two halves of kge_train_step_host for a caller that keeps the NEXT batch in flight while the current step runs
+ * (KGEModel.train_step's input lookahead: upstream's `next(train_iterator)` + `.cuda()`, train_step U9, issued one step
+ * early on a copy stream):
+ *   kge_stage_batch  : the three H2D copies of a batch (pinned host memory for true asynchrony) on `stream`;
+ *                      host_subsampling_weight / dev_subsampling_weight may both be NULL (--uni_weight);
+ *   kge_fetch_floats : n floats device -> host on `stream`, then waits for the stream (the `.item()` of the loss log). */
+KGE_API int kge_stage_batch(const int64_t *host_positive, const int64_t *host_negative,
+                            const float *host_subsampling_weight, int64_t *dev_positive, int64_t *dev_negative,
+                            float *dev_subsampling_weight, int64_t B, int64_t N, void *stream);
+KGE_API int kge_fetch_floats(float *host_dst, const float *dev_src, int64_t n, void *stream);
 
 /*
  * Candidate sweep of the fused step: variant 1 (default) = split sweep, one warp per candidate row with the

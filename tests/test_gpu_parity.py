@@ -334,3 +334,38 @@ def test_sweep_variants_agree():
         grads.append(opt.state[gm.entity_embedding]["exp_avg"].clone())
     np.testing.assert_allclose(losses[0], losses[1], rtol=2e-6)
     assert float((grads[0] - grads[1]).abs().max()) <= 5e-5 * float(grads[0].abs().max())
+
+
+def test_train_step_input_lookahead():
+    """The input lookahead (batch k+1 taken from the iterator and copied H2D while step k runs) changes neither the
+    order in which batches are consumed nor a single bit of the result; StopIteration surfaces on the call that
+    upstream's `next(train_iterator)` would raise it on; a second iterator used in between is served in order too."""
+    E, R, H, B, N = 300, 5, 64, 32, 40
+    args = ko.Args(negative_adversarial_sampling=True, cuda=True)
+    batches = [ko.synthetic_batch(E, R, B if s != 3 else B // 2, N, seed=50 + s) for s in range(6)]  # one ragged batch
+    batches = [(p.pin_memory(), n.pin_memory(), w.pin_memory(), m) for p, n, w, m in batches]
+    runs = []
+    for lookahead in (False, True):
+        _, gm = _pair("RotatE", E, R, H, seed=9)
+        gm.input_lookahead = lookahead
+        opt = torch.optim.Adam(filter(lambda p: p.requires_grad, gm.parameters()), lr=1e-3)
+        it = iter(batches)
+        logs = [type(gm).train_step(gm, opt, it, args) for _ in range(len(batches))]
+        with pytest.raises(StopIteration):
+            type(gm).train_step(gm, opt, it, args)
+        runs.append((logs, gm.entity_embedding.detach().clone(), gm.relation_embedding.detach().clone()))
+    assert runs[0][0] == runs[1][0]
+    assert torch.equal(runs[0][1], runs[1][1]) and torch.equal(runs[0][2], runs[1][2])
+    # two iterators interleaved: each is consumed in its own order
+    _, gm = _pair("RotatE", E, R, H, seed=9)
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, gm.parameters()), lr=1e-3)
+    it_a, it_b = iter(batches[:3]), iter(batches[3:])
+    order = [it_a, it_b, it_a, it_b, it_a, it_b]
+    _, ref = _pair("RotatE", E, R, H, seed=9)
+    ref.input_lookahead = False
+    ropt = torch.optim.Adam(filter(lambda p: p.requires_grad, ref.parameters()), lr=1e-3)
+    for k, it in enumerate(order):
+        got = type(gm).train_step(gm, opt, it, args)
+        want = type(ref).train_step(ref, ropt, iter([batches[k // 2 if it is it_a else 3 + k // 2]]), args)
+        assert got == want
+    assert torch.equal(gm.entity_embedding, ref.entity_embedding)
