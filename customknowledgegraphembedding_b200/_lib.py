@@ -84,6 +84,7 @@ PROTOTYPES = {
                                       C.POINTER(LossOpts), C.POINTER(AdamOpts), C.c_int, _P, _P, _SZ, _P]),
     "kge_stage_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _P]),
     "kge_fetch_floats": (C.c_int, [_P, _P, _I64, _P]),
+    "kge_stream_wait_event": (C.c_int, [_P, _P]),
     "kge_train_sweep": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
                                   C.POINTER(StepBuffers), _P, _SZ, _P]),
     "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,

@@ -366,6 +366,12 @@ int kge_stage_batch(const int64_t* host_positive, const int64_t* host_negative, 
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_stage_batch");
 }
 
+int kge_stream_wait_event(void* stream, void* event) {
+    if (!event) return fail(KGE_ERR_INVALID_ARGUMENT, "event is NULL");
+    cudaError_t e = cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0);
+    return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_stream_wait_event");
+}
+
 int kge_fetch_floats(float* host_dst, const float* dev_src, int64_t n, void* stream) {
     if (!host_dst || !dev_src || n < 0) return fail(KGE_ERR_INVALID_ARGUMENT, "bad arguments");
     cudaStream_t st = (cudaStream_t)stream;

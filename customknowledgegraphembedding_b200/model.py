@@ -101,12 +101,12 @@ class KGEModel(nn.Module):
         self.input_lookahead = True
         self._ahead = {}     # id(iterator) -> (iterator, batch, staged device copy or None); holding the iterator pins its id
         self._stage = None   # copy stream and the pool of staging buffer sets
-        self._loss_dev = self._loss_host = None
+        self._hot = None     # argument cache of the staged train step (pointers, structs, step counters)
 
     def __getstate__(self):
         # streams, events, staged batches and workspaces are per-process scratch: never pickled / deep-copied
         d = self.__dict__.copy()
-        d.update(_ahead={}, _stage=None, _ws={}, _loss_dev=None, _loss_host=None)
+        d.update(_ahead={}, _stage=None, _ws={}, _hot=None)
         return d
 
     # ------------------------------------------------------------------------------------
@@ -213,9 +213,12 @@ class KGEModel(nn.Module):
             return model._train_step_generic(optimizer, positive_sample, negative_sample, subsampling_weight, mode,
                                              adv, alpha, uni, reg)
 
-        out = model._fused_step(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
-                                adv, alpha, uni, reg, staged=staged,
-                                lookahead=train_iterator if model.input_lookahead else None)
+        if (model.input_lookahead and not positive_sample.is_cuda and torch.cuda.current_device() == dev.index):
+            out = model._fused_step_staged(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                                           adv, alpha, uni, reg, staged, train_iterator)
+        else:
+            out = model._fused_step(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                                    adv, alpha, uni, reg)
         pos_l, neg_l, loss, regv = out.tolist() if isinstance(out, torch.Tensor) else (float(x) for x in out)
         log = {"regularization": regv} if reg != 0.0 else {}
         log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
@@ -240,7 +243,7 @@ class KGEModel(nn.Module):
         if st["key"] != key:
             st["key"], st["free"] = key, []
         if st["free"]:
-            dpos, dneg, dw, ev = st["free"].pop()
+            dpos, dneg, dw, ev = st["free"].pop()[:4]
         else:
             dpos = torch.empty((B, 3), dtype=torch.int64, device=dev)
             dneg = torch.empty((B, N), dtype=torch.int64, device=dev)
@@ -250,7 +253,8 @@ class KGEModel(nn.Module):
                                        None if w is None else C.c_void_p(w.data_ptr()), ops._ptr(dpos), ops._ptr(dneg),
                                        ops._ptr(dw), B, N, st["stream_ptr"]), "kge_stage_batch")
         ev.record(st["stream"])
-        return dpos, dneg, dw, ev, (pos, neg, w), key  # (the host sources stay alive with the tuple)
+        # (the host sources stay alive with the tuple; the raw event handle exists once the event has been recorded)
+        return dpos, dneg, dw, ev, (pos, neg, w), key, C.c_void_p(ev.cuda_event)
 
     def _take_ahead(self, lib, iterator, uni, dev):
         """``next(iterator)`` one step early, its H2D copies queued behind nothing but themselves."""
@@ -263,12 +267,73 @@ class KGEModel(nn.Module):
             staged = self._stage_host_batch(lib, batch[0], batch[1], batch[2], uni, dev)
         self._ahead[id(iterator)] = (iterator, batch, staged)
 
+    def _fused_step_staged(self, optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                           adv, alpha, uni, reg, staged, iterator):
+        """The host-batch step of ``train_step`` with the input lookahead: wait for the staged copy of THIS batch, queue
+        the step (kge_train_step), take the NEXT batch from the iterator and start its H2D copies on the copy stream
+        while the GPU works, then read the loss back (kge_fetch_floats).  Between the end of one step and the first
+        kernel of the next the GPU idles for exactly the Python that runs here before the C call, so everything that does
+        not change from step to step (pointers, structs, workspace) is cached in ``_hot`` and revalidated by address."""
+        lib = _lib.load()
+        ent, rel, mod = self.entity_embedding, self.relation_embedding, self._modulus()
+        dev = ent.device
+        st_e, st_r = self._adam_state(optimizer, ent), self._adam_state(optimizer, rel)
+        st_m = self._adam_state(optimizer, mod) if mod is not None else None
+        key = (id(optimizer), ent.data_ptr(), rel.data_ptr(), st_e["exp_avg"].data_ptr(), st_e["exp_avg_sq"].data_ptr(),
+               st_r["exp_avg"].data_ptr(), st_r["exp_avg_sq"].data_ptr(), id(st_e["step"]), id(st_r["step"]),
+               0 if mod is None else mod.data_ptr(), 0 if st_m is None else st_m["exp_avg"].data_ptr())
+        hot = self._hot
+        if hot is None or hot["key"] != key:
+            P = ops._ptr
+            steps = [st["step"] for st in (st_e, st_r, st_m) if st is not None]
+            if any(t.is_cuda for t in steps):  # capturable optimizers keep `step` on the device: general path
+                return self._fused_step(optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
+                                        adv, alpha, uni, reg)
+            adam = AdamOpts(0.0, 0.9, 0.999, 1e-8, 1, 0)
+            host = torch.empty(4, dtype=torch.float32).pin_memory()
+            out_dev = torch.empty(4, dtype=torch.float32, device=dev)
+            hot = self._hot = {
+                "key": key, "steps": [t.numpy() for t in steps], "keep": (steps, host, out_dev),
+                "tables": (P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]), P(st_r["exp_avg"]),
+                           P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None, P(st_m["exp_avg_sq"]) if st_m else None),
+                "adam": adam, "adam_ref": C.byref(adam), "loss": {}, "ws": {},
+                "out": host.numpy(), "out_host": C.c_void_p(host.data_ptr()), "out_dev": P(out_dev),
+                "out_dev3": C.c_void_p(out_dev.data_ptr() + 12)}
+        for v in hot["steps"]:
+            v += 1  # the optimizer's own `step` tensors (0-d views), as torch.optim.Adam.step() would
+        adam = hot["adam"]
+        adam.lr, (adam.beta1, adam.beta2), adam.eps, adam.step = group["lr"], group["betas"], group["eps"], int(hot["steps"][0])
+        lkey = (adv, uni, alpha, reg)
+        lo = hot["loss"].get(lkey)
+        if lo is None:
+            lo = LossOpts(int(adv), int(uni), 1, 0, alpha, reg)
+            lo = hot["loss"][lkey] = (lo, C.byref(lo))
+        desc = self._desc()
+        B, N = negative_sample.shape
+        wkey = (B, N, desc.gamma, desc.embedding_range, desc.interht_eps)
+        ws = hot["ws"].get(wkey)
+        if ws is None:
+            t = self._workspace(_lib.WS_TRAIN_STEP, B, N)
+            ws = hot["ws"][wkey] = (t, ops._ptr(t), t.numel())
+        if staged is None or (staged[2] is None) != bool(uni) or staged[0].device != dev:
+            staged = self._stage_host_batch(lib, positive_sample, negative_sample, subsampling_weight, uni, dev)
+        stream = C.c_void_p(torch._C._cuda_getCurrentRawStream(dev.index))
+        _lib.check(lib.kge_stream_wait_event(stream, staged[6]), "kge_stream_wait_event")
+        _lib.check(lib.kge_train_step(
+            C.byref(desc), ops.mode_id(mode), *hot["tables"], ops._ptr(staged[0]), ops._ptr(staged[1]), ops._ptr(staged[2]),
+            B, N, lo[1], hot["adam_ref"], int(self.deterministic), hot["out_dev"], hot["out_dev3"], ws[1], ws[2], stream),
+            "kge_train_step")
+        if iterator is not None:
+            self._take_ahead(lib, iterator, uni, dev)  # host work + H2D of batch k+1 under step k
+        _lib.check(lib.kge_fetch_floats(hot["out_host"], hot["out_dev"], 4, stream), "kge_fetch_floats")
+        if self._stage is not None and self._stage["key"] == staged[5]:
+            self._stage["free"].append(staged)  # the step is over: its staging set can take a new batch
+        return hot["out"]
+
     def _fused_step(self, optimizer, group, positive_sample, negative_sample, subsampling_weight, mode,
-                    adv, alpha, uni, reg, detach_weights=True, keras_adam=False, staged=None, lookahead=None):
+                    adv, alpha, uni, reg, detach_weights=True, keras_adam=False):
         """One call into kge_train_step(_host).  Batch on the host -> copies inside the C call, returns a numpy
-        [pos_loss, neg_loss, loss, reg]; batch on the device -> fully asynchronous, returns a device tensor.
-        With ``lookahead`` (the train iterator) the host batch goes through staging buffers instead: the step is queued,
-        the NEXT batch is taken from the iterator and copied on a side stream while the GPU works, then the loss is read."""
+        [pos_loss, neg_loss, loss, reg]; batch on the device -> fully asynchronous, returns a device tensor."""
         model = self
         lib = _lib.load()
         dev = model.entity_embedding.device
@@ -291,26 +356,6 @@ class KGEModel(nn.Module):
         # (the device guard costs ~10 us of host time: only taken when the model is not on the current device)
         with (torch.cuda.device(dev) if torch.cuda.current_device() != dev.index else contextlib.nullcontext()):
             stream = ops._stream()
-            if host_batch and (staged is not None or lookahead is not None):
-                if staged is None or (staged[2] is None) != bool(uni) or staged[0].device != dev:
-                    staged = model._stage_host_batch(lib, positive_sample, negative_sample, subsampling_weight, uni, dev)
-                dpos, dneg, dw, ev = staged[:4]
-                torch.cuda.current_stream().wait_event(ev)
-                ws = model._workspace(_lib.WS_TRAIN_STEP, B, N)
-                if model._loss_dev is None or model._loss_dev.device != dev:
-                    model._loss_dev = torch.empty(4, dtype=torch.float32, device=dev)
-                    model._loss_host = np.empty(4, dtype=np.float32)
-                out_dev, out = model._loss_dev, model._loss_host
-                _lib.check(lib.kge_train_step(
-                    C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), *common_state, P(dpos), P(dneg), P(dw),
-                    B, N, C.byref(loss_opts), C.byref(adam), int(model.deterministic), P(out_dev),
-                    C.c_void_p(out_dev.data_ptr() + 12), P(ws), ws.numel(), stream), "kge_train_step")
-                if lookahead is not None:
-                    model._take_ahead(lib, lookahead, uni, dev)  # host work + H2D of batch k+1 under step k
-                _lib.check(lib.kge_fetch_floats(out.ctypes.data_as(C.c_void_p), P(out_dev), 4, stream), "kge_fetch_floats")
-                if model._stage is not None and model._stage["key"] == staged[5]:
-                    model._stage["free"].append(staged[:4])  # the step is over: its staging set can take a new batch
-                return out
             if host_batch:
                 pos = positive_sample.contiguous()
                 neg = negative_sample.contiguous()

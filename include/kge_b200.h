@@ -235,10 +235,12 @@ KGE_API int kge_train_step_host(const kge_model_desc *desc, int mode, float *ent
  * early on a copy stream):
  *   kge_stage_batch  : the three H2D copies of a batch (pinned host memory for true asynchrony) on `stream`;
  *                      host_subsampling_weight / dev_subsampling_weight may both be NULL (--uni_weight);
+ *   kge_stream_wait_event : `stream` waits for a CUDA event (the one recorded after kge_stage_batch on the copy stream);
  *   kge_fetch_floats : n floats device -> host on `stream`, then waits for the stream (the `.item()` of the loss log). */
 KGE_API int kge_stage_batch(const int64_t *host_positive, const int64_t *host_negative,
                             const float *host_subsampling_weight, int64_t *dev_positive, int64_t *dev_negative,
                             float *dev_subsampling_weight, int64_t B, int64_t N, void *stream);
+KGE_API int kge_stream_wait_event(void *stream, void *event);
 KGE_API int kge_fetch_floats(float *host_dst, const float *dev_src, int64_t n, void *stream);
 
 /*
