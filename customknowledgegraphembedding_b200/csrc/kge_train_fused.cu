@@ -830,45 +830,91 @@ __host__ __device__ inline int relation_scratch_ints(int B) { return B + (B + 31
 __device__ __forceinline__ void relation_row_update(long long r, int Dr, const int64_t* __restrict__ pos, int B,
                                                     const float* __restrict__ GR, float* rel, float* m, float* v,
                                                     const AdamScalars& ad, float l3, int* match, int* nmatch) {
-    // every warp tests 32 positives at a time (independent loads) and leaves one bitmap word per group; warp 0 then
-    // expands the bitmap into the list of matching positives in ascending b (popc keeps the order)
+    // every warp tests 32 positives at a time and leaves one bitmap word per group -- four groups per round, so that
+    // four independent loads are in flight per lane; warp 0 then expands the bitmap into the list of matching positives
+    // in ascending b (each lane owns a run of consecutive words; a warp scan of the run totals places them)
     unsigned* bits = reinterpret_cast<unsigned*>(match + B);
-    const int words = (B + 31) / 32, lane = threadIdx.x & 31;
-    for (int w = threadIdx.x >> 5; w < words; w += blockDim.x >> 5) {
-        const int b = 32 * w + lane;
-        const bool hit = (b < B) && (pos[3 * (long long)b + 1] == r);
-        const unsigned mask = __ballot_sync(0xffffffffu, hit);
-        if (lane == 0) bits[w] = mask;
+    const int words = (B + 31) / 32, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int w0 = warp; w0 < words; w0 += 4 * nw) {
+        long long rid[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int b = 32 * (w0 + u * nw) + lane;
+            rid[u] = (b < B) ? pos[3 * (long long)b + 1] : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int w = w0 + u * nw;
+            if (w < words) {  // warp-uniform
+                const unsigned mask = __ballot_sync(0xffffffffu, rid[u] == r);
+                if (lane == 0) bits[w] = mask;
+            }
+        }
     }
     __syncthreads();
     if (threadIdx.x < 32) {
-        int count = 0;
-        for (int w = 0; w < words; ++w) {
-            const unsigned mask = bits[w];
-            if ((mask >> lane) & 1u) match[count + __popc(mask & ((1u << lane) - 1u))] = 32 * w + lane;
-            count += __popc(mask);
+        const int per = (words + 31) / 32, w_lo = min(lane * per, words), w_hi = min(w_lo + per, words);
+        int cnt = 0;
+        for (int w = w_lo; w < w_hi; ++w) cnt += __popc(bits[w]);
+        int off = cnt;  // inclusive scan of the run totals
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, off, o);
+            if (lane >= o) off += v;
         }
-        if (lane == 0) *nmatch = count;
+        if (lane == 31) *nmatch = off;
+        off -= cnt;
+        for (int w = w_lo; w < w_hi; ++w) {
+            unsigned mask = bits[w];
+            while (mask) {
+                match[off++] = 32 * w + (__ffs(mask) - 1);
+                mask &= mask - 1;
+            }
+        }
     }
     __syncthreads();
     const int nm = *nmatch;
-    for (int k = threadIdx.x; k < Dr; k += blockDim.x) {
-        float g = 0.f;
+    // dL/d(row) = sum of GR[match[j]] in ascending j; a thread owns up to four coordinates (stride blockDim) and keeps
+    // 16 independent loads in flight (4 positives x 4 coordinates); the additions of a coordinate stay in ascending j
+    for (int kb = threadIdx.x; kb < Dr; kb += 4 * blockDim.x) {
+        float g[4] = {0.f, 0.f, 0.f, 0.f};
         int j = 0;
-        for (; j + 8 <= nm; j += 8) {  // eight independent loads in flight; the additions keep the ascending order
-            float x[8];
+        for (; j + 4 <= nm; j += 4) {
+            float x[4][4];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) x[u] = GR[(long long)match[j + u] * Dr + k];
+            for (int u = 0; u < 4; ++u) {
+                const float* src = GR + (long long)match[j + u] * Dr;
 #pragma unroll
-            for (int u = 0; u < 8; ++u) g += x[u];
+                for (int c = 0; c < 4; ++c) {
+                    const int k = kb + c * blockDim.x;
+                    x[u][c] = (k < Dr) ? src[k] : 0.f;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) g[c] += x[u][c];
         }
-        for (; j < nm; ++j) g += GR[(long long)match[j] * Dr + k];
-        const long long i = r * Dr + k;
-        float pp = rel[i], mm = m[i], vv = v[i];
-        adam_update(pp, g, mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
-        rel[i] = pp;
-        m[i] = mm;
-        v[i] = vv;
+        for (; j < nm; ++j) {
+            const float* src = GR + (long long)match[j] * Dr;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int k = kb + c * blockDim.x;
+                if (k < Dr) g[c] += src[k];
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int k = kb + c * blockDim.x;
+            if (k < Dr) {
+                const long long i = r * Dr + k;
+                float pp = rel[i], mm = m[i], vv = v[i];
+                adam_update(pp, g[c], mm, vv, ad.beta1, ad.beta2, ad.step_size, ad.inv_sqrt_bc2, ad.eps, l3);
+                rel[i] = pp;
+                m[i] = mm;
+                v[i] = vv;
+            }
+        }
     }
     __syncthreads();  // match / nmatch may be rewritten by the caller's next row
 }
@@ -1197,21 +1243,51 @@ train_modulus_adam_kernel(const float* __restrict__ GM, int B, float* modulus, f
     }
 }
 
-// loss terms [B][2] (pos, neg) -> loss3, fixed order
-__global__ void __launch_bounds__(256) loss_final2_kernel(const float* __restrict__ terms, int B, float* loss3) {
+// loss terms [B][2] (pos, neg) -> loss3, fixed order (one CTA of 1024 threads: the kernel sits on the critical path of
+// the step and is pure latency, so both sums go through one reduction and the loads of a thread are independent)
+__global__ void __launch_bounds__(1024) loss_final2_kernel(const float* __restrict__ terms, int B, float* loss3) {
     pdl_enter();
-    __shared__ float red[32];
+    __shared__ float red[32][2];
     float p = 0.f, n = 0.f;
-    for (int i = threadIdx.x; i < B; i += blockDim.x) {
-        p += terms[2 * i];
-        n += terms[2 * i + 1];
+    if ((reinterpret_cast<uintptr_t>(terms) & 7) == 0) {
+        const float2* t2 = reinterpret_cast<const float2*>(terms);
+#pragma unroll 4
+        for (int i = threadIdx.x; i < B; i += blockDim.x) {
+            const float2 t = t2[i];
+            p += t.x;
+            n += t.y;
+        }
+    } else {
+        for (int i = threadIdx.x; i < B; i += blockDim.x) {
+            p += terms[2 * i];
+            n += terms[2 * i + 1];
+        }
     }
-    p = block_sum(p, red);
-    n = block_sum(n, red);
-    if (threadIdx.x == 0) {
-        loss3[0] = -p;
-        loss3[1] = -n;
-        loss3[2] = (-p + -n) / 2.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        p += __shfl_xor_sync(0xffffffffu, p, o);
+        n += __shfl_xor_sync(0xffffffffu, n, o);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        red[warp][0] = p;
+        red[warp][1] = n;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        p = (lane < nw) ? red[lane][0] : 0.f;
+        n = (lane < nw) ? red[lane][1] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            p += __shfl_xor_sync(0xffffffffu, p, o);
+            n += __shfl_xor_sync(0xffffffffu, n, o);
+        }
+        if (lane == 0) {
+            loss3[0] = -p;
+            loss3[1] = -n;
+            loss3[2] = (-p + -n) / 2.0f;
+        }
     }
 }
 
@@ -1456,7 +1532,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         {
             ProfScope ps(ST_DSCORE, st);
             // (S already holds dL/ds: the sweep's last pass writes it per positive)
-            if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(256), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
+            if ((e = launch_pdl(loss_final2_kernel, dim3(1), dim3(1024), 0, st, fc.terms, (int)B, ws.small)) != cudaSuccess) return e;
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
         if (lo.regularization != 0.f) {
