@@ -317,7 +317,7 @@ def run_ours(a):
                      "note": "algorithmic bytes are row gathers from the 116 MB entity table, most of which the 126 MB L2 "
                              "serves (traffic = DRAM bytes per launch from ncu is ~0.4x of them): frac can pass 1.0 and "
                              "dram_frac is the share of the HBM peak the kernel really draws; what limits the kernel is "
-                             "shared-memory / issue throughput per row (profiles/r1_ncu_summary_tma_ring.md)",
+                             "shared-memory / issue throughput per row (profiles/r1_ncu_summary_final.md)",
                      "step": {"algorithmic_bytes": ab["step"], "achieved": ab["step"] / (step_ms * 1e-3) / 1e9,
                               "frac": ab["step"] / (step_ms * 1e-3) / 1e9 / peak,
                               "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12}},
