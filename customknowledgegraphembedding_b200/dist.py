@@ -85,6 +85,13 @@ def test_step(model, test_triples, all_true_triples, args, group=None, local_fn=
 _BUFFERS = ("S", "Q", "GH", "GT", "GR", "GM", "stats", "terms")
 
 
+def _on(dev):
+    """Device guard only when the tensor's device is not the current one (the guard costs ~10 us of host time)."""
+    if dev.type != "cuda" or torch.cuda.current_device() == dev.index:
+        return contextlib.nullcontext()
+    return torch.cuda.device(dev)
+
+
 class DataParallelStep:
     """``step.train_step(train_iterator, args)`` == ``KGEModel.train_step`` on the concatenation of every rank's batch."""
 
@@ -102,6 +109,7 @@ class DataParallelStep:
         self.peer_exchange = os.environ.get("KGE_DP_PEER_EXCHANGE", "1") != "0"
         self._peer = None
         self._rows_peer = None  # entity table in symmetric memory: updated rows are stored into the other replicas
+        self._wsum_ahead = {}   # id(staged batch) -> all-reduced weight sum queued one step early
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -125,6 +133,16 @@ class DataParallelStep:
             self._gathered["pos"] = torch.empty((self.world * B, 3), dtype=torch.int64, device=dev)
             self._gathered["neg"] = torch.empty((self.world * B, N), dtype=torch.int64, device=dev)
         self._shape = (B, N, dev)
+        self._structs = {}  # pointer structs of the buffers above, built on first use
+
+    def _bufs(self, which):
+        """StepBuffers of the local / gathered buffers (cached: building one costs ~10 us of host time per call)."""
+        src = self._local if which == "local" else self._gathered
+        key = (which,) + tuple(src[k].data_ptr() for k in ("S", "Q"))
+        hit = self._structs.get(which)
+        if hit is None or hit[0] != key:
+            hit = self._structs[which] = (key, StepBuffers(*[C.c_void_p(src[k].data_ptr()) for k in _BUFFERS]))
+        return hit[1]
 
     def _peer_buffers(self, B, N, dev, sizes):
         """The gathered buffers carved from ONE symmetric-memory block, so that every rank can store into every other
@@ -169,8 +187,8 @@ class DataParallelStep:
     def _exchange(self, pos, neg):
         """kge_train_exchange + the barrier that orders every rank's apply after every rank's stores."""
         B, N = neg.shape
-        local = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
-        with torch.cuda.device(pos.device):
+        local = self._bufs("local")
+        with _on(pos.device):
             _lib.check(_lib.load().kge_train_exchange(
                 C.byref(self.model._desc()), ops._ptr(pos), ops._ptr(neg), B, N, C.byref(local), self.rank, self.world,
                 self._peer["tables"], self._peer["pos"], self._peer["neg"], ops._stream()), "kge_train_exchange")
@@ -180,9 +198,9 @@ class DataParallelStep:
     def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
         m = self.model
         B, N = neg.shape
-        bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
+        bufs = self._bufs("local")
         sws = self._sweep_ws(m._desc(), B, N, pos.device)
-        with torch.cuda.device(pos.device):
+        with _on(pos.device):
             _lib.check(_lib.load().kge_train_sweep(
                 C.byref(m._desc()), ops.mode_id(mode), ops._ptr(m.entity_embedding), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(pos), ops._ptr(neg), ops._ptr(w), B, N, C.byref(loss_opts),
@@ -210,9 +228,9 @@ class DataParallelStep:
         need = ops.workspace_bytes(_lib.WS_TRAIN_APPLY, desc, B_all, N)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=ent.device)
-        bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
+        bufs = self._bufs("gathered")
         P = ops._ptr
-        with torch.cuda.device(ent.device):
+        with _on(ent.device):
             _lib.check(_lib.load().kge_train_apply_peers(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
                 P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
@@ -255,7 +273,13 @@ class DataParallelStep:
     def train_step(self, train_iterator, args, sync: bool = True):
         m, opt = self.model, self.optimizer
         m.train()
-        positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
+        # input lookahead, as in KGEModel.train_step: the batch of this call was taken from the iterator and copied H2D
+        # on the copy stream while the previous step ran
+        ahead, staged = m._ahead.pop(id(train_iterator), None) if m._ahead else None, None
+        if ahead is not None:
+            (positive_sample, negative_sample, subsampling_weight, mode), staged = ahead[1], ahead[2]
+        else:
+            positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
         if mode not in ("head-batch", "tail-batch"):
             raise ValueError("mode %s not supported" % mode)
         group_opts = m._fused_adam_plan(opt)
@@ -266,15 +290,26 @@ class DataParallelStep:
         uni = bool(getattr(args, "uni_weight", False))
         reg = float(getattr(args, "regularization", 0.0))
         loss_opts = LossOpts(int(adv), int(uni), 1, 0, float(getattr(args, "adversarial_temperature", 1.0)), reg)
-        pos = positive_sample.to(dev, non_blocking=True).contiguous()
-        neg = negative_sample.to(dev, non_blocking=True).contiguous()
-        w = subsampling_weight.to(dev, dtype=torch.float32, non_blocking=True).contiguous()
+        lookahead = (sync and m.input_lookahead and dev.type == "cuda" and not positive_sample.is_cuda
+                     and torch.cuda.current_device() == dev.index)
+        if lookahead:
+            if staged is None or staged[2] is None or staged[0].device != dev:
+                staged = m._stage_host_batch(_lib.load(), positive_sample, negative_sample, subsampling_weight, False, dev)
+            _lib.check(_lib.load().kge_stream_wait_event(ops._stream(), staged[6]), "kge_stream_wait_event")
+            pos, neg, w = staged[0], staged[1], staged[2]
+        else:
+            pos = positive_sample.to(dev, non_blocking=True).contiguous()
+            neg = negative_sample.to(dev, non_blocking=True).contiguous()
+            w = subsampling_weight.to(dev, dtype=torch.float32, non_blocking=True).contiguous()
         B, N = neg.shape
         self._ensure(B, N, dev)
-        # global sum of the subsampling weights: the loss is that of ONE step on the global batch
-        wsum = w.sum().reshape(1)
-        if self.world > 1:
-            dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
+        # global sum of the subsampling weights: the loss is that of ONE step on the global batch.  With the lookahead
+        # it was queued behind the previous step (see below), so this step starts with the sweep.
+        wsum = self._wsum_ahead.pop(id(staged), None) if lookahead else None
+        if wsum is None:
+            wsum = w.sum().reshape(1)
+            if self.world > 1:
+                dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
         self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
         if self.world > 1 and self._peer is not None:
             self._exchange(pos, neg)  # peer stores over NVLink: GH / GT rows go to their owners only
@@ -310,7 +345,21 @@ class DataParallelStep:
             self._share_rows()
         if not sync:
             return out
+        if lookahead:
+            m._take_ahead(_lib.load(), train_iterator, False, dev)  # next(iterator) + its H2D copies under this step
+            nxt = m._ahead.get(id(train_iterator))
+            self._wsum_ahead.clear()
+            if nxt is not None and nxt[2] is not None:
+                # the weight sum of batch k+1 and its all-reduce go behind step k on the main stream: every rank queues
+                # the same collectives in the same order (all ranks run the same number of steps)
+                _lib.check(_lib.load().kge_stream_wait_event(ops._stream(), nxt[2][6]), "kge_stream_wait_event")
+                nsum = nxt[2][2].sum().reshape(1)
+                if self.world > 1:
+                    dist.all_reduce(nsum, op=dist.ReduceOp.SUM, group=self.group)
+                self._wsum_ahead[id(nxt[2])] = nsum
         pos_l, neg_l, loss, regv = out.tolist()
+        if lookahead and m._stage is not None and m._stage["key"] == staged[5]:
+            m._stage["free"].append(staged)  # the step is over: its staging set can take a new batch
         log = {"regularization": regv} if reg != 0.0 else {}
         log.update({"positive_sample_loss": pos_l, "negative_sample_loss": neg_l, "loss": loss})
         return log
@@ -498,7 +547,7 @@ class RowShardedStep(DataParallelStep):
         desc.nentity = compact.shape[0]
         bufs = StepBuffers(*[C.c_void_p(self._local[k].data_ptr()) for k in _BUFFERS])
         sws = self._sweep_ws(desc, B, N, compact.device)
-        with torch.cuda.device(compact.device):
+        with _on(compact.device):
             _lib.check(_lib.load().kge_train_sweep(
                 C.byref(desc), ops.mode_id(mode), ops._ptr(compact), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(cpos), ops._ptr(cneg), ops._ptr(w), B, N, C.byref(loss_opts),
@@ -517,7 +566,7 @@ class RowShardedStep(DataParallelStep):
             self._ws = torch.empty(need, dtype=torch.uint8, device=ent.device)
         bufs = StepBuffers(*[C.c_void_p(self._gathered[k].data_ptr()) for k in _BUFFERS])
         P = ops._ptr
-        with torch.cuda.device(ent.device):
+        with _on(ent.device):
             _lib.check(_lib.load().kge_train_apply_shard(
                 C.byref(desc), ops.mode_id(mode), P(ent), self.lo, ent.shape[0], P(rel), P(mod), P(st_e["exp_avg"]),
                 P(st_e["exp_avg_sq"]), P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
