@@ -51,7 +51,7 @@ __device__ __forceinline__ void copy_row4(float* __restrict__ dst, const float* 
 
 __global__ void __launch_bounds__(256)
 exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg, int B,
-                int N, int q_row, int De, int Dr, int rank, int world, long long rows_per_rank) {
+                int N, int q_row, int De, int Dr, int rank, int world, long long rows_per_rank, int early) {
     pdl_enter();
     const long long b = blockIdx.x, g = (long long)rank * B + b;
     const long long h = pos[3 * b], t = pos[3 * b + 2];
@@ -59,10 +59,12 @@ exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos
     for (int k = 0; k < world; ++k) {
         const int p = (rank + k) % world;  // start with the own slot, then round the ring: ranks do not all hit one peer
         copy_row4(T.S[p] + g * N, L.S + b * N, N);
-        copy_row4(T.Q[p] + g * q_row, L.Q + b * q_row, q_row);
         copy_row4(T.GR[p] + g * Dr, L.GR + b * Dr, Dr);
-        copy_row4(reinterpret_cast<float*>(T.neg[p] + g * N), reinterpret_cast<const float*>(neg + b * N), 2 * N);
-        if (threadIdx.x < 6) reinterpret_cast<float*>(T.pos[p] + 3 * g)[threadIdx.x] = reinterpret_cast<const float*>(pos + 3 * b)[threadIdx.x];
+        if (early) {  // (otherwise ids and Q went ahead as copy-engine copies: KGE_EXCHANGE_EARLY)
+            copy_row4(T.Q[p] + g * q_row, L.Q + b * q_row, q_row);
+            copy_row4(reinterpret_cast<float*>(T.neg[p] + g * N), reinterpret_cast<const float*>(neg + b * N), 2 * N);
+            if (threadIdx.x < 6) reinterpret_cast<float*>(T.pos[p] + 3 * g)[threadIdx.x] = reinterpret_cast<const float*>(pos + 3 * b)[threadIdx.x];
+        }
         if (threadIdx.x < 2) {
             T.stats[p][2 * g + threadIdx.x] = L.stats[2 * b + threadIdx.x];
             T.terms[p][2 * g + threadIdx.x] = L.terms[2 * b + threadIdx.x];
@@ -75,9 +77,26 @@ exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos
 
 cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* neg, int64_t B, int64_t N,
                             const kge_step_buffers& local, int rank, int world, const kge_step_buffers* peers,
-                            int64_t* const* peer_pos, int64_t* const* peer_neg, cudaStream_t st) {
+                            int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, cudaStream_t st) {
     if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return cudaErrorInvalidValue;
     if (B == 0) return cudaSuccess;
+    const size_t q_row = (size_t)model_planes(P.model) * P.H;
+    if (parts == KGE_EXCHANGE_EARLY) {
+        // What is final as soon as the staging pass of the sweep has run -- the ids and Q, 58 % of the bytes of an exchange
+        // -- goes out as plain copies (contiguous B-row blocks at slot rank * B of every rank's gathered buffers): copy
+        // engines, no SM, so they run under the candidate sweep.  The own slot first, then round the ring.
+        const size_t g0 = (size_t)rank * B;
+        for (int k = 0; k < world; ++k) {
+            const int p = (rank + k) % world;
+            cudaError_t e = cudaMemcpyAsync(peers[p].Q + g0 * q_row, local.Q, (size_t)B * q_row * sizeof(float), cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(peer_neg[p] + g0 * N, neg, (size_t)B * N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(peer_pos[p] + g0 * 3, pos, (size_t)B * 3 * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
     PeerTable T{};
     for (int p = 0; p < world; ++p) {
         T.S[p] = peers[p].S; T.Q[p] = peers[p].Q; T.GH[p] = peers[p].GH; T.GT[p] = peers[p].GT;
@@ -86,7 +105,7 @@ cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* 
     }
     const long long rows_per_rank = (P.E + world - 1) / world;  // dist.shard_range
     return launch_pdl(exchange_kernel, dim3((unsigned)B), dim3(256), 0, st, T, local, pos, neg, (int)B, (int)N,
-                      model_planes(P.model) * P.H, P.De, P.Dr, rank, world, rows_per_rank);
+                      model_planes(P.model) * P.H, P.De, P.Dr, rank, world, rows_per_rank, parts == KGE_EXCHANGE_ALL ? 1 : 0);
 }
 
 }  // namespace kge

@@ -253,6 +253,15 @@ int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, c
                     const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
                     const float* wsum, int64_t B_total, const kge_step_buffers* out, void* ws, size_t ws_bytes,
                     void* stream) {
+    return kge_train_sweep_staged(desc, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
+                                  loss_opts, wsum, B_total, out, ws, ws_bytes, nullptr, stream);
+}
+
+int kge_train_sweep_staged(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
+                           const float* modulus, const int64_t* positive, const int64_t* negative,
+                           const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
+                           const float* wsum, int64_t B_total, const kge_step_buffers* out, void* ws, size_t ws_bytes,
+                           void* stage_event, void* stream) {
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -267,7 +276,8 @@ int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, c
     if (!fused_step_applicable(P, *loss_opts, B_total, N, entity, relation))
         return fail(KGE_ERR_UNSUPPORTED, "kge_train_sweep: the fused step does not apply to this configuration");
     cudaError_t e = launch_train_sweep(P, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
-                                       *loss_opts, wsum, B_total, *out, ws, ws_bytes, (cudaStream_t)stream);
+                                       *loss_opts, wsum, B_total, *out, ws, ws_bytes, (cudaEvent_t)stage_event,
+                                       (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_sweep");
 }
 
@@ -337,6 +347,16 @@ int kge_train_apply_peers(const kge_model_desc* desc, int mode, float* entity, f
 int kge_train_exchange(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B, int64_t N,
                        const kge_step_buffers* local, int rank, int world, const kge_step_buffers* peer_gathered,
                        int64_t* const* peer_positive, int64_t* const* peer_negative, void* stream) {
+    return kge_train_exchange_parts(desc, positive, negative, B, N, local, rank, world, peer_gathered, peer_positive,
+                                    peer_negative, KGE_EXCHANGE_ALL, stream);
+}
+
+int kge_train_exchange_parts(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B,
+                             int64_t N, const kge_step_buffers* local, int rank, int world,
+                             const kge_step_buffers* peer_gathered, int64_t* const* peer_positive,
+                             int64_t* const* peer_negative, int parts, void* stream) {
+    if (parts != KGE_EXCHANGE_EARLY && parts != KGE_EXCHANGE_LATE && parts != KGE_EXCHANGE_ALL)
+        return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be KGE_EXCHANGE_EARLY, _LATE or _ALL");
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -346,7 +366,7 @@ int kge_train_exchange(const kge_model_desc* desc, const int64_t* positive, cons
     if (world < 1 || world > 16 || rank < 0 || rank >= world)
         return fail(KGE_ERR_INVALID_ARGUMENT, "rank %d / world %d (at most 16 peers)", rank, world);
     cudaError_t e = launch_exchange(P, positive, negative, B, N, *local, rank, world, peer_gathered, peer_positive,
-                                    peer_negative, (cudaStream_t)stream);
+                                    peer_negative, parts, (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_exchange");
 }
 

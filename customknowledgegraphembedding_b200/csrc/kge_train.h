@@ -18,7 +18,7 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
 cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
                                const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
-                               void* ws, size_t ws_bytes, cudaStream_t st);
+                               void* ws, size_t ws_bytes, cudaEvent_t stage_ev, cudaStream_t st);
 size_t train_sweep_workspace_bytes(const Params& P, int64_t B, int64_t N);
 cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel, float* modulus, float* m_ent,
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
@@ -28,5 +28,5 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float** out_small, cudaStream_t st);
 cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* neg, int64_t B, int64_t N,
                             const kge_step_buffers& local, int rank, int world, const kge_step_buffers* peers,
-                            int64_t* const* peer_pos, int64_t* const* peer_neg, cudaStream_t st);
+                            int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, cudaStream_t st);
 }

@@ -1393,6 +1393,8 @@ struct FusedCall {
     // kge_train_apply_rows_peers: replicas of the entity table on the other ranks
     int npeers = 0;
     float* const* peers = nullptr;  // host array of npeers device pointers
+    // kge_train_sweep_staged: recorded on the stream as soon as Q[b] of every local positive is final
+    cudaEvent_t stage_ev = nullptr;
 };
 
 template <int MODEL, int CHW, bool HEAD, int R>
@@ -1491,6 +1493,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 A.part = 1;
                 A.item_counter = ws.item_counter;
                 if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 1>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
+                if (fc.stage_ev != nullptr && (e = cudaEventRecord(fc.stage_ev, st)) != cudaSuccess) return e;
                 const int parts = f1w_parts(N);
                 RowsArgs R{ent, fc.neg, fc.Q, modulus, fc.S, ws.PA, ws.PM, ws.item_counter, (int)fc.B, (int)N, parts,
                            (int)((N + parts - 1) / parts), lo.negative_adversarial_sampling, lo.adversarial_temperature};
@@ -1503,6 +1506,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
             }
         } else {
             if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
+            if (fc.stage_ev != nullptr && (e = cudaEventRecord(fc.stage_ev, st)) != cudaSuccess) return e;  // (Q is final with the kernel)
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (fc.phase == 1) return cudaSuccess;
@@ -1618,7 +1622,7 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
 cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
                                const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
-                               void* wsp, size_t ws_bytes, cudaStream_t st) {
+                               void* wsp, size_t ws_bytes, cudaEvent_t stage_ev, cudaStream_t st) {
     // the sweep alone needs a workspace only for the split (warp-per-row) variant: per-item partials + item counter
     FusedWs ws{};
     if (wsp != nullptr && ws_bytes >= train_sweep_workspace_bytes(P, B, N)) {
@@ -1629,6 +1633,7 @@ cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, cons
         ws.item_counter = (int*)((char*)ws.PM + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)));
     }
     FusedCall fc{1, pos, neg, w, B, wsum, B_total, nullptr, nullptr, 0, 0, 0, o.S, o.Q, o.GH, o.GT, o.GR, o.GM, o.stats, o.terms};
+    fc.stage_ev = stage_ev;
     kge_adam_opts ao{0.f, 0.9f, 0.999f, 1e-8f, 1, 0};
     return fused_dispatch(P, mode, const_cast<float*>(ent), const_cast<float*>(rel), const_cast<float*>(modulus), nullptr,
                           nullptr, nullptr, nullptr, nullptr, nullptr, fc, N, lo, adam_scalars(ao), ws, st);

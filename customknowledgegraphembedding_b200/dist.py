@@ -110,6 +110,12 @@ class DataParallelStep:
         self._peer = None
         self._rows_peer = None  # entity table in symmetric memory: updated rows are stored into the other replicas
         self._wsum_ahead = {}   # id(staged batch) -> all-reduced weight sum queued one step early
+        # ids and Q exchanged by copy engines while the candidate sweep runs (kge_train_exchange_parts).  Measured SLOWER
+        # than the one-kernel exchange (2 GPUs 0.669 vs 0.652 ms, 8 GPUs 1.004 vs 0.912 ms per step: 3 * G small peer
+        # copies on one copy-engine stream do not reach the rate of SM stores, and the event between the staging pass and
+        # the rows kernel undoes their programmatic overlap) -- off by default, kept for larger batches / tables.
+        self.early_exchange = os.environ.get("KGE_DP_EARLY_EXCHANGE", "0") != "0"
+        self._early_state = None
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -184,27 +190,41 @@ class DataParallelStep:
         others = [bases[r] for r in range(self.world) if r != self.rank]
         return {"hdl": hdl, "block": block, "ptrs": (C.c_void_p * len(others))(*[C.c_void_p(b) for b in others])}
 
-    def _exchange(self, pos, neg):
-        """kge_train_exchange + the barrier that orders every rank's apply after every rank's stores."""
+    def _exchange(self, pos, neg, parts=_lib.EXCHANGE_ALL, stream=None):
+        """kge_train_exchange(_parts) on the current stream (or ``stream``); the caller follows it with the barrier that
+        orders every rank's apply after every rank's stores."""
         B, N = neg.shape
         local = self._bufs("local")
         with _on(pos.device):
-            _lib.check(_lib.load().kge_train_exchange(
+            _lib.check(_lib.load().kge_train_exchange_parts(
                 C.byref(self.model._desc()), ops._ptr(pos), ops._ptr(neg), B, N, C.byref(local), self.rank, self.world,
-                self._peer["tables"], self._peer["pos"], self._peer["neg"], ops._stream()), "kge_train_exchange")
-            self._peer["hdl"].barrier()
+                self._peer["tables"], self._peer["pos"], self._peer["neg"], int(parts),
+                ops._stream() if stream is None else stream), "kge_train_exchange")
+
+    def _early(self, dev):
+        """Side stream + the two events of the early exchange (ids and Q as copy-engine copies under the sweep)."""
+        if self._early_state is None:
+            side = torch.cuda.Stream(dev)
+            ev_stage, ev_done = torch.cuda.Event(), torch.cuda.Event()
+            ev_stage.record(side)  # (creates the raw handles)
+            ev_done.record(side)
+            self._early_state = {"side": side, "side_ptr": C.c_void_p(side.cuda_stream), "ev_stage": ev_stage,
+                                 "ev_stage_ptr": C.c_void_p(ev_stage.cuda_event), "ev_done": ev_done,
+                                 "ev_done_ptr": C.c_void_p(ev_done.cuda_event)}
+        return self._early_state
 
     # ---- the two kernel calls (overridable: tests/test_dist_cpu.py) ------------------------------------
-    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
+    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts, stage_event=None):
         m = self.model
         B, N = neg.shape
         bufs = self._bufs("local")
         sws = self._sweep_ws(m._desc(), B, N, pos.device)
         with _on(pos.device):
-            _lib.check(_lib.load().kge_train_sweep(
+            _lib.check(_lib.load().kge_train_sweep_staged(
                 C.byref(m._desc()), ops.mode_id(mode), ops._ptr(m.entity_embedding), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(pos), ops._ptr(neg), ops._ptr(w), B, N, C.byref(loss_opts),
-                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), ops._stream()), "kge_train_sweep")
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), stage_event, ops._stream()),
+                "kge_train_sweep")
 
     def _sweep_ws(self, desc, B, N, dev):
         """Workspace of the split (warp-per-row) sweep: per-item partial dL/dq + item counter."""
@@ -310,11 +330,26 @@ class DataParallelStep:
             wsum = w.sum().reshape(1)
             if self.world > 1:
                 dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
-        self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
-        if self.world > 1 and self._peer is not None:
+        plain_sweep = type(self)._sweep is DataParallelStep._sweep
+        if self.world > 1 and self._peer is not None and self.early_exchange and plain_sweep:
+            # ids and Q leave on a side stream (copy engines) as soon as the staging pass has run, under the candidate
+            # sweep; the kernel sends the rest after the sweep; the barrier is ordered after both
+            lib, es, main = _lib.load(), self._early(dev), ops._stream()
+            self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts, stage_event=es["ev_stage_ptr"])
+            _lib.check(lib.kge_stream_wait_event(es["side_ptr"], es["ev_stage_ptr"]), "kge_stream_wait_event")
+            self._exchange(pos, neg, _lib.EXCHANGE_EARLY, stream=es["side_ptr"])
+            es["ev_done"].record(es["side"])
+            self._exchange(pos, neg, _lib.EXCHANGE_LATE)
+            _lib.check(lib.kge_stream_wait_event(main, es["ev_done_ptr"]), "kge_stream_wait_event")
+            self._peer["hdl"].barrier()
+            pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
+        elif self.world > 1 and self._peer is not None:
+            self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
             self._exchange(pos, neg)  # peer stores over NVLink: GH / GT rows go to their owners only
+            self._peer["hdl"].barrier()
             pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
         elif self.world > 1:
+            self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
             with _coalesced(self.group, dev):
                 dist.all_gather_into_tensor(self._gathered["pos"], pos, group=self.group)
                 dist.all_gather_into_tensor(self._gathered["neg"], neg, group=self.group)
@@ -322,6 +357,7 @@ class DataParallelStep:
                     dist.all_gather_into_tensor(self._gathered[k], self._local[k], group=self.group)
             pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
         else:
+            self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
             pos_all, neg_all = pos, neg
             for k in _BUFFERS:
                 self._gathered[k] = self._local[k]

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 6
+#define KGE_B200_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -332,6 +332,28 @@ KGE_API int kge_train_exchange(const kge_model_desc *desc, const int64_t *positi
                                int64_t N, const kge_step_buffers *local, int rank, int world,
                                const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
                                int64_t *const *peer_negative, void *stream);
+
+/* The exchange in two pieces, so that the larger one hides behind the candidate sweep:
+ *   KGE_EXCHANGE_EARLY  ids and Q -- final as soon as the staging pass of the sweep has run (the event of
+ *                       kge_train_sweep_staged) -- as plain device-to-device copies of contiguous B-row blocks: copy
+ *                       engines, no SM; the caller issues them on a side stream that waits for that event;
+ *   KGE_EXCHANGE_LATE   S, GR, GM, stats, terms to every rank and GH / GT to their owners (the kernel), after the sweep;
+ *   KGE_EXCHANGE_ALL    == kge_train_exchange.
+ * The barrier before kge_train_apply has to be ordered after both pieces. */
+enum { KGE_EXCHANGE_EARLY = 1, KGE_EXCHANGE_LATE = 2, KGE_EXCHANGE_ALL = 3 };
+KGE_API int kge_train_exchange_parts(const kge_model_desc *desc, const int64_t *positive, const int64_t *negative,
+                                     int64_t B, int64_t N, const kge_step_buffers *local, int rank, int world,
+                                     const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
+                                     int64_t *const *peer_negative, int parts, void *stream);
+
+/* kge_train_sweep that records `stage_event` (a cudaEvent_t, may be NULL) on `stream` as soon as Q[b] of every local
+ * positive is final: after the staging pass of the split sweep, after the whole kernel for the row-group variant. */
+KGE_API int kge_train_sweep_staged(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
+                                   const float *modulus, const int64_t *positive, const int64_t *negative,
+                                   const float *subsampling_weight, int64_t B, int64_t N,
+                                   const kge_loss_opts *loss_opts, const float *wsum, int64_t B_total,
+                                   const kge_step_buffers *out, void *ws, size_t ws_bytes, void *stage_event,
+                                   void *stream);
 
 /*
  * kge_train_apply over a ROW-SHARDED entity table: `entity_shard`, `adam_m_shard`, `adam_v_shard` hold only the rows

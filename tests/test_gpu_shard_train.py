@@ -145,9 +145,12 @@ def test_apply_parts_argument_checks():
                         out, parts=bad)
 
 
+@pytest.mark.parametrize("pieces", [False, True])
 @pytest.mark.parametrize("world", [1, 2, 3])
-def test_peer_exchange_places_every_row_where_it_is_needed(world):
-    """kge_train_exchange with the ranks emulated on one GPU (every "peer" block is a plain tensor here; over real
+def test_peer_exchange_places_every_row_where_it_is_needed(world, pieces):
+    """``pieces``: kge_train_exchange_parts EARLY (ids + Q as copies, on a side stream) + LATE (the kernel) instead of
+    the one-kernel exchange -- the same bytes land in the same places.
+    kge_train_exchange with the ranks emulated on one GPU (every "peer" block is a plain tensor here; over real
     ranks the same pointers come from symmetric memory -- scratch/dist_check.py): ids, S, Q, GR and the scalars land
     in every rank's gathered buffers at slot rank * B + b; GH / GT rows only at the owner of the head / tail."""
     import ctypes as C
@@ -172,8 +175,18 @@ def test_peer_exchange_places_every_row_where_it_is_needed(world):
     lib = _lib.load()
     for r in range(world):
         loc = StepBuffers(*[C.c_void_p(local[r][k].data_ptr()) for k in names])
-        _lib.check(lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r, world,
-                                          tables, ppos, pneg, ops._stream()), "kge_train_exchange")
+        if pieces:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            _lib.check(lib.kge_train_exchange_parts(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r,
+                                                    world, tables, ppos, pneg, _lib.EXCHANGE_EARLY,
+                                                    C.c_void_p(side.cuda_stream)), "kge_train_exchange_parts")
+            _lib.check(lib.kge_train_exchange_parts(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r,
+                                                    world, tables, ppos, pneg, _lib.EXCHANGE_LATE, ops._stream()),
+                       "kge_train_exchange_parts")
+        else:
+            _lib.check(lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r, world,
+                                              tables, ppos, pneg, ops._stream()), "kge_train_exchange")
     torch.cuda.synchronize()
     rows = (E + world - 1) // world
     for p in range(world):
