@@ -49,6 +49,33 @@ __device__ __forceinline__ void copy_row4(float* __restrict__ dst, const float* 
     }
 }
 
+// one row of n 4-byte elements to the same offset of every rank's buffer: each 16-byte chunk is loaded ONCE and stored
+// to all `world` destinations (independent fire-and-forget stores, constant indices into the parameter bank) -- the
+// per-peer loop around a load/store pair read the local row once per peer and kept one store in flight per thread
+template <typename PtrArray>
+__device__ __forceinline__ void fan_row4(const PtrArray& dst, long long dst_off, const float* __restrict__ src, int n, int world) {
+    bool vec = ((n & 3) == 0) && ((dst_off & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+#pragma unroll
+    for (int p = 0; p < kMaxPeers; ++p)
+        if (p < world) vec = vec && ((reinterpret_cast<uintptr_t>(dst[p]) & 15) == 0);
+    if (vec) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        for (int i = threadIdx.x; i < n / 4; i += blockDim.x) {
+            const float4 v = s4[i];
+#pragma unroll
+            for (int p = 0; p < kMaxPeers; ++p)
+                if (p < world) reinterpret_cast<float4*>(reinterpret_cast<float*>(dst[p]) + dst_off)[i] = v;
+        }
+    } else {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const float v = src[i];
+#pragma unroll
+            for (int p = 0; p < kMaxPeers; ++p)
+                if (p < world) (reinterpret_cast<float*>(dst[p]) + dst_off)[i] = v;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg, int B,
                 int N, int q_row, int De, int Dr, int rank, int world, long long rows_per_rank, int early) {
@@ -56,20 +83,19 @@ exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos
     const long long b = blockIdx.x, g = (long long)rank * B + b;
     const long long h = pos[3 * b], t = pos[3 * b + 2];
     const int own_h = (int)(h / rows_per_rank), own_t = (int)(t / rows_per_rank);
-    for (int k = 0; k < world; ++k) {
-        const int p = (rank + k) % world;  // start with the own slot, then round the ring: ranks do not all hit one peer
-        copy_row4(T.S[p] + g * N, L.S + b * N, N);
-        copy_row4(T.GR[p] + g * Dr, L.GR + b * Dr, Dr);
-        if (early) {  // (otherwise ids and Q went ahead as copy-engine copies: KGE_EXCHANGE_EARLY)
-            copy_row4(T.Q[p] + g * q_row, L.Q + b * q_row, q_row);
-            copy_row4(reinterpret_cast<float*>(T.neg[p] + g * N), reinterpret_cast<const float*>(neg + b * N), 2 * N);
-            if (threadIdx.x < 6) reinterpret_cast<float*>(T.pos[p] + 3 * g)[threadIdx.x] = reinterpret_cast<const float*>(pos + 3 * b)[threadIdx.x];
-        }
-        if (threadIdx.x < 2) {
-            T.stats[p][2 * g + threadIdx.x] = L.stats[2 * b + threadIdx.x];
-            T.terms[p][2 * g + threadIdx.x] = L.terms[2 * b + threadIdx.x];
-        }
-        if (threadIdx.x == 0) T.GM[p][g] = L.GM[b];
+    fan_row4(T.S, g * N, L.S + b * N, N, world);
+    fan_row4(T.GR, g * Dr, L.GR + b * Dr, Dr, world);
+    if (early) {  // (otherwise ids and Q went ahead as copy-engine copies: KGE_EXCHANGE_EARLY)
+        fan_row4(T.Q, g * q_row, L.Q + b * q_row, q_row, world);
+        fan_row4(T.neg, 2 * g * N, reinterpret_cast<const float*>(neg + b * N), 2 * N, world);  // int64 ids as float pairs
+        fan_row4(T.pos, 6 * g, reinterpret_cast<const float*>(pos + 3 * b), 6, world);
+    }
+    fan_row4(T.stats, 2 * g, L.stats + 2 * b, 2, world);
+    fan_row4(T.terms, 2 * g, L.terms + 2 * b, 2, world);
+    fan_row4(T.GM, g, L.GM + b, 1, world);
+    // the compact gradient rows of the head / tail entity go to the rank that owns the row, and only there
+#pragma unroll
+    for (int p = 0; p < kMaxPeers; ++p) {
         if (p == own_h) copy_row4(T.GH[p] + g * De, L.GH + b * De, De);
         if (p == own_t) copy_row4(T.GT[p] + g * De, L.GT + b * De, De);
     }
