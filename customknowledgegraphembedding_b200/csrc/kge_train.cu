@@ -313,6 +313,20 @@ int kge_train_apply_peers(const kge_model_desc* desc, int mode, float* entity, f
                           const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
                           int64_t entity_hi, int parts, int npeers, float* const* peer_entity, float* loss3, float* reg1,
                           void* ws, size_t ws_bytes, void* stream) {
+    return kge_train_apply_multicast(desc, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
+                                     adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
+                                     loss_opts, adam_opts, gathered, entity_lo, entity_hi, parts, npeers, peer_entity, nullptr,
+                                     loss3, reg1, ws, ws_bytes, stream);
+}
+
+int kge_train_apply_multicast(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
+                              float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
+                              float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
+                              const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
+                              const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
+                              int64_t entity_hi, int parts, int npeers, float* const* peer_entity,
+                              float* multicast_entity, float* loss3, float* reg1, void* ws, size_t ws_bytes,
+                              void* stream) {
     if (npeers < 0 || npeers > 15 || (npeers > 0 && !peer_entity))
         return fail(KGE_ERR_INVALID_ARGUMENT, "npeers must be 0..15 with a pointer table");
     if (parts <= 0 || (parts & ~KGE_APPLY_ALL)) return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be a non-empty subset of KGE_APPLY_*");
@@ -332,7 +346,7 @@ int kge_train_apply_peers(const kge_model_desc* desc, int mode, float* entity, f
     cudaError_t e = launch_train_apply(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                                        adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
                                        *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, parts, npeers, peer_entity,
-                                       ws, ws_bytes, &small, st);
+                                       multicast_entity, ws, ws_bytes, &small, st);
     if (e != cudaSuccess) return fail_cuda(e, "kge_train_apply");
     if (!(parts & KGE_APPLY_PREPARE)) return KGE_OK;  // the loss belongs to the piece that computes it
     if (reg1 == loss3 + 3) {

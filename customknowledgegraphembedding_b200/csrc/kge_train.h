@@ -24,8 +24,8 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, int parts, int npeers, float* const* peers, void* ws, size_t ws_bytes,
-                               float** out_small, cudaStream_t st);
+                               int64_t e_hi, int parts, int npeers, float* const* peers, float* mc, void* ws,
+                               size_t ws_bytes, float** out_small, cudaStream_t st);
 cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* neg, int64_t B, int64_t N,
                             const kge_step_buffers& local, int rank, int world, const kge_step_buffers* peers,
                             int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, cudaStream_t st);

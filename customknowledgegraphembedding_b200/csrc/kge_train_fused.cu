@@ -943,6 +943,9 @@ struct EntityArgs {
 struct EntityPeers {
     int npeers;
     float* peer[kMaxRowPeers];
+    // NVSwitch multicast mapping of the table (symmetric memory): ONE multimem.st per chunk reaches every replica -- the
+    // SM issues a seventh of the remote stores of the per-peer loop at 8 GPUs.  NULL: per-peer stores.
+    float* mc;
 };
 struct NoPeers {};
 
@@ -1198,6 +1201,19 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
         if constexpr (PEERS) {
             // NVLink stores into the other ranks' replicas, after the local row / m / v traffic has been issued: the
             // updated row is still in registers
+            if (X.mc != nullptr) {
+                float* mrow_all = X.mc + e * (long long)P.De;
+#pragma unroll
+                for (int p = 0; p < CP; ++p)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        const int k0 = 4 * (tid + j * T);
+                        if (k0 < H)
+                            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mrow_all + p * H + k0),
+                                         "f"(c[p][j][0]), "f"(c[p][j][1]), "f"(c[p][j][2]), "f"(c[p][j][3])
+                                         : "memory");
+                    }
+            } else
 #pragma unroll
             for (int q = 0; q < kMaxRowPeers; ++q) {  // constant indices: the pointer table stays in the parameter bank
                 if (q >= X.npeers) break;
@@ -1393,6 +1409,7 @@ struct FusedCall {
     // kge_train_apply_rows_peers: replicas of the entity table on the other ranks
     int npeers = 0;
     float* const* peers = nullptr;  // host array of npeers device pointers
+    float* mc = nullptr;            // multicast mapping of the entity table (kge_train_apply_multicast)
     // kge_train_sweep_staged: recorded on the stream as soon as Q[b] of every local positive is final
     cudaEvent_t stage_ev = nullptr;
 };
@@ -1462,7 +1479,7 @@ static cudaError_t launch_entity(const Params& P, const CoordConsts& kc, int hea
                                  const EntityPeers& X, const AdamScalars& ad, float l3, cudaStream_t st) {
     const int ethreads = std::max(32, (((P.H / 4 + ECH - 1) / ECH + 31) / 32) * 32);
 #define KGE_ENT(HD, TM)                                                                                       \
-    (X.npeers > 0 ? launch_entity_inst<MODEL, ECH, HD, TM, true>(P, kc, modulus, A, X, ad, l3, ethreads, st)   \
+    ((X.npeers > 0 || X.mc != nullptr) ? launch_entity_inst<MODEL, ECH, HD, TM, true>(P, kc, modulus, A, X, ad, l3, ethreads, st)   \
                   : launch_entity_inst<MODEL, ECH, HD, TM, false>(P, kc, modulus, A, X, ad, l3, ethreads, st))
     if (ethreads <= 128) return head ? KGE_ENT(true, 128) : KGE_ENT(false, 128);
     return head ? KGE_ENT(true, 256) : KGE_ENT(false, 256);
@@ -1551,7 +1568,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         ProfScope ps(ST_ENTITY, st);
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
                      fc.e_lo, fc.e_hi};
-        EntityPeers X{fc.npeers, {}};
+        EntityPeers X{fc.npeers, {}, fc.mc};
         for (int q = 0; q < fc.npeers; ++q) X.peer[q] = fc.peers[q];
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
         if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, X, ad, l3, st)) != cudaSuccess) return e;
@@ -1643,14 +1660,15 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, int parts, int npeers, float* const* peers, void* wsp, size_t ws_bytes,
-                               float** out_small, cudaStream_t st) {
+                               int64_t e_hi, int parts, int npeers, float* const* peers, float* mc, void* wsp,
+                               size_t ws_bytes, float** out_small, cudaStream_t st) {
     if (npeers < 0 || npeers > kMaxRowPeers) return cudaErrorInvalidValue;
     if (ws_bytes < fused_step_workspace_bytes(P, B_all, N)) return cudaErrorInvalidValue;
     const FusedWs ws = fused_carve(P, B_all, N, wsp);
     *out_small = ws.small;
     FusedCall fc{2, nullptr, nullptr, nullptr, 0, nullptr, B_all, pos_all, neg_all, B_all, e_lo, e_hi,
                  in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, parts, npeers, peers};
+    fc.mc = mc;
     return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
                           ws, st);
 }

@@ -188,7 +188,10 @@ class DataParallelStep:
         ent.data = block.view(ent.shape)
         bases = [int(p) for p in hdl.buffer_ptrs]
         others = [bases[r] for r in range(self.world) if r != self.rank]
-        return {"hdl": hdl, "block": block, "ptrs": (C.c_void_p * len(others))(*[C.c_void_p(b) for b in others])}
+        # NVSwitch multicast mapping of the block (0 where the fabric has none): one multimem.st reaches every replica
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0) if os.environ.get("KGE_DP_MULTICAST", "1") != "0" else 0
+        return {"hdl": hdl, "block": block, "ptrs": (C.c_void_p * len(others))(*[C.c_void_p(b) for b in others]),
+                "mc": C.c_void_p(mc) if mc else None}
 
     def _exchange(self, pos, neg, parts=_lib.EXCHANGE_ALL, stream=None):
         """kge_train_exchange(_parts) on the current stream (or ``stream``); the caller follows it with the barrier that
@@ -236,7 +239,7 @@ class DataParallelStep:
         return ws
 
     def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None,
-               row_peers=None):
+               row_peers=None, multicast=None):
         """kge_train_apply_peers on the rows ``[lo, hi)`` (default: everything this rank owns, all parts);
         ``row_peers``: ctypes array of the other ranks' table pointers -- updated rows are stored there too."""
         m, opt = self.model, self.optimizer
@@ -251,13 +254,13 @@ class DataParallelStep:
         bufs = self._bufs("gathered")
         P = ops._ptr
         with _on(ent.device):
-            _lib.check(_lib.load().kge_train_apply_peers(
+            _lib.check(_lib.load().kge_train_apply_multicast(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
                 P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
                 P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
                 C.byref(adam), C.byref(bufs), self.lo if lo is None else lo, self.hi if hi is None else hi, int(parts),
-                0 if row_peers is None else len(row_peers), row_peers, P(out), C.c_void_p(out.data_ptr() + 12),
-                P(self._ws), self._ws.numel(), ops._stream()), "kge_train_apply_peers")
+                0 if row_peers is None else len(row_peers), row_peers, multicast, P(out),
+                C.c_void_p(out.data_ptr() + 12), P(self._ws), self._ws.numel(), ops._stream()), "kge_train_apply_peers")
 
     def _apply_overlapped(self, mode, pos_all, neg_all, loss_opts, adam, out):
         """Owner-parallel apply with the broadcast of the updated rows hidden behind it: the owned range is cut into
@@ -372,7 +375,8 @@ class DataParallelStep:
         plain = type(self)._apply is DataParallelStep._apply and type(self)._share_rows is DataParallelStep._share_rows
         if self.world > 1 and plain and self._rows_peer is not None and reg == 0.0:
             # the broadcast of the owned rows rides on the Adam epilogue as NVLink stores; one barrier closes the step
-            self._apply(mode, pos_all, neg_all, loss_opts, adam, out, row_peers=self._rows_peer["ptrs"])
+            self._apply(mode, pos_all, neg_all, loss_opts, adam, out, row_peers=self._rows_peer["ptrs"],
+                        multicast=self._rows_peer["mc"])
             self._rows_peer["hdl"].barrier()
         elif self.world > 1 and self.overlap_chunks > 1 and dev.type == "cuda" and plain:
             self._apply_overlapped(mode, pos_all, neg_all, loss_opts, adam, out)

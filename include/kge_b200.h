@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 7
+#define KGE_B200_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -318,6 +318,20 @@ KGE_API int kge_train_apply_peers(const kge_model_desc *desc, int mode, float *e
                                   const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
                                   int npeers, float *const *peer_entity, float *loss3, float *reg1, void *ws,
                                   size_t ws_bytes, void *stream);
+
+/* kge_train_apply_peers with the replicas reached through ONE NVSwitch multicast mapping of the table instead of a
+ * pointer per peer (`multicast_entity`: the multicast address of the symmetric-memory block that holds the table on
+ * every rank; NULL = per-peer stores): every 16-byte chunk of an updated row leaves the SM as one `multimem.st`, the
+ * switch replicates it to all ranks (the local replica included).  `npeers` / `peer_entity` are ignored when it is set. */
+KGE_API int kge_train_apply_multicast(const kge_model_desc *desc, int mode, float *entity, float *relation,
+                                      float *modulus, float *adam_m_entity, float *adam_v_entity,
+                                      float *adam_m_relation, float *adam_v_relation, float *adam_m_modulus,
+                                      float *adam_v_modulus, const int64_t *positive_all, const int64_t *negative_all,
+                                      int64_t B_all, int64_t N, const kge_loss_opts *loss_opts,
+                                      const kge_adam_opts *adam_opts, const kge_step_buffers *gathered,
+                                      int64_t entity_lo, int64_t entity_hi, int parts, int npeers,
+                                      float *const *peer_entity, float *multicast_entity, float *loss3, float *reg1,
+                                      void *ws, size_t ws_bytes, void *stream);
 
 /*
  * Between kge_train_sweep and kge_train_apply: the exchange of the per-positive buffers over NVLink peer memory,
