@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
 EXCHANGE_EARLY, EXCHANGE_LATE, EXCHANGE_ALL = 1, 2, 3  # kge_train_exchange_parts
 
@@ -106,6 +106,9 @@ PROTOTYPES = {
                                      C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _P]),
     "kge_train_exchange_parts": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
                                            C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, _P]),
+    "kge_train_exchange_multicast": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
+                                               C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int,
+                                               C.POINTER(StepBuffers), _P, _P, _P]),
     "kge_train_apply_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                         C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P,
                                         _P, _P, _SZ, _P]),

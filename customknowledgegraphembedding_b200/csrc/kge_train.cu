@@ -369,6 +369,15 @@ int kge_train_exchange_parts(const kge_model_desc* desc, const int64_t* positive
                              int64_t N, const kge_step_buffers* local, int rank, int world,
                              const kge_step_buffers* peer_gathered, int64_t* const* peer_positive,
                              int64_t* const* peer_negative, int parts, void* stream) {
+    return kge_train_exchange_multicast(desc, positive, negative, B, N, local, rank, world, peer_gathered, peer_positive,
+                                        peer_negative, parts, nullptr, nullptr, nullptr, stream);
+}
+
+int kge_train_exchange_multicast(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B,
+                                 int64_t N, const kge_step_buffers* local, int rank, int world,
+                                 const kge_step_buffers* peer_gathered, int64_t* const* peer_positive,
+                                 int64_t* const* peer_negative, int parts, const kge_step_buffers* multicast_gathered,
+                                 int64_t* multicast_positive, int64_t* multicast_negative, void* stream) {
     if (parts != KGE_EXCHANGE_EARLY && parts != KGE_EXCHANGE_LATE && parts != KGE_EXCHANGE_ALL)
         return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be KGE_EXCHANGE_EARLY, _LATE or _ALL");
     Params P;
@@ -380,7 +389,8 @@ int kge_train_exchange_parts(const kge_model_desc* desc, const int64_t* positive
     if (world < 1 || world > 16 || rank < 0 || rank >= world)
         return fail(KGE_ERR_INVALID_ARGUMENT, "rank %d / world %d (at most 16 peers)", rank, world);
     cudaError_t e = launch_exchange(P, positive, negative, B, N, *local, rank, world, peer_gathered, peer_positive,
-                                    peer_negative, parts, (cudaStream_t)stream);
+                                    peer_negative, parts, multicast_gathered, multicast_positive, multicast_negative,
+                                    (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_exchange");
 }
 

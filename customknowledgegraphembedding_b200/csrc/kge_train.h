@@ -28,5 +28,6 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                size_t ws_bytes, float** out_small, cudaStream_t st);
 cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* neg, int64_t B, int64_t N,
                             const kge_step_buffers& local, int rank, int world, const kge_step_buffers* peers,
-                            int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, cudaStream_t st);
+                            int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, const kge_step_buffers* mcb,
+                            int64_t* mc_pos, int64_t* mc_neg, cudaStream_t st);
 }

@@ -175,7 +175,17 @@ class DataParallelStep:
         tables = (StepBuffers * G)(*[StepBuffers(*[C.c_void_p(b + offsets[k]) for k in _BUFFERS]) for b in bases])
         pos_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["pos"]) for b in bases])
         neg_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["neg"]) for b in bases])
-        return {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs}
+        out = {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs, "mc": None}
+        # NVSwitch multicast mapping of the block: what goes to every rank leaves as one multimem.st per chunk
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0) if os.environ.get("KGE_DP_MULTICAST", "1") != "0" else 0
+        # Measured SLOWER than the per-rank stores for the exchange (2 GPUs 0.637 vs 0.623 ms, 4 GPUs 0.703 vs 0.691): the
+        # exchange is bound by what ARRIVES at a rank (the same bytes either way) and the own copy takes the trip through
+        # the switch too -- unlike the row stores of the entity kernel, where the SM-side cost of 7 remote stores per chunk
+        # was the problem.  Off unless KGE_DP_MULTICAST_EXCHANGE=1.
+        if mc and os.environ.get("KGE_DP_MULTICAST_EXCHANGE", "0") == "1":
+            out["mc"] = (StepBuffers(*[C.c_void_p(mc + offsets[k]) for k in _BUFFERS]), C.c_void_p(mc + offsets["pos"]),
+                         C.c_void_p(mc + offsets["neg"]))
+        return out
 
     def _peer_table(self):
         """Move the (replicated) entity table into symmetric memory, once: every rank can then store the rows it
@@ -199,9 +209,11 @@ class DataParallelStep:
         B, N = neg.shape
         local = self._bufs("local")
         with _on(pos.device):
-            _lib.check(_lib.load().kge_train_exchange_parts(
+            mc = self._peer["mc"]
+            _lib.check(_lib.load().kge_train_exchange_multicast(
                 C.byref(self.model._desc()), ops._ptr(pos), ops._ptr(neg), B, N, C.byref(local), self.rank, self.world,
                 self._peer["tables"], self._peer["pos"], self._peer["neg"], int(parts),
+                None if mc is None else C.byref(mc[0]), None if mc is None else mc[1], None if mc is None else mc[2],
                 ops._stream() if stream is None else stream), "kge_train_exchange")
 
     def _early(self, dev):

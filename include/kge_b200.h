@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 8
+#define KGE_B200_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -359,6 +359,18 @@ KGE_API int kge_train_exchange_parts(const kge_model_desc *desc, const int64_t *
                                      int64_t B, int64_t N, const kge_step_buffers *local, int rank, int world,
                                      const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
                                      int64_t *const *peer_negative, int parts, void *stream);
+
+/* kge_train_exchange_parts with everything that goes to EVERY rank (ids, S, Q, GR, GM, stats, terms) sent through the
+ * NVSwitch multicast mappings of the gathered buffers (`multicast_gathered`, `multicast_positive`, `multicast_negative`:
+ * multicast addresses of the same symmetric-memory block the peer pointers address; all NULL = per-rank stores): one
+ * `multimem.st` per 16-byte chunk instead of `world` stores.  GH / GT rows still go to their owners through
+ * `peer_gathered`. */
+KGE_API int kge_train_exchange_multicast(const kge_model_desc *desc, const int64_t *positive, const int64_t *negative,
+                                         int64_t B, int64_t N, const kge_step_buffers *local, int rank, int world,
+                                         const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
+                                         int64_t *const *peer_negative, int parts,
+                                         const kge_step_buffers *multicast_gathered, int64_t *multicast_positive,
+                                         int64_t *multicast_negative, void *stream);
 
 /* kge_train_sweep that records `stage_event` (a cudaEvent_t, may be NULL) on `stream` as soon as Q[b] of every local
  * positive is final: after the staging pass of the split sweep, after the whole kernel for the row-group variant. */
