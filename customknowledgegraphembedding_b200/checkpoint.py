@@ -59,6 +59,15 @@ def load_checkpoint(model, optimizer, init_checkpoint: str, do_train: bool = Tru
     model.load_state_dict(checkpoint["model_state_dict"])
     if do_train and optimizer is not None:
         optimizer.load_state_dict(checkpoint["optimizer_state_dict"])
+        # torch keeps a non-capturable Adam's `step` wherever torch.load put it: with map_location="cuda" that is the
+        # GPU, and every later train_step would read it back with a device sync (and miss the staged fast path, which
+        # wants the host-side counters torch.optim.Adam itself creates).  Put them where Adam.step() would.
+        for group in optimizer.param_groups:
+            if not group.get("capturable", False):
+                for p in group["params"]:
+                    st = optimizer.state.get(p)
+                    if st and torch.is_tensor(st.get("step")) and st["step"].is_cuda:
+                        st["step"] = st["step"].detach().to("cpu", torch.float32)
     return {k: v for k, v in checkpoint.items() if k not in ("model_state_dict", "optimizer_state_dict")}
 
 

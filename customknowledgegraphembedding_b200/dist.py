@@ -127,6 +127,17 @@ class DataParallelStep:
     def _ensure(self, B, N, dev):
         if self._shape == (B, N, dev):
             return
+        if B <= 0 or N <= 0:
+            raise ValueError("train_step: empty batch on rank %d (B=%d, N=%d)" % (self.rank, B, N))
+        if self.world > 1 and dist.is_initialized():
+            # gathered buffers, symmetric-memory offsets and B_total are all world * B: every rank must bring the same
+            # shape.  One small all-reduce per shape CHANGE (not per step); a mismatch raises on every rank.
+            shp = torch.tensor([B, -B, N, -N], dtype=torch.int64, device=dev)
+            dist.all_reduce(shp, op=dist.ReduceOp.MAX, group=self.group)
+            bmax, bmin, nmax, nmin = int(shp[0]), -int(shp[1]), int(shp[2]), -int(shp[3])
+            if bmax != bmin or nmax != nmin:
+                raise ValueError("train_step: ranks bring different batch shapes (B %d..%d, N %d..%d); use "
+                                 "drop_last=True / equal shares per rank" % (bmin, bmax, nmin, nmax))
         sizes = self._row_sizes(N)
         self._local = {k: torch.empty(B * s, dtype=torch.float32, device=dev) for k, s in sizes.items()}
         self._peer = None

@@ -6,7 +6,10 @@ the reference's two ``run.py`` files, wired to the B200 hot path.
   -init -save --max_steps --warm_up_steps --save_checkpoint_steps --valid_steps --log_steps --test_log_steps
   --nentity --nrelation``
 * TF codes (/root/reference/tensorflow_codes/run.py:19-36): ``-ip/--input_path`` (TFRecord shards, one record per
-  batch), ``-sf/--score_function``, ``-tr``, ``-bz``, ``--nentity``, ``--nrelation``, ``--hidden_dim``, ``--gamma``.
+  batch), ``-sf/--score_function``, ``-tr``, ``-bz``, ``--nentity``, ``--nrelation``, ``--hidden_dim``, ``--gamma``,
+  ``--epochs``, ``--steps_per_epoch``.  A command with ``-ip`` and none of ``--do_train/--do_valid/--do_test/-init`` is
+  the TF program's command line (README.md:10-20) and runs ``run_tf``: the TF trainer's semantics (gradient through the
+  softmax weights, Keras Adam eps 1e-7, ``lrfn`` per-epoch schedule, ``steps_per_tpu_call = 99`` accounting).
 
 What differs from upstream is only where the work happens: batches come from the on-GPU sampler (or from TFRecord
 shards through the TF-free reader), ``train_step`` / ``test_step`` are the fused kernels.  This is glue -- no
@@ -63,7 +66,39 @@ def parse_args(args=None):
     p.add_argument("--nentity", type=int, default=0, help="DO NOT MANUALLY SET (needed with --input_path)")
     p.add_argument("--nrelation", type=int, default=0, help="DO NOT MANUALLY SET (needed with --input_path)")
     p.add_argument("--seed", type=int, default=0)
+    # the TF trainer's own flags (/root/reference/tensorflow_codes/run.py:29-30)
+    p.add_argument("--epochs", type=int, default=1)
+    p.add_argument("--steps_per_epoch", type=int, default=1000)
     return p.parse_args(args)
+
+
+def is_tf_command(args) -> bool:
+    """The reference's TF entry point has no --do_train / -save (tensorflow_codes/run.py:20-37): a command that names
+    TFRecord input and none of the PyTorch-side mode flags is that program's command line (README.md:10-20)."""
+    return bool(args.input_path) and not (args.do_train or args.do_valid or args.do_test or args.init_checkpoint)
+
+
+def run_tf(args, strategy=None):
+    """``run(strategy, args)`` of /root/reference/tensorflow_codes/run.py:87-128 on the B200 kernels: TFRecord batches,
+    ``TFKGEModel``, Keras-Adam with ``LRSchedule(step) = lrfn(step // steps_per_epoch)``, a ``Sum`` metric, and
+    ``Trainer.training(steps_per_tpu_call=99, epochs, steps_per_epoch)`` -- gradient through the softmax weights,
+    epsilon 1e-7, the reference's step accounting.  Returns the trainer."""
+    from .tf_compat import KerasAdam, SumMetric, TFKGEModel, Trainer, _DefaultStrategy
+    strategy = strategy if strategy is not None else _DefaultStrategy()
+    print("Number of accelerators: ", strategy.num_replicas_in_sync)
+    dataset = TFRecordBatchReader(args.input_path, args.batch_size, repeat=True, pin=True,
+                                  nentity=args.nentity, nrelation=args.nrelation)
+    kge_model = TFKGEModel(model_name=args.model, nentity=args.nentity, nrelation=args.nrelation,
+                           hidden_dim=args.hidden_dim, gamma=args.gamma,
+                           double_entity_embedding=args.double_entity_embedding,
+                           double_relation_embedding=args.double_relation_embedding,
+                           triple_relation_embedding=args.triple_relation_embedding)
+    spe = args.steps_per_epoch
+    optimizer = KerasAdam(learning_rate=lambda step: ck.lrfn(step // spe, strategy.num_replicas_in_sync))
+    trainer = Trainer(strategy=strategy, dataloader=dataset, model=kge_model, optimizer=optimizer,
+                      metrics=SumMetric("training_loss"))
+    trainer.training(steps_per_tpu_call=99, epochs=args.epochs, steps_per_epoch=spe)
+    return trainer
 
 
 def read_triple(file_path, entity2id, relation2id):
@@ -96,6 +131,10 @@ def log_metrics(mode, step, metrics):
 
 def main(args=None):
     args = parse_args(args) if not isinstance(args, argparse.Namespace) else args
+    if is_tf_command(args):
+        if not args.nentity or not args.nrelation:
+            raise ValueError("--nentity / --nrelation are required with --input_path")
+        return run_tf(args).model.kge, {}
     if (not args.do_train) and (not args.do_valid) and (not args.do_test):
         raise ValueError("one of train/val/test mode must be choosed.")
     if args.init_checkpoint:
@@ -136,7 +175,8 @@ def main(args=None):
     if args.do_train:
         if args.input_path:  # the TF trainer's input: pre-built batches (run.py:87-92)
             train_iterator = iter(TFRecordBatchReader(args.input_path, args.batch_size, repeat=True, pin=True,
-                                                      as_torch_batch=True))
+                                                      as_torch_batch=True, nentity=args.nentity,
+                                                      nrelation=args.nrelation))
         else:
             index = TrainTripleIndex(train_triples, args.nentity, args.nrelation)
             train_iterator = BidirectionalGpuIterator(index, args.negative_sample_size, args.batch_size, seed=args.seed)

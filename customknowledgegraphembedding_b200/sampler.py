@@ -78,12 +78,20 @@ class BidirectionalGpuIterator:
 
     ``rank`` / ``world``: every rank walks the same permutations and takes its contiguous share of each global batch,
     so the union over ranks is the batch a single process would have produced (the sampler is keyed by the global
-    positive index)."""
+    positive index).  With ``world > 1`` the short last batch of an epoch is dropped (``drop_last`` defaults to True
+    there): the multi-GPU steps exchange fixed-shape per-positive buffers and need the same B on every rank."""
 
     def __init__(self, index: TrainTripleIndex, negative_sample_size: int, batch_size: int, seed: int = 0,
-                 rank: int = 0, world: int = 1, drop_last: bool = False):
+                 rank: int = 0, world: int = 1, drop_last: Optional[bool] = None):
         self.index, self.N, self.B = index, int(negative_sample_size), int(batch_size)
-        self.seed, self.rank, self.world, self.drop_last = int(seed), int(rank), int(world), drop_last
+        if drop_last is None:
+            drop_last = int(world) > 1
+        if int(world) > 1 and not drop_last:
+            raise ValueError("BidirectionalGpuIterator: world > 1 needs drop_last=True (a short last batch would give the "
+                             "ranks unequal, possibly empty, shares)")
+        if int(world) > 1 and len(index) < self.B * int(world):
+            raise ValueError("fewer training triples (%d) than one global batch (%d x %d)" % (len(index), self.B, world))
+        self.seed, self.rank, self.world, self.drop_last = int(seed), int(rank), int(world), bool(drop_last)
         self.step = 0
         self._state = {m: {"epoch": -1, "perm": None, "cursor": 0, "served": 0} for m in ("head-batch", "tail-batch")}
 

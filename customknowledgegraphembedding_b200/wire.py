@@ -49,8 +49,23 @@ def iter_records(path: str, verify_crc: bool = True) -> Iterator[np.ndarray]:
         off = nxt.value
 
 
-def parse_example(payload, batch_size: int, pin: bool = False):
-    """``parse_tfrecord_fn`` + ``reshape_function(batch_size)`` (run.py:40-66) -> four torch tensors."""
+def check_id_ranges(pos, neg, nentity: int = 0, nrelation: int = 0):
+    """Entity / relation ids of a parsed batch against the table sizes: ``tf.gather`` / ``index_select`` raise on an
+    out-of-range id, the row-gather kernels would read (and the Adam bucket build would write) out of bounds."""
+    if nentity:
+        lo = min(int(pos[:, 0].min()), int(pos[:, 2].min()), int(neg.min()))
+        hi = max(int(pos[:, 0].max()), int(pos[:, 2].max()), int(neg.max()))
+        if lo < 0 or hi >= nentity:
+            raise IndexError("entity id out of range [0, %d): batch holds ids in [%d, %d]" % (nentity, lo, hi))
+    if nrelation:
+        lo, hi = int(pos[:, 1].min()), int(pos[:, 1].max())
+        if lo < 0 or hi >= nrelation:
+            raise IndexError("relation id out of range [0, %d): batch holds ids in [%d, %d]" % (nrelation, lo, hi))
+
+
+def parse_example(payload, batch_size: int, pin: bool = False, nentity: int = 0, nrelation: int = 0):
+    """``parse_tfrecord_fn`` + ``reshape_function(batch_size)`` (run.py:40-66) -> four torch tensors.  With ``nentity`` /
+    ``nrelation`` the ids are range-checked (IndexError, as the reference's gathers would raise)."""
     lib = _lib.load()
     buf = np.ascontiguousarray(np.frombuffer(payload, dtype=np.uint8)) if not isinstance(payload, np.ndarray) else payload
     if not buf.flags["C_CONTIGUOUS"]:
@@ -68,7 +83,10 @@ def parse_example(payload, batch_size: int, pin: bool = False):
     if n_pos != B * 3 or n_w != B or n_mode != B or n_neg == 0 or n_neg % B:
         raise ValueError("record does not hold a batch of %d: %d positive ids, %d negatives, %d weights, %d modes"
                          % (B, n_pos, n_neg, n_w, n_mode))
-    return pos.view(B, 3), neg[:n_neg].view(B, n_neg // B), w.view(B, 1), mode
+    pos, neg = pos.view(B, 3), neg[:n_neg].view(B, n_neg // B)
+    if nentity or nrelation:
+        check_id_ranges(pos, neg, nentity, nrelation)
+    return pos, neg, w.view(B, 1), mode
 
 
 def build_example(positive_sample, negative_sample, subsampling_weight, mode) -> bytes:
@@ -119,7 +137,7 @@ class TFRecordBatchReader:
     ``(positive [B,3], negative [B,N], weight [B], mode_name)`` instead of the TF-side one."""
 
     def __init__(self, paths, batch_size: int, repeat: bool = True, verify_crc: bool = True, pin: bool = False,
-                 as_torch_batch: bool = False):
+                 as_torch_batch: bool = False, nentity: int = 0, nrelation: int = 0):
         if isinstance(paths, str):
             paths = sorted(glob.glob(paths)) if any(ch in paths for ch in "*?[") else [paths]
         self.paths: List[str] = list(paths)
@@ -127,13 +145,15 @@ class TFRecordBatchReader:
             raise FileNotFoundError("no TFRecord shard matches")
         self.batch_size, self.repeat, self.verify_crc, self.pin = int(batch_size), repeat, verify_crc, pin
         self.as_torch_batch = as_torch_batch
+        self.nentity, self.nrelation = int(nentity or 0), int(nrelation or 0)  # 0: no range check
 
     def __iter__(self):
         while True:
             n = 0
             for path in self.paths:
                 for payload in iter_records(path, self.verify_crc):
-                    pos, neg, w, mode = parse_example(payload, self.batch_size, pin=self.pin)
+                    pos, neg, w, mode = parse_example(payload, self.batch_size, pin=self.pin, nentity=self.nentity,
+                                                        nrelation=self.nrelation)
                     n += 1
                     if self.as_torch_batch:
                         yield pos, neg, w.view(-1), MODE_NAMES[int(mode[0])]

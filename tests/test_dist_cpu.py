@@ -154,6 +154,16 @@ def _worker(rank, world, port, tmp):
     _, _, want_loss = ko.kge_loss(ref((pos_all, neg_all), "tail-batch"), ref(pos_all), torch.cat(step.w_all),
                                   negative_adversarial_sampling=True)
     assert abs(log["loss"] - want_loss.item()) < 1e-6
+
+    # ---------------- unequal batch shapes across ranks are refused, on every rank, before any exchange -------------
+    step2 = Step(gm, opt)
+    step2.w_all = step.w_all
+    bad = ko.synthetic_batch(E, R, B + rank, N, seed=99, mode="tail-batch")
+    try:
+        step2.train_step(iter([bad]), targs)
+        raise AssertionError("unequal B was accepted")
+    except ValueError as e:
+        assert "different batch shapes" in str(e), e
     dist.barrier()
     dist.destroy_process_group()
     open(os.path.join(tmp, "ok%d" % rank), "w").close()

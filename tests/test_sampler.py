@@ -117,3 +117,24 @@ def test_gpu_iterator_feeds_train_step():
         p1, n1, w1, m1 = next(r1)
         assert m == m0 == m1
         assert torch.equal(torch.cat([p0, p1]), p) and torch.equal(torch.cat([n0, n1]), n) and torch.equal(torch.cat([w0, w1]), w)
+
+
+def test_iterator_shares_are_equal_across_ranks_over_epochs():
+    """world > 1: drop_last is forced, so every rank gets exactly B positives in every step -- also across the epoch
+    boundary where a short last batch used to be split 890/889 (or leave a rank empty).  Host logic only (CPU index)."""
+    from customknowledgegraphembedding_b200.sampler import TrainTripleIndex, BidirectionalGpuIterator
+    E, R, B, world = 50, 3, 8, 3
+    tr = _triples(E, R, 70, seed=4)          # 70+ triples, global batch 24: 2 full batches per epoch, remainder dropped
+    idx = TrainTripleIndex(tr, E, R, device="cpu")
+    its = [BidirectionalGpuIterator(idx, 4, B, seed=2, rank=r, world=world) for r in range(world)]
+    assert all(it.drop_last for it in its)
+    for step in range(9):                     # three epochs per mode
+        mode = "head-batch" if step % 2 == 0 else "tail-batch"
+        shares = [it._next_positions(mode) for it in its]
+        assert [len(s[0]) for s in shares] == [B] * world
+        assert [s[1] for s in shares] == [shares[0][1] + r * B for r in range(world)]   # consecutive global indices
+        assert len(set(torch.cat([s[0] for s in shares]).tolist())) == B * world        # disjoint
+    with pytest.raises(ValueError):
+        BidirectionalGpuIterator(idx, 4, B, rank=0, world=2, drop_last=False)
+    with pytest.raises(ValueError):
+        BidirectionalGpuIterator(idx, 4, 64, rank=0, world=2)
