@@ -33,7 +33,7 @@ sys.path.insert(0, REPO)
 WORKLOAD = dict(model="RotatE", nentity=14541, nrelation=237, hidden_dim=1000, gamma=9.0, batch=1024,
                 negatives=256, adversarial_temperature=1.0, lr=5e-5)
 WORKLOAD_NAME = "RotatE FB15k-237-shaped (E=14541,R=237) H=1000 gamma=9 B=1024 N=256 -adv, fwd+loss+bwd+dense Adam"
-CPU_SAMPLE_B = 64  # positives per CPU-baseline step (x256 negatives): ~5 s of host work per step here
+CPU_SAMPLE_B = 64  # positives of the CPU arm's larger probe step (the timed sample is sized from the budget)
 
 
 def log(*a):
@@ -120,10 +120,28 @@ def synthetic_batch(nentity, nrelation, batch, negatives, seed):
     return pos, neg, w, ("head-batch" if seed % 2 == 0 else "tail-batch")
 
 
-def cpu_baseline(steps, warmup, threads=None, budget_s=None):
-    """The oracle's train_step on the host cores: bounded sample (<= CPU_SAMPLE_B positives x N negatives per step).
-    ``budget_s``: the whole run (warm-up + steps) has to end within about that many seconds -- two probe steps (full and
-    1/8 sample) give a linear cost model, and the positives per step are halved until the run fits (never below 8)."""
+def shared_config(world):
+    """The `config` object of BOTH arms (ours and --impl reference): same workload, same keys."""
+    w = WORKLOAD
+    return {"workload": WORKLOAD_NAME,
+            "parallelism": "single GPU" if world == 1 else
+            "dp%d: %d positives per GPU, ONE optimizer step on the global batch of %d; sweep data-parallel over "
+            "positives, apply owner-parallel over entity rows; per-positive buffers exchanged by peer stores over "
+            "NVLink (symmetric memory), updated rows stored into every replica by the Adam epilogue (NVSwitch "
+            "multicast); NCCL moves one float (the weight sum)" % (world, w["batch"], w["batch"] * world),
+            "l2": "no flush: tables + Adam state = %.2f GB per step > 126 MB L2; the entity table itself (116 MB) "
+                  "is partly L2-resident for the gathers, as in any real run" %
+                  ((w["nentity"] * 2 * w["hidden_dim"] + w["nrelation"] * w["hidden_dim"]) * 12 / 1e9),
+            "backward": "fixed-order fused step (no float atomics, no dense gradient table)"}
+
+
+def cpu_baseline(steps, warmup, threads=None, budget_s=30.0):
+    """The oracle's train_step on the host cores, bounded sample of the workload: a first-touch step and two probe
+    steps (64 and 8 positives) give a linear cost model  t(b) = fixed + per_pos * b  (fixed = dense autograd gradient
+    tables + dense Adam over both full tables, paid whatever b is); the positives per step are the LARGEST power of two
+    <= the batch for which warm-up + steps fit ``budget_s`` (never below 8).  Reports the measured throughput of that
+    sample and the model's extrapolation to the full batch (the sample amortises `fixed` over fewer positives, so
+    the measured number understates the CPU arm; the extrapolated one does not)."""
     import torch
     from oracle import kge_oracle as ko
     w = WORKLOAD
@@ -139,26 +157,34 @@ def cpu_baseline(steps, warmup, threads=None, budget_s=None):
         ko.train_step(m, opt, iter([batch]), args)
         return time.perf_counter() - t0
 
-    sample_b = CPU_SAMPLE_B
-    if budget_s is not None and (steps + warmup) > 4:
-        one(10_000, CPU_SAMPLE_B)  # first touch of the tables and the Adam state
-        t_full, t_small = one(10_001, CPU_SAMPLE_B), one(10_002, CPU_SAMPLE_B // 8)
-        per_pos = max(0.0, (t_full - t_small) / (CPU_SAMPLE_B - CPU_SAMPLE_B // 8))
-        fixed = max(0.0, t_small - per_pos * (CPU_SAMPLE_B // 8))
-        while sample_b > 8 and (steps + warmup) * (fixed + per_pos * sample_b) > budget_s:
-            sample_b //= 2
+    one(10_000, 8)  # first touch of the tables and the Adam state
+    t_full, t_small = one(10_001, CPU_SAMPLE_B), one(10_002, CPU_SAMPLE_B // 8)
+    per_pos = max(1e-6, (t_full - t_small) / (CPU_SAMPLE_B - CPU_SAMPLE_B // 8))
+    fixed = max(0.0, t_small - per_pos * (CPU_SAMPLE_B // 8))
+    sample_b = w["batch"]
+    while sample_b > 8 and (steps + warmup) * (fixed + per_pos * sample_b) > budget_s:
+        sample_b //= 2
     times = []
     for s in range(warmup + steps):
         dt = one(s, sample_b)
         if s >= warmup:
             times.append(dt)
     total = sum(times)
+    # refit per_pos with the measured sample (more positives than the probes: a better slope)
+    if sample_b > CPU_SAMPLE_B:
+        per_pos = max(1e-6, (total / len(times) - t_small) / (sample_b - CPU_SAMPLE_B // 8))
+        fixed = max(0.0, t_small - per_pos * (CPU_SAMPLE_B // 8))
+    full = w["batch"] * w["negatives"] / (fixed + per_pos * w["batch"])
     return {"value": sample_b * w["negatives"] * len(times) / total, "unit": "triples*neg/s", "cores": cores,
             "kind": "port",
-            "sample": "%d steps of %d positives x %d negatives (1/%d of the batch) incl. dense Adam over the full "
-                      "tables, torch %s CPU fp32" % (len(times), sample_b, w["negatives"],
-                                                    w["batch"] // sample_b, torch.__version__),
-            "ms_per_step": 1e3 * total / len(times)}
+            "sample": "%d steps of %d positives x %d negatives (%s of the batch: the largest power of two whose run fits "
+                      "%.0f s) incl. dense Adam over the full tables, torch %s CPU fp32; cost model t(b) = %.3f s + "
+                      "%.4f s * b -> %.0f triples*neg/s extrapolated to the full batch of %d" % (
+                          len(times), sample_b, w["negatives"],
+                          "all" if sample_b == w["batch"] else "1/%d" % (w["batch"] // sample_b), budget_s,
+                          torch.__version__, fixed, per_pos, full, w["batch"]),
+            "ms_per_step": 1e3 * total / len(times), "sample_positives": sample_b,
+            "full_batch_extrapolated": full, "fixed_s": fixed, "per_positive_s": per_pos}
 
 
 def run_reference(a):
@@ -171,12 +197,51 @@ def run_reference(a):
         "impl": "reference", "metric": "train_triples_neg_per_sec", "value": base["value"], "unit": "triples*neg/s",
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": base["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAME, "reference_arm": "CPU oracle (port) on host cores; " + base["sample"]},
-        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "config": shared_config(a.gpus),  # the same object as the other arm's: same workload, same keys
+        "reference_arm": "CPU oracle (port of the absent PyTorch submodule) on the host cores; " + base["sample"],
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "full_batch_extrapolated")},
         "e2e": {"value": base["value"], "unit": "triples*neg/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
+
+
+def table_checksum(model):
+    """Exact integer checksum of both tables (fp32 bit patterns summed as int64)."""
+    import torch
+    out = []
+    for t in (model.entity_embedding, model.relation_embedding):
+        out.append(int(t.detach().contiguous().view(torch.int32).to(torch.int64).sum().item()))
+    return out
+
+
+def run_dist_check(kb, model, step_obj, targs, w, dev, rank, world, dist, make_ref, nsteps=3, seed0=777_000):
+    """Before timing: `nsteps` global steps of the N-rank step against ONE GPU's KGEModel.train_step on the concatenated
+    batch (run by rank 0 on a private replica built by ``make_ref``): per-step loss within 2e-6 relative, tables within
+    5e-3 * lr after the steps.  The batches of every rank are seeded, so rank 0 can rebuild the global batch."""
+    import torch
+    lr = w["lr"]
+    ref = ropt = None
+    if rank == 0:
+        ref = make_ref()
+        ropt = torch.optim.Adam(filter(lambda p: p.requires_grad, ref.parameters()), lr=lr)
+    loss_rel, losses = 0.0, []
+    for s in range(nsteps):
+        batches = [synthetic_batch(w["nentity"], w["nrelation"], w["batch"], w["negatives"], seed=seed0 + 1000 * r + s)
+                   for r in range(world)]
+        p, n, sw, m = batches[rank]
+        log = step_obj.train_step(iter([(p.to(dev), n.to(dev), sw.to(dev), m)]), targs)
+        if rank == 0:
+            cat = (torch.cat([b[0] for b in batches]).to(dev), torch.cat([b[1] for b in batches]).to(dev),
+                   torch.cat([b[2] for b in batches]).to(dev), m)
+            rlog = kb.KGEModel.train_step(ref, ropt, iter([cat]), targs)
+            loss_rel = max(loss_rel, abs(log["loss"] - rlog["loss"]) / abs(rlog["loss"]))
+            losses.append((log["loss"], rlog["loss"]))
+    out = None
+    if rank == 0:
+        out = {"steps": nsteps, "global_batch": w["batch"] * world, "loss_rel_max": loss_rel, "losses": losses,
+               "tol_loss_rel": 2e-6, "tol_table": 5e-3 * lr}
+    return ref, out
 
 
 def run_ours(a):
@@ -254,6 +319,22 @@ def run_ours(a):
             ms = float(t.item())
         return ms
 
+    dist_check = None
+    if dp is not None and not a.no_dist_check:
+        def make_ref():
+            ref = kb.KGEModel(w["model"], w["nentity"], w["nrelation"], w["hidden_dim"], w["gamma"], True, False).to(dev)
+            ref.load_state_dict(model.state_dict())
+            return ref
+        ref, dist_check = run_dist_check(kb, model, dp, targs, w, dev, rank, world, dist, make_ref)
+        if rank == 0:
+            dE = float((model.entity_embedding.detach() - ref.entity_embedding.detach()).abs().max())
+            dR = float((model.relation_embedding.detach() - ref.relation_embedding.detach()).abs().max())
+            dist_check.update(max_abs_diff_entity=dE, max_abs_diff_relation=dR)
+            dist_check["ok_before_timing"] = bool(dist_check["loss_rel_max"] <= dist_check["tol_loss_rel"]
+                                                  and max(dE, dR) <= dist_check["tol_table"])
+        del ref
+        torch.cuda.empty_cache()
+
     sampler = ClockSampler(local_rank)
     device_steps(W, 0)  # warm-up (also allocates the workspace and Adam state)
     sampler.start()
@@ -281,11 +362,26 @@ def run_ours(a):
             else:
                 last_log.update(kb.KGEModel.train_step(model, opt, it, targs))
     ms_e2e = timed(e2e_steps)
+    # ---- after the timed train regions: every replica holds bit-identical tables ---------------------
+    if dp is not None and not a.no_dist_check:
+        cs = torch.tensor(table_checksum(model), dtype=torch.int64, device=dev)
+        allcs = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        if rank == 0:
+            stack = torch.stack(allcs)
+            spread = (stack.max(0).values - stack.min(0).values).tolist()
+            dist_check["checksum_spread_after_timing"] = spread
+            dist_check["checksums_rank0"] = cs.tolist()
+            dist_check["ok"] = bool(dist_check["ok_before_timing"] and spread == [0, 0])
+            if not dist_check["ok"]:
+                log("DIST CHECK FAILED: %s" % json.dumps(dist_check))
     # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
     if a.train_only:
         smp = ev = ev_gemm = None
         ev_10m = {"skipped": "--train-only"}
+        tr_interht = train_config_bench(CONFIG3, dev, timed, min(K, 50)) if (world == 1 and a.interht) else None
     else:
+        tr_interht = train_config_bench(CONFIG3, dev, timed, min(K, 50)) if world == 1 else None
         smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
         ev = eval_bench(model, w, dev, timed, rank, world)
         ev_gemm = eval_gemm_bench(dev, timed, world)
@@ -313,15 +409,7 @@ def run_ours(a):
         "metric": "train_triples_neg_per_sec", "value": total_units / (ms_value * 1e-3), "unit": "triples*neg/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": step_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAME,
-                   "parallelism": "single GPU" if world == 1 else
-                   "dp%d: %d positives per GPU, ONE optimizer step on the global batch of %d (sweep data-parallel, "
-                   "apply owner-parallel over entity rows; NCCL all-gather of per-positive buffers and updated rows)"
-                   % (world, w["batch"], w["batch"] * world),
-                   "l2": "no flush: tables + Adam state + gradients = %.2f GB per step > 126 MB L2; the entity table "
-                         "itself (116 MB) is L2-resident for the gathers, as in any real run" %
-                         ((w["nentity"] * 2 * w["hidden_dim"] + w["nrelation"] * w["hidden_dim"]) * 16 / 1e9),
-                   "backward": "deterministic" if a.deterministic else "atomic"},
+        "config": shared_config(world),
         "e2e": {"value": total_units / (ms_e2e * 1e-3), "unit": "triples*neg/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 16, "ms_per_step": ms_e2e / K, "loss": last_log.get("loss")},
         "gpu_launches": int(sum(v[1] for v in stages.values())),
@@ -338,6 +426,8 @@ def run_ours(a):
                               "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12}},
         "stages_ms_per_step": {k: v[0] / K for k, v in stages.items()},
         "profiled_region_ms_per_step": ms_prof / K,
+        "dist_check": dist_check,
+        "train_interht": tr_interht,
         "gpu_sampler": smp,
         "eval": ev,
         "eval_gemm": ev_gemm,
@@ -345,11 +435,74 @@ def run_ours(a):
         "clocks": sampler.summary(),
     }
     log("timing done; running the bounded CPU baseline sample ...")
-    base = cpu_baseline(steps=2, warmup=1) if not a.no_cpu_baseline else None
-    line["cpu_baseline"] = ({k: base[k] for k in ("value", "unit", "cores", "kind", "sample")} if base else None)
+    base = cpu_baseline(steps=2, warmup=1, budget_s=30.0) if not a.no_cpu_baseline else None
+    line["cpu_baseline"] = ({k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "full_batch_extrapolated")}
+                            if base else None)
     emit(line)
     if dist is not None:
         dist.destroy_process_group()
+
+
+CONFIG3 = dict(model="InterHT", nentity=40943, nrelation=11, hidden_dim=1000, gamma=24.0, batch=1024, negatives=512,
+               adversarial_temperature=1.0, lr=5e-5)
+
+
+def train_config_bench(cfg, dev, timed, K, semantics=("pytorch", "tf")):
+    """BASELINE.json configs[2]: InterHT, wn18rr sizes (40943 entities, 11 relations), H = 1000, gamma 24, batch 1024,
+    512 negatives, one B200 -- device-resident batches, K steps per timed region, per-stage CUDA events.  Two loss
+    semantics: 'pytorch' (KGEModel.train_step: detached softmax weights, torch Adam) and 'tf' (the reference's own
+    Trainer.train_step_fn, tensorflow_codes/supervisor.py:15-28 over model.py:148-224: gradient THROUGH the softmax
+    weights, temperature 1, Keras Adam epsilon placement)."""
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import _lib
+    lib = _lib.load()
+    de, dr, tr = {"InterHT": (True, False, True), "RotatE": (True, False, False)}[cfg["model"]]
+    E, R, H, B, N = cfg["nentity"], cfg["nrelation"], cfg["hidden_dim"], cfg["batch"], cfg["negatives"]
+    De, Dr = (2 * H if de else H), (3 * H if tr else (2 * H if dr else H))
+    peak, peak_src = peaks()
+    units = B * N
+    # SURVEY 8(d) per-step byte model
+    step_bytes = units * (3 * De * 4 + 16) + B * (2 * De + Dr) * 12 + (E * De + R * Dr) * 24
+    out = {"workload": "%s E=%d R=%d H=%d gamma=%g B=%d N=%d -adv" % (cfg["model"], E, R, H, cfg["gamma"], B, N),
+           "unit": "triples*neg/s", "algorithmic_bytes_per_step": step_bytes}
+    nb = 8
+    batches = []
+    for s in range(nb):
+        p, n, sw, m = synthetic_batch(E, R, B, N, seed=5000 + s)
+        batches.append((p.to(dev), n.to(dev), sw.to(dev), m))
+    for sem in semantics:
+        torch.manual_seed(0)
+        model = kb.KGEModel(cfg["model"], E, R, H, cfg["gamma"], de, dr, tr).to(dev)
+        opt = torch.optim.Adam(filter(lambda p: p.requires_grad, model.parameters()), lr=cfg["lr"],
+                               eps=1e-7 if sem == "tf" else 1e-8)
+        group = model._fused_adam_plan(opt)
+
+        def steps(n):
+            for i in range(n):
+                p, ng, sw, m = batches[i % nb]
+                model._fused_step(opt, group, p, ng, sw, m, True, cfg["adversarial_temperature"], False, 0.0,
+                                  detach_weights=(sem != "tf"), keras_adam=(sem == "tf"))
+        steps(3)
+        ms = timed(lambda: steps(K))
+        lib.kge_profile_enable(1)
+        timed(lambda: steps(K))
+        nst = lib.kge_profile_num_stages()
+        ms_sum, launches = (C.c_float * nst)(), (C.c_int64 * nst)()
+        lib.kge_profile_read(ms_sum, launches, 1)
+        lib.kge_profile_enable(0)
+        stages = {lib.kge_profile_stage_name(i).decode(): ms_sum[i] / K for i in range(nst) if launches[i] > 0}
+        step_ms = ms / K
+        out[sem] = {"value": units * K / (ms * 1e-3), "ms_per_step": step_ms, "stages_ms_per_step": stages,
+                    "gpu_launches_per_step": int(sum(launches)) // K,
+                    "roofline": {"bound": "hbm", "achieved": step_bytes / (step_ms * 1e-3) / 1e9, "peak": peak,
+                                 "unit": "GB/s", "frac": step_bytes / (step_ms * 1e-3) / 1e9 / peak,
+                                 "frac_of_8TBs": step_bytes / (step_ms * 1e-3) / 8e12, "peak_source": peak_src,
+                                 "note": "whole step against SURVEY 8(d)'s byte model (three passes over the candidate "
+                                         "rows + p/m/v read+write); the 327 MB table does not fit the 126 MB L2"}}
+        del model, opt
+        torch.cuda.empty_cache()
+    return out
 
 
 def eval_bench(model, w, dev, timed, rank, world=1):
@@ -552,6 +705,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eval10m", action="store_true", help="skip the 10M-entity sharded eval section (80 GB table)")
     ap.add_argument("--train-only", action="store_true", help="tuning loops: only the headline train step sections")
+    ap.add_argument("--interht", action="store_true", help="with --train-only: also time BASELINE configs[2] (InterHT)")
+    ap.add_argument("--no-dist-check", action="store_true", help="N > 1: skip the correctness check around the timed region")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)  # K steps as asked; the positives per step shrink until the run fits ~3 minutes (cpu_baseline)

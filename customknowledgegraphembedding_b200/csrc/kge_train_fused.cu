@@ -67,9 +67,25 @@ __device__ __forceinline__ void load_coords(float (&x)[CP][CH][4], const float* 
         }
 }
 
-// dL/ds of one negative score: scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s) without -adv)
-__device__ __forceinline__ float dscore_value(float s, float m_b, float scale_b, int adv, float alpha) {
-    return adv ? scale_b * expf(s * alpha - m_b) * sigmoidf(s) : scale_b * sigmoidf(s);
+// dL/ds of one negative score: scale_b * exp(alpha*s - m_b) * sigma(s)   (or scale_b * sigma(s) without -adv).
+// Attached softmax weights (the TF graph model, /root/reference/tensorflow_codes/model.py:168-171,195-198: no
+// stop-gradient on softmax(s)): d/ds_n sum_m p_m l_m = p_n (l'_n + alpha (l_n - Lbar)), l = logsigmoid(-s),
+// Lbar = sum_m p_m l_m  ->  scale_b * e_n * (sigma(s_n) - alpha (l_n - Lbar)).
+__device__ __forceinline__ float dscore_value(float s, float m_b, float scale_b, int adv, float alpha, bool att = false,
+                                              float lbar = 0.f) {
+    if (!adv) return scale_b * sigmoidf(s);
+    const float e = expf(s * alpha - m_b);
+    if (att) return scale_b * e * (sigmoidf(s) - alpha * (log_sigmoid(-s) - lbar));
+    return scale_b * e * sigmoidf(s);
+}
+
+// 1 / |x| of an InterHT half-row from its sum of squares.  eps = 0: tf.linalg.normalize (model.py:215-218, no clamp);
+// eps > 0: F.normalize(x, 2, -1) -- x / max(|x|, eps).  proj = 0 where the clamp is active: there y = x / eps and the
+// backward has no projection term.
+__device__ __forceinline__ float inv_norm(float ss, float eps, float& proj) {
+    const float n = sqrtf(ss);
+    proj = (eps > 0.f && n < eps) ? 0.f : 1.f;
+    return 1.0f / ((eps > 0.f) ? fmaxf(n, eps) : n);
 }
 
 struct SweepArgs {
@@ -100,14 +116,16 @@ struct SweepArgs {
 // ------------------------------------------------------------------------------------------------
 // PART (SweepArgs.part) is a template parameter so that the staging and merge passes of the split sweep do not carry
 // the register footprint of the row-group sweep they skip.
-template <int MODEL, int CH, int RPI, int PART>
+// ATT: attached softmax weights (TF graph-model gradient) -- a second dL/dq accumulator (sum_n e_n ds_n/dq, the factor
+// of alpha * Lbar, known only after the last row) rides along; row-group sweep (PART 0) only.
+template <int MODEL, int CH, int RPI, int PART, bool ATT = false>
 __global__ void __launch_bounds__(256)
 train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL), RP = rel_planes_of(MODEL);
     __shared__ float red[4 * 32 * 2];      // block reductions: up to 8 values x 32 warps
     __shared__ float red2[2][RPI * 32];    // row-sum partials of the sweep, double-buffered by row group
-    __shared__ float sh_cn[RPI][2], sh_fin[8];
+    __shared__ float sh_cn[RPI][2], sh_fin[8];  // sh_fin: m, z, l, g, g2
 
     const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = (T + 31) >> 5;
     const int H = P.H, N = A.N;
@@ -153,8 +171,9 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                     ss[1] = fmaf(fe[1][j][i], fe[1][j][i], ss[1]);
                 }
             block_reduce_vals<2>(ss, red);
-            nrm[0] = 1.0f / sqrtf(ss[0]);
-            nrm[1] = 1.0f / sqrtf(ss[1]);
+            float pj;
+            nrm[0] = inv_norm(ss[0], P.interht_eps, pj);
+            nrm[1] = inv_norm(ss[1], P.interht_eps, pj);
         }
 #pragma unroll
         for (int j = 0; j < CH; ++j)
@@ -194,8 +213,15 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         for (int j = 0; j < CH; ++j)
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[p][j][i] = 0.f;
+    float acc2[ATT ? QP : 1][ATT ? CH : 1][4];  // ATT: sum_n e_n ds_n/dq
+#pragma unroll
+    for (int p = 0; p < (ATT ? QP : 1); ++p)
+#pragma unroll
+        for (int j = 0; j < (ATT ? CH : 1); ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc2[p][j][i] = 0.f;
     // online-softmax state, replicated in the lanes of warp 0
-    float m_run = -INFINITY, z_run = 0.f, l_run = 0.f, g_run = 0.f;
+    float m_run = -INFINITY, z_run = 0.f, l_run = 0.f, g_run = 0.f, g2_run = 0.f;
 
     // every candidate use is counted for the bucket build (integer atomics, off the critical path)
     if (A.counts != nullptr)
@@ -231,8 +257,9 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
             }
             block_reduce_vals<2 * RPI>(ss, red);
             if (tid < RPI) {
-                sh_cn[tid][0] = 1.0f / sqrtf(ss[2 * tid]);
-                sh_cn[tid][1] = 1.0f / sqrtf(ss[2 * tid + 1]);
+                float pj;
+                sh_cn[tid][0] = inv_norm(ss[2 * tid], P.interht_eps, pj);
+                sh_cn[tid][1] = inv_norm(ss[2 * tid + 1], P.interht_eps, pj);
             }
             __syncthreads();
         }
@@ -267,7 +294,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         __syncthreads();
         // Every warp finishes the rows itself (lane rr takes row rr) and advances its own copy of the softmax
         // recurrence: identical arithmetic in every warp, so no second barrier and no serial section.
-        float wgt_lane, sc = 1.0f;
+        float wgt_lane, wgt2_lane = 0.f, sc = 1.0f;
         {
             const int n = n0 + lane;
             const bool valid = lane < RPI && n < N;
@@ -285,9 +312,14 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                 const float e = valid ? expf(a - m_new) : 0.f;
                 z_run = z_run * sc + warp_sum(e);
                 l_run = l_run * sc + warp_sum(e * ls);
-                if (MODEL == KGE_PROTATE) g_run = g_run * sc + warp_sum(e * sig * tot);
-                m_run = m_new;
                 wgt_lane = e * sig;
+                if constexpr (ATT) {
+                    wgt_lane = e * (sig - A.alpha * ls);
+                    wgt2_lane = e;
+                    if (MODEL == KGE_PROTATE) g2_run = g2_run * sc + warp_sum(e * tot);
+                }
+                if (MODEL == KGE_PROTATE) g_run = g_run * sc + warp_sum(wgt_lane * tot);
+                m_run = m_new;
             } else {
                 l_run += warp_sum(ls);
                 if (MODEL == KGE_PROTATE) g_run += warp_sum(sig * tot);
@@ -302,10 +334,19 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                 for (int j = 0; j < CH; ++j)
 #pragma unroll
                     for (int i = 0; i < 4; ++i) acc[p][j][i] *= sc;
+            if constexpr (ATT) {
+#pragma unroll
+                for (int p = 0; p < QP; ++p)
+#pragma unroll
+                    for (int j = 0; j < CH; ++j)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc2[p][j][i] *= sc;
+            }
         }
 #pragma unroll
         for (int rr = 0; rr < RPI; ++rr) {
             const float wgt = __shfl_sync(0xffffffffu, wgt_lane, rr);
+            const float wgt2 = ATT ? __shfl_sync(0xffffffffu, wgt2_lane, rr) : 0.f;
 #pragma unroll
             for (int j = 0; j < CH; ++j)
 #pragma unroll
@@ -317,6 +358,13 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                     else dq_accumulate<MODEL, false>(aa, dd, s1, wgt, kc);
 #pragma unroll
                     for (int p = 0; p < QP; ++p) acc[p][j][i] = aa[p];
+                    if constexpr (ATT) {
+                        float a2[3] = {acc2[0][j][i], (QP > 1) ? acc2[QP > 1 ? 1 : 0][j][i] : 0.f, (QP > 2) ? acc2[QP > 2 ? 2 : 0][j][i] : 0.f};
+                        if (head) dq_accumulate<MODEL, true>(a2, dd, s1, wgt2, kc);
+                        else dq_accumulate<MODEL, false>(a2, dd, s1, wgt2, kc);
+#pragma unroll
+                        for (int p = 0; p < QP; ++p) acc2[p][j][i] = a2[p];
+                    }
                 }
         }
     }
@@ -389,19 +437,30 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         sh_fin[1] = z_run;
         sh_fin[2] = l_run;
         sh_fin[3] = g_run;
+        sh_fin[4] = g2_run;
     }
     __syncthreads();
     const float m_b = sh_fin[0];
     const float denom = A.adv ? sh_fin[1] : (float)N;
     const float negterm = sh_fin[2] / denom;
     const float scale_b = 0.5f * coef / denom;  // dL/ds_n = scale_b * e_n * sigma(s_n)
-    const float gsum = sh_fin[3];
+    const bool att = ATT && A.adv;
+    const float att_k = att ? A.alpha * negterm : 0.f;  // weight of the second accumulator: alpha * Lbar
+    const float gsum = sh_fin[3] + att_k * sh_fin[4];
+    if constexpr (ATT) {
+#pragma unroll
+        for (int p = 0; p < QP; ++p)
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[p][j][i] = fmaf(att_k, acc2[p][j][i], acc[p][j][i]);
+    }
     // F2b folded in: S[b,:] <- dL/ds.  The raw scores are not read again by anybody; every later consumer (the entity
     // kernel of this rank, or of the row owners after the exchange) wants the derivative, and here the work stays with
     // the rank that owns the positive instead of being repeated on the global batch by every rank.
     for (int n = tid; n < N; n += T) {
         const long long i = b * N + n;
-        A.S[i] = dscore_value(A.S[i], m_b, scale_b, A.adv, A.alpha);
+        A.S[i] = dscore_value(A.S[i], m_b, scale_b, A.adv, A.alpha, att, negterm);
     }
     // dL/dq of the negative part
 #pragma unroll
@@ -417,6 +476,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     load_coords<CP, CH>(te, trow, H, tid, T, H);
     load_coords<RP, CH>(rv, rrow, H, tid, T, H);
     float nh[2] = {0.f, 0.f}, nt[2] = {0.f, 0.f};
+    float pjh[2] = {1.f, 1.f}, pjt[2] = {1.f, 1.f};  // InterHT: 0 where the F.normalize clamp is active (no projection)
     if constexpr (MODEL == KGE_INTERHT) {
         float ss[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -429,8 +489,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                 ss[3] = fmaf(te[1][j][i], te[1][j][i], ss[3]);
             }
         block_reduce_vals<4>(ss, red);
-        nh[0] = 1.0f / sqrtf(ss[0]); nh[1] = 1.0f / sqrtf(ss[1]);
-        nt[0] = 1.0f / sqrtf(ss[2]); nt[1] = 1.0f / sqrtf(ss[3]);
+        nh[0] = inv_norm(ss[0], P.interht_eps, pjh[0]); nh[1] = inv_norm(ss[1], P.interht_eps, pjh[1]);
+        nt[0] = inv_norm(ss[2], P.interht_eps, pjt[0]); nt[1] = inv_norm(ss[3], P.interht_eps, pjt[1]);
     }
     // q1 = planes in single form (fixed entity = head); equal to q in tail-batch mode
     float q1[QP][CH][4], crs[CH][4], srs[CH][4];
@@ -491,6 +551,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         }
     if constexpr (MODEL == KGE_INTERHT) {
         block_reduce_vals<2>(dots, red);
+        dots[0] *= pjt[0];
+        dots[1] *= pjt[1];
 #pragma unroll
         for (int j = 0; j < CH; ++j)
 #pragma unroll
@@ -521,6 +583,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
                 dA[3] = fmaf(q[1][j][i] - 1.0f, acc[1][j][i], dA[3]);
             }
         block_reduce_vals<4>(dA, red);
+        dA[0] *= pjh[0]; dA[1] *= pjh[1];  // single-form chain: fixed entity = h
+        dA[2] *= pjt[0]; dA[3] *= pjt[1];  // mode-form chain (head-batch): fixed entity = t
     }
     float* gh = A.GH + b * (long long)P.De;
     float* gt = A.GT + b * (long long)P.De;
@@ -1068,7 +1132,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
             for (int l = tid; l < 2 * lines; l += T)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"((l < lines ? mline : vline - (size_t)lines * 128) + (size_t)l * 128));
         }
-        float cn[2] = {0.f, 0.f};
+        float cn[2] = {0.f, 0.f}, cpj[2] = {1.f, 1.f};
         if constexpr (MODEL == KGE_INTERHT) {
             if (beg < end) {  // uniform over the block
                 float ss[2] = {0.f, 0.f};
@@ -1080,8 +1144,8 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
                         ss[1] = fmaf(c[1][j][i], c[1][j][i], ss[1]);
                     }
                 block_reduce_vals<2>(ss, red);
-                cn[0] = 1.0f / sqrtf(ss[0]);
-                cn[1] = 1.0f / sqrtf(ss[1]);
+                cn[0] = inv_norm(ss[0], P.interht_eps, cpj[0]);
+                cn[1] = inv_norm(ss[1], P.interht_eps, cpj[1]);
             }
         }
         for (int base = beg; base < end; base += kUseChunk) {
@@ -1132,6 +1196,8 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
                             dots[1] = fmaf(bh, dbc[j][k], dots[1]);
                         }
                     block_reduce_vals<2>(dots, red);
+                    dots[0] *= cpj[0];  // clamped half-row (F.normalize eps): y = x / eps, no projection term
+                    dots[1] *= cpj[1];
 #pragma unroll
                     for (int j = 0; j < CH; ++j)
 #pragma unroll
@@ -1324,8 +1390,10 @@ struct FusedWs {
 static inline int f1w_parts(int64_t N) { return (int)std::max<int64_t>(1, std::min<int64_t>(8, (N + 31) / 32)); }
 static int g_sweep_variant = 1;  // 1 = warp per row (F1w) where it applies, 0 = row groups per CTA
 void train_set_sweep_variant(int v) { g_sweep_variant = v ? 1 : 0; }
-static inline bool f1w_applies(const Params& P) {
-    return g_sweep_variant == 1 && P.model != KGE_INTERHT && P.H % 4 == 0 && P.H <= 1024;
+static inline bool att_weights(const kge_loss_opts& lo) { return !lo.detach_weights && lo.negative_adversarial_sampling; }
+static inline bool f1w_applies(const Params& P, const kge_loss_opts& lo) {
+    // (attached softmax weights carry a second dL/dq accumulator: row-group sweep, where a thread owns few coordinates)
+    return g_sweep_variant == 1 && P.model != KGE_INTERHT && P.H % 4 == 0 && P.H <= 1024 && !att_weights(lo);
 }
 
 static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
@@ -1369,8 +1437,6 @@ size_t train_sweep_workspace_bytes(const Params& P, int64_t B, int64_t N) {
 
 bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, int64_t N, const void* ent,
                            const void* rel) {
-    if (!lo.detach_weights && lo.negative_adversarial_sampling) return false;  // TF graph-model gradient: v1 path
-    if (P.interht_eps != 0.f) return false;
     if (!vec4_ok(P, ent, rel)) return false;
     if (P.H > 4096) return false;
     if (B * N + 2 * B >= 0x7fffffffLL || P.E >= 0x7fffffffLL) return false;
@@ -1503,7 +1569,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
                     lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
                     fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
-        if (fc.phase != 2 && ws.PA != nullptr && f1w_applies(P)) {
+        if (fc.phase != 2 && ws.PA != nullptr && f1w_applies(P, lo)) {
             if constexpr (MODEL != KGE_INTERHT) {
                 // split sweep: stage Q | one warp per candidate row | merge + positive score + chain rule
                 ps.launches(3);
@@ -1522,7 +1588,11 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 2>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
             }
         } else {
-            if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
+            if (att_weights(lo))
+                e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0, true>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A);
+            else
+                e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0, false>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A);
+            if (e != cudaSuccess) return e;
             if (fc.stage_ev != nullptr && (e = cudaEventRecord(fc.stage_ev, st)) != cudaSuccess) return e;  // (Q is final with the kernel)
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;

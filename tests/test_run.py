@@ -88,7 +88,7 @@ def test_readme_command_runs_the_tf_trainer(tmp_path, capsys):
     opt = ko.KerasAdam([om.entity_embedding, om.relation_embedding], lr=1e-5)  # lrfn(0) = LR_START
     pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=0)
     want = ko.tf_train_step(om, opt, (pos, neg, w.view(-1, 1), torch.full((B,), 0 if mode == "head-batch" else 1)))
-    np.testing.assert_allclose(seen["losses"][0], float(want["loss"]), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(seen["losses"][0], float(want), rtol=1e-5, atol=1e-6)
     with pytest.raises(IndexError):  # ids beyond --nentity: refused like tf.gather would
         run.main(cmd.replace("--nentity %d" % E, "--nentity 50").split())
 
@@ -145,7 +145,7 @@ def test_resume_keeps_the_staged_fast_path(tmp_path):
     data, save = str(tmp_path / "data"), str(tmp_path / "model")
     _write_dataset(data)
     common = ["--data_path", data, "--model", "RotatE", "-de", "-d", "16", "-g", "6.0", "-n", "8", "-b", "16", "-adv",
-              "-lr", "0.01", "-save", save, "--log_steps", "1000", "--save_checkpoint_steps", "1000", "--valid_steps", "1000"]
+              "-lr", "0.01", "-save", save, "--warm_up_steps", "1000", "--log_steps", "1000", "--save_checkpoint_steps", "1000", "--valid_steps", "1000"]
     run.main(["--do_train", "--max_steps", "5"] + common)
     model, _ = run.main(["--do_train", "-init", save, "--max_steps", "9"] + common)
     ck = torch.load(os.path.join(save, "checkpoint"), weights_only=False)
