@@ -386,6 +386,11 @@ def run_ours(a):
         ev = eval_bench(model, w, dev, timed, rank, world)
         ev_gemm = eval_gemm_bench(dev, timed, world)
         ev_10m = eval_10m_bench(dev, timed, world) if not a.no_eval10m else {"skipped": "--no-eval10m"}
+    tr_sharded = None
+    if a.sharded or not a.train_only:
+        tr_sharded = {"yago3-10": train_sharded_bench("yago3-10", dev, timed, rank, world, dist, min(K, 20))}
+        if not a.no_eval10m:
+            tr_sharded["synthetic-10M"] = train_sharded_bench("synthetic-10M", dev, timed, rank, world, dist, min(K, 10))
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -428,6 +433,7 @@ def run_ours(a):
         "profiled_region_ms_per_step": ms_prof / K,
         "dist_check": dist_check,
         "train_interht": tr_interht,
+        "train_sharded": tr_sharded,
         "gpu_sampler": smp,
         "eval": ev,
         "eval_gemm": ev_gemm,
@@ -502,6 +508,111 @@ def train_config_bench(cfg, dev, timed, K, semantics=("pytorch", "tf")):
                                          "rows + p/m/v read+write); the 327 MB table does not fit the 126 MB L2"}}
         del model, opt
         torch.cuda.empty_cache()
+    return out
+
+
+SHARDED = {
+    "yago3-10": dict(model="RotatE", nentity=123182, nrelation=37, hidden_dim=1000, gamma=24.0, batch=1024, negatives=1024,
+                     adversarial_temperature=1.0, lr=5e-5),
+    "synthetic-10M": dict(model="RotatE", nentity=10_000_000, nrelation=237, hidden_dim=1000, gamma=24.0, batch=1024,
+                          negatives=1024, adversarial_temperature=1.0, lr=5e-5),
+}
+
+
+def train_sharded_bench(name, dev, timed, rank, world, dist, K, check=True):
+    """BASELINE.json configs[4]: RotatE H = 1000, 1024 negatives, batch 1024 per GPU, entity table (and Adam state)
+    ROW-SHARDED over the ranks -- no rank holds the table.  Per step and rank: touched ids by bitmap + scan, rows pulled
+    from their owners over NVLink into a compact table, sweep on the compact table, per-positive buffers to the owners by
+    peer stores, owners update their rows in place.  ONE optimizer step on the global batch (weak scaling).
+    `check`: 3 steps against KGEModel.train_step of one GPU on the concatenated batch (full table on rank 0)."""
+    import torch
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import dist as kd
+    cfg = SHARDED[name]
+    E, R, H, B, N = cfg["nentity"], cfg["nrelation"], cfg["hidden_dim"], cfg["batch"], cfg["negatives"]
+    De = 2 * H
+    lo, hi = kd.shard_range(E, rank, world)
+    cap = min(E, B * N + 2 * B)
+    need = (hi - lo) * De * 4 * 4 + cap * De * 4 + world * B * (N * 12 + 4 * De * 4) + (6 << 30)
+    free, _ = torch.cuda.mem_get_info(dev)
+    fits = torch.tensor([1 if free >= need else 0], device=dev)
+    if dist is not None:
+        dist.all_reduce(fits, op=dist.ReduceOp.MIN)
+    if int(fits.item()) == 0:
+        return {"skipped": "needs %.0f GB free per GPU at %d ranks, %.0f GB available" % (need / 1e9, world, free / 1e9)}
+    targs = argparse.Namespace(cuda=True, negative_adversarial_sampling=True, adversarial_temperature=1.0, uni_weight=False,
+                               regularization=0.0)
+    model = kd.RowShardedKGEModel(cfg["model"], E, R, H, cfg["gamma"], True, False, device=dev, seed=11)
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, model.parameters()), lr=cfg["lr"])
+    step = kd.RowShardedStep(model, opt)
+    out = {"workload": "RotatE E=%d R=%d H=1000 gamma=%g B=%d per GPU N=%d -adv, row-sharded table" % (E, R, cfg["gamma"], B, N),
+           "unit": "triples*neg/s", "n_gpus": world, "rows_per_gpu": hi - lo, "scaling": "weak"}
+    # ---- correctness before timing (tables that fit one GPU three times over) ------------------------------------
+    if check and E * De * 4 * 4 < 100e9:
+        ref = None
+        if rank == 0:
+            full = kd.RowShardedKGEModel(cfg["model"], E, R, H, cfg["gamma"], True, False, device=dev, seed=11, rank_world=(0, 1))
+            ref = kb.KGEModel(cfg["model"], E, R, H, cfg["gamma"], True, False).to(dev)
+            with torch.no_grad():
+                ref.entity_embedding.copy_(full.entity_embedding)
+                ref.relation_embedding.copy_(full.relation_embedding)
+            del full
+
+        def make_ref():
+            return ref
+        wl = dict(cfg)
+        ref, dc = run_dist_check(kb, model, step, targs, wl, dev, rank, world, dist, make_ref, seed0=555_000)
+        table = ref.entity_embedding.detach().clone() if rank == 0 else torch.empty((E, De), dtype=torch.float32, device=dev)
+        rel = ref.relation_embedding.detach().clone() if rank == 0 else torch.empty_like(model.relation_embedding)
+        if dist is not None:
+            dist.broadcast(table, src=0)
+            dist.broadcast(rel, src=0)
+        d = torch.stack([(model.entity_embedding.detach() - table[lo:hi]).abs().max() if hi > lo else torch.zeros((), device=dev),
+                         (model.relation_embedding.detach() - rel).abs().max()])
+        if dist is not None:
+            dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            dc.update(max_abs_diff_entity=float(d[0]), max_abs_diff_relation=float(d[1]))
+            dc["ok"] = bool(dc["loss_rel_max"] <= dc["tol_loss_rel"] and float(d.max()) <= dc["tol_table"])
+            out["dist_check"] = dc
+        del table, rel, ref
+        torch.cuda.empty_cache()
+    nb = 4
+    batches = []
+    for s in range(nb):
+        p, n, sw, m = synthetic_batch(E, R, B, N, seed=9000 + 1000 * rank + s)
+        batches.append((p.to(dev), n.to(dev), sw.to(dev), m))
+
+    def steps(k):
+        for i in range(k):
+            step.train_step(iter([batches[i % nb]]), targs, sync=False)
+    steps(3)
+    ms = timed(lambda: steps(K))
+    step_ms = ms / K
+    peak, peak_src = peaks()
+    units = B * N
+    # per GPU and step: candidate rows once from the compact table in the sweep, once more as the pulled unique rows
+    # (read at the owner, written locally), p/m/v read+write of the owned rows, Q rows per use in the apply
+    uniq = step.rows_touched()
+    bytes_gpu = units * (De * 4 + 12) + uniq * De * 4 * 2 + (hi - lo) * De * 24 + (world * units // world) * (De * 4 + 8)
+    out.update({"value": world * units * K / (ms * 1e-3), "ms_per_step": step_ms, "steps": K,
+                "unique_rows_per_gpu": uniq, "pulled_bytes_per_gpu": uniq * De * 4,
+                "roofline": {"bound": "hbm", "achieved": bytes_gpu / (step_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": bytes_gpu / (step_ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_gpu": bytes_gpu,
+                             "peak_source": peak_src,
+                             "note": "per GPU: B*N candidate rows read in the sweep + unique rows pulled (read + write) + "
+                                     "p/m/v of the owned rows (read + write) + one staged Q row per use in the owners' "
+                                     "apply; the table does not fit the 126 MB L2"}})
+    # the loss every rank reports is that of the global batch: identical on all ranks
+    last = step.train_step(iter([batches[0]]), targs)
+    t = torch.tensor([last["loss"]], dtype=torch.float64, device=dev)
+    if dist is not None:
+        allv = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(allv, t)
+        out["loss_spread_over_ranks"] = float(torch.stack(allv).max() - torch.stack(allv).min())
+    out["loss"] = last["loss"]
+    del step, model, opt, batches
+    torch.cuda.empty_cache()
     return out
 
 
@@ -705,6 +816,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eval10m", action="store_true", help="skip the 10M-entity sharded eval section (80 GB table)")
     ap.add_argument("--train-only", action="store_true", help="tuning loops: only the headline train step sections")
+    ap.add_argument("--sharded", action="store_true", help="with --train-only: also the row-sharded train sections (configs[4])")
     ap.add_argument("--interht", action="store_true", help="with --train-only: also time BASELINE configs[2] (InterHT)")
     ap.add_argument("--no-dist-check", action="store_true", help="N > 1: skip the correctness check around the timed region")
     a = ap.parse_args()

@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
 EXCHANGE_EARLY, EXCHANGE_LATE, EXCHANGE_ALL = 1, 2, 3  # kge_train_exchange_parts
 
@@ -112,6 +112,9 @@ PROTOTYPES = {
     "kge_train_apply_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                         C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P,
                                         _P, _P, _SZ, _P]),
+    "kge_shard_compact_workspace_bytes": (_SZ, [_I64]),
+    "kge_shard_compact": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _I64, _P, _P, _SZ, _P]),
+    "kge_shard_fetch_rows": (C.c_int, [_P, _P, _I64, _I64, C.POINTER(C.c_void_p), C.c_int, _I64, _P, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
     "kge_profile_enable": (C.c_int, [C.c_int]),
     "kge_profile_num_stages": (C.c_int, []),

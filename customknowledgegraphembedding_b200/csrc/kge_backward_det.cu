@@ -196,7 +196,7 @@ __global__ void scan_add_kernel(int* out, const int* __restrict__ block_sums, lo
     if (i < n) {
         const int v = out[i] + block_sums[i / kScanBlock];
         out[i] = v;
-        cursor[i] = v;
+        if (cursor != nullptr) cursor[i] = v;
     } else if (i == n) {
         out[n] = block_sums[(n + kScanBlock - 1) / kScanBlock];
     }
@@ -299,6 +299,16 @@ cudaError_t launch_histogram(int mode, const int64_t* pos, const int64_t* neg, l
     const long long total = BN + 2 * B;
     const int hb = (int)std::min<long long>((total + 255) / 256, 8LL * sm_count());
     return launch_pdl(det_histogram_kernel, dim3(hb), dim3(256), 0, st, mode, pos, neg, BN, B, counts, e_lo, e_hi);
+}
+
+// exclusive scan of in[0..n) -> out[0..n] (out[n] = total); block_sums: (n + 1023) / 1024 + 2 ints of scratch
+cudaError_t launch_exclusive_scan(const int* in, int* out, int* block_sums, long long n, cudaStream_t st) {
+    const int nblocks = (int)((n + kScanBlock - 1) / kScanBlock);
+    cudaError_t e;
+    if ((e = launch_pdl(scan_block_kernel, dim3(std::max(nblocks, 1)), dim3(256), 0, st, in, out, block_sums, n)) != cudaSuccess) return e;
+    if ((e = launch_pdl(scan_sums_kernel, dim3(1), dim3(1024), 0, st, block_sums, nblocks)) != cudaSuccess) return e;
+    return launch_pdl(scan_add_kernel, dim3((unsigned)((n + 1 + 255) / 256)), dim3(256), 0, st, out, (const int*)block_sums, n,
+                      (int*)nullptr);
 }
 
 // exclusive scan of counts -> offsets (+ a copy in cursor), then scatter every use into its bucket

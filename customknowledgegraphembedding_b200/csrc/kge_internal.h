@@ -45,6 +45,16 @@ cudaError_t launch_scan_fill(int mode, const int64_t* pos, const int64_t* neg, l
                              int* counts, int* offsets, int* cursor, int* items, int* block_sums, long long e_lo,
                              long long e_hi, cudaStream_t st);
 
+cudaError_t launch_exclusive_scan(const int* in, int* out, int* block_sums, long long n, cudaStream_t st);
+
+// row-sharded train step (kge_shard.cu): touched rows of a batch -> compact ids, rows pulled from the owners' shards
+size_t shard_compact_workspace_bytes(int64_t nentity);
+cudaError_t launch_shard_compact(const int64_t* pos, const int64_t* neg, int64_t B, int64_t N, int64_t E, int64_t* cpos,
+                                 int64_t* cneg, int64_t* uniq, int64_t capacity, int* n_unique, void* ws, cudaStream_t st);
+cudaError_t launch_shard_fetch_rows(const int64_t* uniq, const int* n_unique, int64_t capacity, int64_t De,
+                                    const float* const* shards, int world, int64_t rows_per_rank, float* compact,
+                                    cudaStream_t st);
+
 // K2
 cudaError_t launch_loss_final(const float* terms, int64_t B, float* loss3, cudaStream_t st);
 size_t loss_workspace_bytes(int64_t B);

@@ -754,6 +754,11 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
                     if (j < jfull || k0 < H)  // j < jfull is warp-uniform: every lane of the chunk is inside the row
                         lds128(c[pl][j], row_s + (uint32_t)(pl * H + 128 * j) * 4u);
                 }
+            // The slot is refilled by the async proxy (TMA) while it was read through the generic proxy: the proxy fence
+            // orders every lane's reads before the refill that lane 0 issues after the warp barrier.  Without it the
+            // refill was seen to overtake a lane's reads about once in 10^5 rows (config 2: three of 8192 items mixed the
+            // coordinates of two consecutive rows -- scratch/diag_sweep.py, tests/test_gpu_baseline_sizes.py).
+            fence_proxy_async();
             __syncwarp();  // every lane has lifted its part of the slot
             if (n + R < n1) {
                 if (lane == 0) issue_row(id_ahead);

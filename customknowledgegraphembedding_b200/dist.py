@@ -569,6 +569,74 @@ class RowShardedStep(DataParallelStep):
         self.rank, self.world = model.rank, model.world
         self.lo, self.hi = model.lo, model.hi
         self.last_exchange = {}
+        # kernel path (kge_shard_compact + kge_shard_fetch_rows): touched ids by bitmap + scan, rows pulled from the
+        # owners' shards through peer mappings -- no torch.unique, no all-to-all, no host sync.  Needs CUDA and, with
+        # world > 1, the shards in symmetric memory; otherwise (gloo tests, KGE_SHARD_KERNELS=0) the torch / NCCL
+        # all-to-all plumbing below is used.
+        self.use_kernels = os.environ.get("KGE_SHARD_KERNELS", "1") != "0"
+        self.shard_ptrs = None      # ctypes array of `world` device pointers (tests inject emulated shards here)
+        self._shard_hdl = None
+        self._cstate = None         # compact-table buffers of the kernel path
+
+    # ---- kernel path -----------------------------------------------------------------------------------------
+    def _peer_table(self):
+        """(called by _ensure once the peer buffers exist) Move this rank's SHARD into symmetric memory so that every
+        rank can read the rows it needs straight from their owner.  No replica of the table exists anywhere."""
+        import torch.distributed._symmetric_memory as symm
+        ent = self.model.entity_embedding
+        rows_per = (self.model.nentity + self.world - 1) // self.world
+        block = symm.empty(max(rows_per, 1) * self.model.entity_dim, dtype=torch.float32, device=ent.device)
+        block[:ent.numel()].copy_(ent.data.reshape(-1))
+        hdl = symm.rendezvous(block, self.group if self.group is not None else dist.group.WORLD)
+        ent.data = block[:ent.numel()].view(ent.shape)
+        self.shard_ptrs = (C.c_void_p * self.world)(*[C.c_void_p(int(p)) for p in hdl.buffer_ptrs])
+        self._shard_hdl = hdl
+        hdl.barrier()  # every shard is in place before anybody's first pull
+        return {"hdl": hdl, "block": block, "ptrs": None, "mc": None}
+
+    def _kernel_path(self, dev) -> bool:
+        if not self.use_kernels or dev.type != "cuda" or self.model.entity_dim % 4:
+            return False
+        if self.shard_ptrs is None and self.world == 1:
+            self.shard_ptrs = (C.c_void_p * 1)(C.c_void_p(self.model.entity_embedding.data_ptr()))
+        return self.shard_ptrs is not None
+
+    def _compact_state(self, B, N, dev):
+        m = self.model
+        cap = min(m.nentity, B * N + 2 * B)
+        key = (B, N, dev, cap)
+        if self._cstate is None or self._cstate["key"] != key:
+            need = _lib.load().kge_shard_compact_workspace_bytes(m.nentity)
+            self._cstate = {
+                "key": key, "cap": cap,
+                "cpos": torch.empty((B, 3), dtype=torch.int64, device=dev),
+                "cneg": torch.empty((B, N), dtype=torch.int64, device=dev),
+                "uniq": torch.empty(cap, dtype=torch.int64, device=dev),
+                "n": torch.zeros(1, dtype=torch.int32, device=dev),
+                "table": torch.empty((cap, m.entity_dim), dtype=torch.float32, device=dev),
+                "ws": torch.empty(need, dtype=torch.uint8, device=dev)}
+        return self._cstate
+
+    def _sweep_kernels(self, mode, pos, neg, w, wsum, B_total, loss_opts):
+        m, lib = self.model, _lib.load()
+        B, N = neg.shape
+        cs = self._compact_state(B, N, pos.device)
+        P = ops._ptr
+        nshards = len(self.shard_ptrs)
+        rows_per = (m.nentity + nshards - 1) // nshards  # shard_range: contiguous blocks of ceil(E / world) rows
+        if nshards == 1 and self._shard_hdl is None:  # (the parameter may have been re-allocated: .to(), load_state_dict)
+            self.shard_ptrs[0] = C.c_void_p(m.entity_embedding.data_ptr())
+        with _on(pos.device):
+            stream = ops._stream()
+            _lib.check(lib.kge_shard_compact(P(pos), P(neg), B, N, m.nentity, P(cs["cpos"]), P(cs["cneg"]), P(cs["uniq"]),
+                                             cs["cap"], P(cs["n"]), P(cs["ws"]), cs["ws"].numel(), stream), "kge_shard_compact")
+            _lib.check(lib.kge_shard_fetch_rows(P(cs["uniq"]), P(cs["n"]), cs["cap"], m.entity_dim, self.shard_ptrs,
+                                                nshards, rows_per, P(cs["table"]), stream), "kge_shard_fetch_rows")
+        self._run_sweep(mode, cs["table"], cs["cpos"], cs["cneg"], w, wsum, B_total, loss_opts)
+
+    def rows_touched(self) -> int:
+        """Unique rows of the last local batch (reads the device counter: a sync -- for reports, not for the step)."""
+        return int(self._cstate["n"].item()) if self._cstate is not None else self.last_exchange.get("rows_requested", 0)
 
     # ---- 1: rows of the local batch from their owners ------------------------------------------------------
     def fetch_rows(self, ids_sorted: torch.Tensor) -> torch.Tensor:
@@ -596,6 +664,8 @@ class RowShardedStep(DataParallelStep):
     def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
         m = self.model
         B, N = neg.shape
+        if self._kernel_path(pos.device):
+            return self._sweep_kernels(mode, pos, neg, w, wsum, B_total, loss_opts)
         ids = torch.cat([pos[:, 0], pos[:, 2], neg.reshape(-1)])
         uniq, inv = torch.unique(ids, sorted=True, return_inverse=True)
         compact = self.fetch_rows(uniq).contiguous()
@@ -638,5 +708,7 @@ class RowShardedStep(DataParallelStep):
                 self._ws.numel(), ops._stream()), "kge_train_apply_shard")
 
     def _share_rows(self):
-        """Rows stay with their owners: nothing to broadcast."""
-        return
+        """Rows stay with their owners: nothing to broadcast.  With the shards in symmetric memory one barrier closes the
+        step: every owner's update is complete before anybody pulls rows for the next batch."""
+        if self._shard_hdl is not None:
+            self._shard_hdl.barrier()

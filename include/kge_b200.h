@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 9
+#define KGE_B200_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -396,6 +396,28 @@ KGE_API int kge_train_apply_shard(const kge_model_desc *desc, int mode, float *e
                                   const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
                                   const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi,
                                   float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * The two steps in front of kge_train_sweep on a ROW-SHARDED table ("all-gather of the touched rows"):
+ *
+ * kge_shard_compact   the entity ids the local batch touches -> `unique_ids` (sorted ascending, *n_unique of them, a
+ *   device scalar: nothing returns to the host) and the batch re-indexed by position in that list
+ *   (compact_positive [B,3], compact_negative [B,N]; relation ids are copied).  Bitmap mark + popcount scan: no sort.
+ *   capacity = rows of `unique_ids` / of the compact table, >= min(nentity, B*N + 2B).
+ *   ws: kge_shard_compact_workspace_bytes(nentity).
+ * kge_shard_fetch_rows   compact_table[u] = row unique_ids[u] of the global table, read from the shard of the rank that
+ *   owns it: shard_ptrs[r] (HOST array of `world` DEVICE pointers) is the base of rank r's rows
+ *   [r * rows_per_rank, (r+1) * rows_per_rank) -- the own shard and peer mappings of the others (symmetric memory /
+ *   cudaIpc over NVLink).  The caller orders the call after the owners' previous update (a barrier across ranks).
+ * Replaces the torch.unique / all-to-all plumbing; the reference keeps full replicas (tensorflow_codes/run.py:8-17).
+ */
+KGE_API size_t kge_shard_compact_workspace_bytes(int64_t nentity);
+KGE_API int kge_shard_compact(const int64_t *positive, const int64_t *negative, int64_t B, int64_t N, int64_t nentity,
+                              int64_t *compact_positive, int64_t *compact_negative, int64_t *unique_ids,
+                              int64_t capacity, int32_t *n_unique, void *ws, size_t ws_bytes, void *stream);
+KGE_API int kge_shard_fetch_rows(const int64_t *unique_ids, const int32_t *n_unique, int64_t capacity,
+                                 int64_t entity_dim, const float *const *shard_ptrs, int world, int64_t rows_per_rank,
+                                 float *compact_table, void *stream);
 
 /*
  * N1  on-GPU negative sampler.  Replaces TrainDataset.__getitem__ of the PyTorch codes (U11; TF twin

@@ -12,6 +12,7 @@ GOLDEN = os.path.join(REPO, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices of one box (real NCCL / NVLink ranks)")
 
 
 def pytest_collection_modifyitems(config, items):

@@ -1,5 +1,14 @@
-"""torchrun --nproc-per-node 2 scratch/dist_check.py : real 2-GPU run of dist.DataParallelStep / dist.test_step
-against the single-process result on the concatenated batch."""
+"""python -m torch.distributed.run --nproc-per-node G tests/multigpu_worker.py : REAL G-GPU run (NCCL + symmetric memory
+over NVLink) of every multi-rank path, each against the single-GPU result on the concatenated batch:
+
+  * dist.DataParallelStep (replicated table): peer-store exchange, NVSwitch multicast row stores where the fabric has
+    them -- per-step loss within 2e-6, tables within 5e-3 * lr, replicas bit-identical across ranks afterwards;
+  * dist.test_step (candidates sharded) and RowShardedKGEModel.test_step (table sharded): ranks and metrics EQUAL;
+  * dist.RowShardedStep: kernel path (kge_shard_compact + rows pulled from the owners' symmetric-memory shards) and the
+    NCCL all-to-all path (KGE_SHARD_KERNELS=0 semantics via use_kernels=False);
+  * unequal batch shapes across ranks are refused on every rank.
+
+Launched by tests/test_multigpu.py (marker `multigpu`, skipped below 2 GPUs); prints MULTIGPU CHECK OK on success."""
 import os, sys
 import numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -30,6 +39,15 @@ for name in ("RotatE", "TransE", "InterHT", "ComplEx"):
         if rank == 0:
             print(name, "step", s, "loss single", la["loss"], "sharded", lb["loss"], "max|dE|", d, "max|dR|", dr_, flush=True)
         assert abs(la["loss"] - lb["loss"]) <= 2e-6 * abs(la["loss"]) and d <= 5e-3 * lr and dr_ <= 5e-3 * lr
+    # every replica holds the same bits after the steps
+    cs = torch.tensor([int(b.entity_embedding.detach().view(torch.int32).to(torch.int64).sum()),
+                       int(b.relation_embedding.detach().view(torch.int32).to(torch.int64).sum())], device="cuda")
+    allcs = [torch.empty_like(cs) for _ in range(world)]
+    dist.all_gather(allcs, cs)
+    assert all(torch.equal(allcs[0], c) for c in allcs), "replicas differ across ranks: %s" % [c.tolist() for c in allcs]
+    if rank == 0:
+        print(name, "replicas bit-identical on", world, "ranks; multicast rows:",
+              bool(step._rows_peer and step._rows_peer["mc"] is not None), "peer exchange:", step._peer is not None, flush=True)
     rng = np.random.RandomState(1)
     true = [(int(x), int(y), int(z)) for x, y, z in zip(rng.randint(0, 50, 600), rng.randint(0, R, 600), rng.randint(0, E, 600))]
     m1 = kb.KGEModel.test_step(a, true[:100], true, args); r1 = a.last_eval["ranks"].copy()
@@ -43,8 +61,9 @@ for name in ("RotatE", "TransE", "InterHT", "ComplEx"):
     assert np.array_equal(r1, r3) and m1 == m3, (r1[:10], r3[:10])
     if rank == 0:
         print(name, "row-sharded table eval == single eval (rows/rank %d)" % sm.entity_embedding.shape[0], flush=True)
-# row-sharded TRAIN step over NCCL: all-to-all of ids and rows, compact-table sweep, shard apply
-for name in ("RotatE", "InterHT"):
+# row-sharded TRAIN step: kernel path (bitmap compaction + rows pulled from symmetric-memory shards) and the NCCL
+# all-to-all path; compact-table sweep, exchange to the owners, shard apply
+for name, kernels in (("RotatE", True), ("InterHT", True), ("TransE", True), ("RotatE", False)):
     om = ko.make_model(name, E, R, H, 12.0, seed=1)
     de, dr, tr = ko.model_flags(name)
     a = kb.KGEModel(name, E, R, H, 12.0, de, dr, tr); a.load_state_dict(om.state_dict()); a = a.cuda()
@@ -52,6 +71,7 @@ for name in ("RotatE", "InterHT"):
     oa = torch.optim.Adam(filter(lambda p: p.requires_grad, a.parameters()), lr=lr)
     sm = kd.RowShardedKGEModel.from_full(b)
     step = kd.RowShardedStep(sm, torch.optim.Adam(filter(lambda p: p.requires_grad, sm.parameters()), lr=lr))
+    step.use_kernels = kernels
     args = ko.Args(negative_adversarial_sampling=True, cuda=True, nentity=E, nrelation=R)
     for s in range(3):
         batches = [ko.synthetic_batch(E, R, B, N, seed=300 * s + r, mode="tail-batch" if s % 2 else "head-batch") for r in range(world)]
@@ -60,7 +80,21 @@ for name in ("RotatE", "InterHT"):
         lb = step.train_step(iter([batches[rank]]), args)
         d = float((a.entity_embedding[sm.lo:sm.hi] - sm.entity_embedding).abs().max())
         if rank == 0:
-            print(name, "row-sharded step", s, "loss single", la["loss"], "sharded", lb["loss"], "max|dE(shard)|", d, step.last_exchange, flush=True)
+            print(name, "row-sharded step", s, "kernel path" if (kernels and step.shard_ptrs is not None) else "NCCL all-to-all",
+                  "loss single", la["loss"], "sharded", lb["loss"], "max|dE(shard)|", d, "rows touched", step.rows_touched(), flush=True)
         assert abs(la["loss"] - lb["loss"]) <= 2e-6 * abs(la["loss"]) and d <= 5e-3 * lr
+    assert (step.shard_ptrs is not None) == kernels, "kernel path expected %s" % kernels
+    dR = float((a.relation_embedding - sm.relation_embedding).abs().max())
+    assert dR <= 5e-3 * lr, dR
+# unequal batch shapes are refused on every rank, before any exchange
+om = ko.make_model("RotatE", E, R, H, 12.0, seed=2)
+c = kb.KGEModel("RotatE", E, R, H, 12.0, True, False); c.load_state_dict(om.state_dict()); c = c.cuda()
+step = kd.DataParallelStep(c, torch.optim.Adam(filter(lambda p: p.requires_grad, c.parameters()), lr=lr))
+bad = ko.synthetic_batch(E, R, B + rank, N, seed=7, mode="tail-batch")
+try:
+    step.train_step(iter([bad]), ko.Args(negative_adversarial_sampling=True, cuda=True))
+    raise AssertionError("unequal B accepted")
+except ValueError as e:
+    assert "different batch shapes" in str(e)
 dist.barrier(); dist.destroy_process_group()
-if rank == 0: print("DIST CHECK OK")
+if rank == 0: print("MULTIGPU CHECK OK")

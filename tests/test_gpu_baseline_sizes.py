@@ -45,7 +45,7 @@ def _rel_err(got, want, scale):
 
 GRAD_TOL = 5e-5        # of the largest entry of the gradient table
 GRAD_OUTLIERS = 2e-6   # fraction of elements allowed outside GRAD_TOL (ill-conditioned coordinates, see below); >= 4
-GRAD_MAX = 1e-3        # ... none of them further than this
+GRAD_MAX = 3e-3        # ... none of them further than this (a flipped sign(v) moves one use's contribution by twice its size)
 
 
 def _one_step_case(name, E, R, H, B, N, mode, gamma=None, adv=True, uni=False, alpha=1.0, lr=1e-3, seed=0,
@@ -315,3 +315,40 @@ def test_eval_10m_slice_against_oracle():
                 near = int((np.abs(s - st64) <= NEAR_TOL * (9.0 + abs(st64))).sum())
                 assert ng[i] == c64 or min(c32, c64) - near <= ng[i] <= max(c32, c64) + near, (mode, i, ng[i], c32, c64)
     print("10M slice: %d of %d counts differ from the fp32 oracle (each adjudicated against fp64 above)" % (unequal, 2 * Q))
+
+
+def test_sweep_variants_agree_at_config2():
+    """The warp-per-row sweep (rows through a TMA slot per warp, 8 work items per positive handed out by an atomic
+    counter to ~1800 resident warps) against the row-group sweep at the headline size, six batches: dL/ds and the
+    compact per-positive gradient rows agree row by row.  The two differ in summation order only (2e-7 of a row's
+    largest entry); a slot refill that overtakes a lane's reads mixes two candidate rows and shows as 1e-4 .. 1e-3."""
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import _lib, dist as kd
+    E, R, H, B, N = 14541, 237, 1000, 1024, 256
+    lib = _lib.load()
+    torch.manual_seed(0)
+    gm = kb.KGEModel("RotatE", E, R, H, 9.0, True, False).cuda()
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, gm.parameters()), lr=1e-3)
+    lo = kd.LossOpts(1, 0, 1, 0, 1.0, 0.0)
+    worst = {}
+    for seed in range(6):
+        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=seed)
+        pos, neg, w = pos.cuda(), neg.cuda(), w.cuda()
+        wsum = w.sum().reshape(1)
+        out = {}
+        try:
+            for variant in (0, 1):
+                lib.kge_train_set_sweep_variant(variant)
+                st = kd.DataParallelStep(gm, opt)
+                st._ensure(B, N, pos.device)
+                st._sweep(mode, pos, neg, w, wsum, B, lo)
+                torch.cuda.synchronize()
+                out[variant] = {k: v.clone() for k, v in st._local.items()}
+        finally:
+            lib.kge_train_set_sweep_variant(1)
+        for k, width in (("S", N), ("GH", 2 * H), ("GT", 2 * H), ("GR", H)):
+            a, b = out[0][k].view(B, width).double(), out[1][k].view(B, width).double()
+            rowerr = ((a - b).abs().amax(1) / a.abs().amax(1).clamp_min(1e-30)).max().item()
+            worst[k] = max(worst.get(k, 0.0), rowerr)
+    print("sweep variants, worst row-relative difference over 6 batches:", {k: "%.2e" % v for k, v in worst.items()})
+    assert all(v <= 2e-5 for v in worst.values()), worst

@@ -45,9 +45,81 @@ def test_world1_sharded_step_equals_plain_step(name):
         assert torch.equal(sm.relation_embedding, ref.relation_embedding), s
 
 
+@pytest.mark.parametrize("E,B,N", [(300, 7, 13), (33, 4, 50), (1, 2, 3), (10_000_019, 64, 256), (4096, 16, 1000)])
+def test_shard_compact_matches_torch_unique(E, B, N):
+    """kge_shard_compact (bitmap mark + popcount scan) == torch.unique(sorted=True, return_inverse=True) of the ids a
+    batch touches -- the sorted unique list, its length and the re-indexed batch; E not a multiple of 32, a table past
+    2^23 words, a batch that touches every row (capacity = E)."""
+    import ctypes as C
+    from customknowledgegraphembedding_b200 import _lib, ops
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(E + N)
+    pos = torch.stack([torch.randint(0, E, (B,), generator=g), torch.randint(0, 5, (B,), generator=g),
+                       torch.randint(0, E, (B,), generator=g)], 1).cuda()
+    neg = torch.randint(0, E, (B, N), generator=g).cuda()
+    if E > 1000:
+        neg[0, 0], neg[0, 1], pos[1, 0] = E - 1, 0, E - 1   # the ends of the table
+    cap = min(E, B * N + 2 * B)
+    cpos, cneg = torch.empty_like(pos), torch.empty_like(neg)
+    uniq = torch.full((cap,), -1, dtype=torch.int64, device="cuda")
+    n = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ws = torch.empty(lib.kge_shard_compact_workspace_bytes(E), dtype=torch.uint8, device="cuda")
+    P = ops._ptr
+    for _ in range(2):  # the workspace is reusable as is (the bitmap is cleared by the call)
+        _lib.check(lib.kge_shard_compact(P(pos), P(neg), B, N, E, P(cpos), P(cneg), P(uniq), cap, P(n), P(ws), ws.numel(),
+                                         ops._stream()), "kge_shard_compact")
+    want, inv = torch.unique(torch.cat([pos[:, 0], pos[:, 2], neg.reshape(-1)]), sorted=True, return_inverse=True)
+    assert int(n) == want.numel()
+    assert torch.equal(uniq[:int(n)], want)
+    assert torch.equal(cpos[:, 0], inv[:B]) and torch.equal(cpos[:, 2], inv[B:2 * B]) and torch.equal(cpos[:, 1], pos[:, 1])
+    assert torch.equal(cneg.reshape(-1), inv[2 * B:])
+    with pytest.raises(ValueError):
+        _lib.check(lib.kge_shard_compact(P(pos), P(neg), B, N, E, P(cpos), P(cneg), P(uniq), cap - 1 if cap > 1 else 0, P(n),
+                                         P(ws), ws.numel(), ops._stream()), "kge_shard_compact")
+
+
+@pytest.mark.parametrize("De", [2000, 30, 4100, 8])
+@pytest.mark.parametrize("world", [1, 3, 8])
+def test_shard_fetch_rows_from_emulated_shards(De, world):
+    """kge_shard_fetch_rows: rows of the global table pulled from `world` shards (here all on one GPU; over real ranks
+    the pointers are symmetric-memory peer mappings) == table[ids]; ragged last shard, an empty shard, every row width
+    path (16-byte lanes in 4 / 8 / 16 chunks, scalar)."""
+    import ctypes as C
+    from customknowledgegraphembedding_b200 import _lib, ops, dist as kd
+    lib = _lib.load()
+    E = 1001 if world < 8 else 9   # 9 rows over 8 ranks: shards of 2 rows, the last ranks empty
+    torch.manual_seed(De + world)
+    table = torch.randn(E, De, device="cuda")
+    shards, ptrs = [], []
+    for r in range(world):
+        lo, hi = kd.shard_range(E, r, world)
+        sh = table[lo:hi].clone() if hi > lo else torch.zeros(1, De, device="cuda")
+        shards.append(sh)
+        ptrs.append(C.c_void_p(sh.data_ptr()))
+    ids = torch.unique(torch.randint(0, E, (700,), device="cuda"))
+    cap = ids.numel() + 5
+    uniq = torch.cat([ids, torch.full((5,), E + 7, dtype=torch.int64, device="cuda")])  # past n_unique: never read
+    n = torch.tensor([ids.numel()], dtype=torch.int32, device="cuda")
+    out = torch.full((cap, De), -7.0, device="cuda")
+    arr = (C.c_void_p * world)(*ptrs)
+    rows_per = (E + world - 1) // world
+    _lib.check(lib.kge_shard_fetch_rows(ops._ptr(uniq), ops._ptr(n), cap, De, arr, world, rows_per, ops._ptr(out),
+                                        ops._stream()), "kge_shard_fetch_rows")
+    assert torch.equal(out[:ids.numel()], table[ids])
+    assert bool((out[ids.numel():] == -7.0).all())
+
+
 @pytest.mark.parametrize("name", ["RotatE", "TransE", "InterHT", "pRotatE"])
 @pytest.mark.parametrize("world", [2, 3])
-def test_emulated_ranks_equal_plain_step(name, world):
+def test_emulated_ranks_kernel_path_equal_plain_step(name, world):
+    """The same emulation with the kernel path of the sweep: touched ids by kge_shard_compact, rows pulled by
+    kge_shard_fetch_rows from the (emulated) owners' shards instead of the torch.unique / all-to-all plumbing."""
+    test_emulated_ranks_equal_plain_step(name, world, kernels=True)
+
+
+@pytest.mark.parametrize("name", ["RotatE", "TransE", "InterHT", "pRotatE"])
+@pytest.mark.parametrize("world", [2, 3])
+def test_emulated_ranks_equal_plain_step(name, world, kernels=False):
     import customknowledgegraphembedding_b200 as kb
     from customknowledgegraphembedding_b200 import dist as kd
     E, R, H, B, N, lr = 211, 5, 32, 12, 20, 1e-3
@@ -70,7 +142,12 @@ def test_emulated_ranks_equal_plain_step(name, world):
         gathered = {}
         for r, st in enumerate(steps):
             sl = slice(r * half, (r + 1) * half)
-            st.fetch_rows = lambda ids, table=table: table[ids]  # the all-to-all, emulated
+            if kernels:
+                import ctypes as C
+                st.shard_ptrs = (C.c_void_p * world)(*[C.c_void_p(s.entity_embedding.data_ptr()) for s in shards])
+            else:
+                st.use_kernels = False
+                st.fetch_rows = lambda ids, table=table: table[ids]  # the all-to-all, emulated
             st.world = 1
             st._shape = None
             st._ensure(half, N, pos.device)
