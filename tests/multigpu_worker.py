@@ -80,10 +80,10 @@ for name, kernels in (("RotatE", True), ("InterHT", True), ("TransE", True), ("R
         lb = step.train_step(iter([batches[rank]]), args)
         d = float((a.entity_embedding[sm.lo:sm.hi] - sm.entity_embedding).abs().max())
         if rank == 0:
-            print(name, "row-sharded step", s, "kernel path" if (kernels and step.shard_ptrs is not None) else "NCCL all-to-all",
+            print(name, "row-sharded step", s, "kernel path" if step._kernel_path(sm.entity_embedding.device) else "NCCL all-to-all",
                   "loss single", la["loss"], "sharded", lb["loss"], "max|dE(shard)|", d, "rows touched", step.rows_touched(), flush=True)
         assert abs(la["loss"] - lb["loss"]) <= 2e-6 * abs(la["loss"]) and d <= 5e-3 * lr
-    assert (step.shard_ptrs is not None) == kernels, "kernel path expected %s" % kernels
+    assert step._kernel_path(sm.entity_embedding.device) == kernels, "kernel path expected %s" % kernels
     dR = float((a.relation_embedding - sm.relation_embedding).abs().max())
     assert dR <= 5e-3 * lr, dR
 # unequal batch shapes are refused on every rank, before any exchange
