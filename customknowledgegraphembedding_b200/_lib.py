@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
 EXCHANGE_EARLY, EXCHANGE_LATE, EXCHANGE_ALL = 1, 2, 3  # kge_train_exchange_parts
 
@@ -66,6 +66,8 @@ PROTOTYPES = {
     "kge_score_forward": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _I64, _I64, _P, _P]),
     "kge_score_backward": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, C.c_int, _P, _SZ, _P]),
     "kge_loss_forward_backward": (C.c_int, [_P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _P, _P, _P, _SZ, _P]),
+    "kge_loss_static_max_b": (C.c_int64, []),
+    "kge_loss_forward_backward_static": (C.c_int, [_P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _P, _P, _P]),
     "kge_l3_sum_cubes": (C.c_int, [_P, _I64, _P, _P, _SZ, _P]),
     "kge_adam_dense": (C.c_int, [_P, _P, _P, _P, _I64, C.POINTER(AdamOpts), C.c_float, C.c_int, _P]),
     "kge_eval_rank": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, C.c_int, _P, _SZ, _P]),

@@ -44,8 +44,24 @@ def _deps_mtime() -> float:
     return max(os.path.getmtime(f) for f in files)
 
 
+def _headers_mtime() -> float:
+    files = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if not f.endswith(".cu")]
+    files += [os.path.join(INCLUDE, "kge_b200.h"), __file__]
+    return max(os.path.getmtime(f) for f in files)
+
+
+def _obj_of(src: str) -> str:
+    return os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
+
+
+def _stale(src: str) -> bool:
+    """An object is rebuilt when it is older than its source or than any header (a header change rebuilds everything)."""
+    obj = _obj_of(src)
+    return not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), _headers_mtime())
+
+
 def needs_build() -> bool:
-    return not os.path.exists(LIB) or os.path.getmtime(LIB) < _deps_mtime()
+    return not os.path.exists(LIB) or os.path.getmtime(LIB) < _deps_mtime() or any(_stale(s) for s in sources())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -56,7 +72,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
     extra = ["-Xptxas", "-v"] if verbose else []
 
     def compile_one(src):
-        obj = os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
+        obj = _obj_of(src)
+        if not force and not _stale(src):
+            return obj  # incremental: only the translation units that changed
         cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", src, "-o", obj]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:

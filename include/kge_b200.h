@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 10
+#define KGE_B200_ABI_VERSION 11
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -143,6 +143,28 @@ KGE_API int kge_score_backward(const kge_model_desc *desc, int mode, const float
 KGE_API int kge_loss_forward_backward(const float *negative_score, const float *positive_score,
                               const float *subsampling_weight, int64_t B, int64_t N, const kge_loss_opts *opts,
                               float *loss3, float *dneg, float *dpos, void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * K2 without any allocation or caller workspace: kge_loss_forward_backward whose 2B+8 floats of scratch live in a
+ * file-scope __device__ array inside the library.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results (bit for bit: the same two kernels) as kge_loss_forward_backward.
+ *   - limit: B <= KGE_LOSS_STATIC_MAX_B positives (kge_loss_static_max_b() returns it); a larger B is refused with
+ *     KGE_ERR_INVALID_ARGUMENT and a message naming the limit.  The array is 2 * 65536 + 8 floats = 512 KB per GPU that
+ *     loads the library, held until the process exits.
+ *   - the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the first call on a device
+ *     asks the runtime for the array's device address (cudaGetSymbolAddress, once per device, with that device current)
+ *     -- make that first call outside a stream capture.
+ *   - every call on a device shares the array, which keeps the last call's contents; K2 writes every term before it
+ *     reads it, so nothing needs clearing.  Calls that OVERLAP on the GPU (different streams, or different host threads
+ *     on one device) RACE on the array: serialise them, or use kge_loss_forward_backward with separate workspaces.
+ */
+#define KGE_LOSS_STATIC_MAX_B 65536
+KGE_API int64_t kge_loss_static_max_b(void);
+KGE_API int kge_loss_forward_backward_static(const float *negative_score, const float *positive_score,
+                                             const float *subsampling_weight, int64_t B, int64_t N,
+                                             const kge_loss_opts *opts, float *loss3, float *dneg, float *dpos,
+                                             void *stream);
 
 /* L3 regulariser value (tensorflow_codes/model.py:33-39): out[0] = sum |x|^3 over n elements (device
  * scalar, overwritten).  ws: 1024 floats. */
