@@ -13,6 +13,14 @@
 //                epilogue counts score > true / score == true, skipping the true entity itself
 //   5 filter     per filtered (query, entity) pair (one warp): undo its contribution to the counters
 //
+// Centred accumulation (distance models): a score is gamma - sum_k term_k with ~H terms of similar size, and a plain
+// fp32 running sum loses ~1e-6 of the sum to rounding over H = 1000 adds -- the spacing of neighbouring candidates'
+// scores at E >= 1e4, so ranks flip against the exact ranking of the same fp32 tables.  Here the running sum is shifted
+// after every chunk of 16 coordinates by a per-query constant cen_q = (true entity's sum) / #chunks: candidates that
+// score near the true entity keep |running sum| ~ 0.1 instead of ~ sum, which cuts the rounding error ~30x; candidates
+// far from it lose nothing that matters.  Only differences to the true score are compared, and every pair of a query
+// is shifted by the same constant the same number of times, so the ranking is that of the unshifted sums.
+//
 // Bit-consistency: 3, 4 and 5 evaluate a pair with the SAME instruction sequence (explicit
 // round-to-nearest intrinsics, no contraction freedom) in the SAME order, so the true entity
 // scores exactly its true score inside the tile and a filtered entity is subtracted iff it was
@@ -90,6 +98,13 @@ __device__ __forceinline__ float2 accum2(float2 acc, float q0, float q1, float2 
     }
 }
 
+// models whose score is gamma - (a sum of H non-negative terms): centred accumulation, chunks of kCenChunk coordinates
+template <int MODEL>
+__host__ __device__ constexpr bool centered() {
+    return MODEL == KGE_TRANSE || MODEL == KGE_ROTATE || MODEL == KGE_PROTATE || MODEL == KGE_INTERHT;
+}
+constexpr int kCenChunk = 16;  // == kKC of the tile kernel
+
 template <int MODEL>
 __device__ __forceinline__ float finalize(float acc, const EvalConsts& c) {
     if constexpr (MODEL == KGE_DISTMULT || MODEL == KGE_COMPLEX) return acc;
@@ -113,7 +128,8 @@ constexpr size_t pair_smem() { return (size_t)kPairWarps * pair_strips<MODEL>() 
 
 template <int MODEL, bool HEAD>
 __device__ __forceinline__ float pair_score_warp(const float* __restrict__ qrow, const float* __restrict__ erow, int H,
-                                                 const EvalConsts& c, float ina, float inb, float* __restrict__ strip) {
+                                                 const EvalConsts& c, float ina, float inb, float* __restrict__ strip,
+                                                 float cen = 0.f, float* raw_acc = nullptr) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes(MODEL);
     const int lane = threadIdx.x & 31;
     float acc = 0.f;
@@ -150,16 +166,24 @@ __device__ __forceinline__ float pair_score_warp(const float* __restrict__ qrow,
                     acc = __fmaf_rn(strip[2 * kPairChunk + i], strip[3 * kPairChunk + i],
                                     __fmaf_rn(strip[i], strip[kPairChunk + i], acc));
             } else {
-                int i = 0;
-                for (; i + 4 <= n; i += 4) {
-                    const float4 t = *reinterpret_cast<const float4*>(strip + i);
-                    acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, t.x), t.y), t.z), t.w);
+                // chunks of kCenChunk coordinates (kPairChunk is a multiple: strip offsets are absolute chunk boundaries),
+                // the running sum shifted by cen after each -- exactly what a thread of the tile kernel does; a partial
+                // last chunk (H % 16 != 0) is padded there with +0 terms and shifted too
+                for (int i0 = 0; i0 < n; i0 += kCenChunk) {
+                    const int m = min(kCenChunk, n - i0);
+                    int i = 0;
+                    for (; i + 4 <= m; i += 4) {
+                        const float4 t = *reinterpret_cast<const float4*>(strip + i0 + i);
+                        acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, t.x), t.y), t.z), t.w);
+                    }
+                    for (; i < m; ++i) acc = __fadd_rn(acc, strip[i0 + i]);
+                    acc = __fsub_rn(acc, cen);
                 }
-                for (; i < n; ++i) acc = __fadd_rn(acc, strip[i]);
             }
         }
         __syncwarp();
     }
+    if (raw_acc != nullptr) *raw_acc = __shfl_sync(0xffffffffu, acc, 0);
     return __shfl_sync(0xffffffffu, finalize<MODEL>(acc, c), 0);
 }
 
@@ -252,7 +276,7 @@ __global__ void __launch_bounds__(32 * kPairWarps)
 eval_true_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
                  const float* __restrict__ qrows, const float* __restrict__ Qs, const float* __restrict__ tna,
                  const float* __restrict__ tnb, const int64_t* __restrict__ queries, long long Q,
-                 float* __restrict__ true_score) {
+                 float* __restrict__ true_score, float* __restrict__ true_cmp, float* __restrict__ cen) {
     extern __shared__ __align__(16) float smem[];
     float* strip = smem + (size_t)(threadIdx.x >> 5) * pair_strips<MODEL>() * kPairChunk;
     const long long q = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);  // one warp per query
@@ -260,8 +284,20 @@ eval_true_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
     if (MODEL == KGE_PROTATE) c.modulus = __ldg(modulus_p);
     const int qdim = model_planes(MODEL) * P.H;
     const float a = (MODEL == KGE_INTERHT) ? tna[q] : 0.f, b = (MODEL == KGE_INTERHT) ? tnb[q] : 0.f;
-    const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, true_row<HEAD>(P, ent, qrows, queries, q), P.H, c, a, b, strip);
-    if ((threadIdx.x & 31) == 0) true_score[q] = s;
+    const float* trow = true_row<HEAD>(P, ent, qrows, queries, q);
+    float acc0 = 0.f;
+    const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, trow, P.H, c, a, b, strip, 0.f, &acc0);
+    float s_cmp = s, cq = 0.f;
+    if constexpr (centered<MODEL>()) {
+        // the query's shift: the true entity's own mean chunk sum; then the true score again, shifted like every candidate
+        cq = __fdiv_rn(acc0, (float)((P.H + kCenChunk - 1) / kCenChunk));
+        s_cmp = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, trow, P.H, c, a, b, strip, cq);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        true_score[q] = s;   // the plain score: what the caller sees
+        true_cmp[q] = s_cmp; // what candidates are compared with
+        cen[q] = cq;
+    }
 }
 
 // ---- 5 filter --------------------------------------------------------------------------------
@@ -272,7 +308,8 @@ eval_filter_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, 
                    const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
                    const int64_t* __restrict__ queries, long long Q, const int64_t* __restrict__ indptr,
                    const int64_t* __restrict__ idx, long long e_lo, long long e_hi,
-                   const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+                   const float* __restrict__ true_score, const float* __restrict__ cen, unsigned long long* n_greater,
+                   unsigned long long* n_equal) {
     extern __shared__ __align__(16) float smem[];
     float* strip = smem + (size_t)(threadIdx.x >> 5) * pair_strips<MODEL>() * kPairChunk;
     const int lane = threadIdx.x & 31;
@@ -297,7 +334,8 @@ eval_filter_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, 
         for (long long j = indptr[q] + lane; j < f; j += 32) dup |= (idx[j] == e);
         if (__any_sync(0xffffffffu, dup)) continue;
         const float a = (MODEL == KGE_INTERHT) ? ina[e] : 0.f, b = (MODEL == KGE_INTERHT) ? inb[e] : 0.f;
-        const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b, strip);
+        const float s = pair_score_warp<MODEL, HEAD>(Qs + q * qdim, ent + e * (long long)P.De, P.H, c, a, b, strip,
+                                                     centered<MODEL>() ? cen[q] : 0.f);
         if (lane == 0) {
             const float t = true_score[q];
             if (s > t) atomicAdd(n_greater + q, ~0ULL);      // -1
@@ -319,9 +357,12 @@ __global__ void __launch_bounds__(kEvalThreads)
 eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, const float* __restrict__ ent,
                  const float* __restrict__ Qs, const float* __restrict__ ina, const float* __restrict__ inb,
                  const int64_t* __restrict__ queries, long long Q, long long e_lo, long long e_hi,
-                 const float* __restrict__ true_score, unsigned long long* n_greater, unsigned long long* n_equal) {
+                 const float* __restrict__ true_score, const float* __restrict__ cen, unsigned long long* n_greater,
+                 unsigned long long* n_equal) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes(MODEL);
+    static_assert(kCenChunk == kKC, "the centring chunk is the tile kernel's k chunk");
     extern __shared__ __align__(16) float smem[];
+    __shared__ __align__(16) float cen_s[kTQ];  // per-query shift of the running sum (0 for the dot-product models)
     // [buf][plane][k][row]
     float* Qt = smem;
     float* Et = smem + 2 * QP * kKC * kTQ;
@@ -395,6 +436,7 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
         for (int j = 0; j < 4; ++j) acc[i][j] = make_float2(0.f, 0.f);
 
     const int nchunks = (H + kKC - 1) / kKC;
+    if (tid < kTQ) cen_s[tid] = (centered<MODEL>() && q0 + tid < Q) ? cen[q0 + tid] : 0.f;
     fetch(0);
     stash(0, 0);
     __syncthreads();
@@ -437,6 +479,17 @@ eval_tile_kernel(Params P, EvalConsts c, const float* __restrict__ modulus_p, co
                     }
                 }
         }
+        if constexpr (centered<MODEL>()) {  // shift the running sums: acc - cen_q (== acc + (-cen_q), one rounding)
+            const float4 ca = *reinterpret_cast<const float4*>(cen_s + ty * 4);
+            const float4 cb = *reinterpret_cast<const float4*>(cen_s + 64 + ty * 4);
+            const float cq[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float2 m = make_float2(-cq[i], -cq[i]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = __fadd2_rn(acc[i][j], m);
+            }
+        }
         if (ch + 1 < nchunks) {
             stash(buf ^ 1, (ch + 1) * kKC);  // the other buffer was last read in iteration ch-1
             __syncthreads();
@@ -476,7 +529,7 @@ static inline size_t ev_align(size_t x) { return (x + 255) & ~(size_t)255; }
 
 size_t eval_workspace_bytes(const Params& P, int64_t Q, int64_t nfilter) {
     if (eval_mma_applies(P)) return eval_mma_workspace_bytes(P, Q, nfilter);
-    size_t total = ev_align((size_t)Q * model_planes(P.model) * P.H * sizeof(float));
+    size_t total = ev_align((size_t)Q * model_planes(P.model) * P.H * sizeof(float)) + 2 * ev_align((size_t)Q * sizeof(float));
     if (P.model == KGE_INTERHT) total += 2 * ev_align((size_t)P.E * sizeof(float)) + 2 * ev_align((size_t)Q * sizeof(float));
     return total + 256;
 }
@@ -489,10 +542,12 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
                                      void* ws, cudaStream_t st) {
     const int qdim = model_planes(MODEL) * P.H;
     float* Qs = (float*)ws;
+    float* true_cmp = (float*)((char*)ws + ev_align((size_t)Q * qdim * sizeof(float)));  // shifted true scores
+    float* cen = (float*)((char*)true_cmp + ev_align((size_t)Q * sizeof(float)));        // per-query shifts
     float *ina = nullptr, *inb = nullptr, *tna = nullptr, *tnb = nullptr;
     if (MODEL == KGE_INTERHT) {
         // candidate norms for rows [e_lo, e_hi) only, addressed by global id through an offset base
-        float* na = (float*)((char*)ws + ev_align((size_t)Q * qdim * sizeof(float)));
+        float* na = (float*)((char*)cen + ev_align((size_t)Q * sizeof(float)));
         float* nb = (float*)((char*)na + ev_align((size_t)P.E * sizeof(float)));
         tna = (float*)((char*)nb + ev_align((size_t)P.E * sizeof(float)));
         tnb = (float*)((char*)tna + ev_align((size_t)Q * sizeof(float)));
@@ -522,20 +577,20 @@ static cudaError_t launch_eval_model(const Params& P, const float* ent, const fl
         cudaFuncSetAttribute(eval_filter_kernel<MODEL, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pair);
     }
     eval_true_kernel<MODEL, HEAD><<<(unsigned)((Q + kPairWarps - 1) / kPairWarps), 32 * kPairWarps, smem_pair, st>>>(
-        P, c, modulus, ent, qrows, Qs, tna, tnb, queries, Q, true_score);
+        P, c, modulus, ent, qrows, Qs, tna, tnb, queries, Q, true_score, true_cmp, cen);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (e_hi > e_lo) {
         constexpr size_t smem = eval_tile_smem<MODEL>();
         cudaFuncSetAttribute(eval_tile_kernel<MODEL, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         dim3 grid((unsigned)((e_hi - e_lo + kTE - 1) / kTE), (unsigned)((Q + kTQ - 1) / kTQ));
         eval_tile_kernel<MODEL, HEAD><<<grid, kEvalThreads, smem, st>>>(P, c, modulus, ent, Qs, ina, inb, queries, Q, e_lo,
-                                                                         e_hi, true_score, n_greater, n_equal);
+                                                                         e_hi, true_cmp, cen, n_greater, n_equal);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     if (indptr != nullptr && idx != nullptr) {
         // the number of filter entries lives on the device (indptr[Q]): grid-stride over it, no host sync
         eval_filter_kernel<MODEL, HEAD><<<8 * sm_count(), 32 * kPairWarps, smem_pair, st>>>(
-            P, c, modulus, ent, Qs, ina, inb, queries, Q, indptr, idx, e_lo, e_hi, true_score, n_greater, n_equal);
+            P, c, modulus, ent, Qs, ina, inb, queries, Q, indptr, idx, e_lo, e_hi, true_cmp, cen, n_greater, n_equal);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     return cudaSuccess;
