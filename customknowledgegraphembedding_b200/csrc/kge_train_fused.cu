@@ -109,7 +109,45 @@ struct SweepArgs {
     const float* PA;     // [B*parts][QP*H] partial dL/dq, relative to the item's own running max
     const float* PM;     // [B*parts][2]    (running max, pRotatE modulus partial)
     int* item_counter;   // part 1: work counter of F1w, reset here (stream order puts it before F1w)
+    // InterHT: (1/|a_e|, 1/|b_e|, proj_a, proj_b) of every row of `ent`, computed once per step by
+    // interht_inv_norm_kernel -- the sweep reads a candidate's two norms instead of reducing them over the CTA for every
+    // row group (that was 3 of the 4 block barriers and 8 of the 12 warp reductions per group of 4 rows).
+    const float4* invn;
 };
+
+// One warp per entity row: sums of squares of the two half rows -> inverse norms (tf.linalg.normalize / F.normalize eps).
+__global__ void __launch_bounds__(256)
+interht_inv_norm_kernel(const float* __restrict__ ent, long long E, int H, float eps, float4* __restrict__ invn) {
+    pdl_enter();
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long e = warp; e < E; e += nw) {
+        const float* row = ent + e * 2LL * H;
+        float sa = 0.f, sb = 0.f;
+        if ((H & 3) == 0) {
+            for (int k = 4 * lane; k < H; k += 128) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(row + k));
+                const float4 b = __ldg(reinterpret_cast<const float4*>(row + H + k));
+                sa = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, sa))));
+                sb = fmaf(b.x, b.x, fmaf(b.y, b.y, fmaf(b.z, b.z, fmaf(b.w, b.w, sb))));
+            }
+        } else {
+            for (int k = lane; k < H; k += 32) {
+                const float a = __ldg(row + k), b = __ldg(row + H + k);
+                sa = fmaf(a, a, sa);
+                sb = fmaf(b, b, sb);
+            }
+        }
+        sa = warp_sum(sa);
+        sb = warp_sum(sb);
+        if (lane == 0) {
+            float pa, pb;
+            const float ia = inv_norm(sa, eps, pa), ib = inv_norm(sb, eps, pb);
+            invn[e] = make_float4(ia, ib, pa, pb);
+        }
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // F1
@@ -125,7 +163,7 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL), RP = rel_planes_of(MODEL);
     __shared__ float red[4 * 32 * 2];      // block reductions: up to 8 values x 32 warps
     __shared__ float red2[2][RPI * 32];    // row-sum partials of the sweep, double-buffered by row group
-    __shared__ float sh_cn[RPI][2], sh_fin[8];  // sh_fin: m, z, l, g, g2
+    __shared__ float sh_fin[8];  // m, z, l, g, g2
 
     const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = (T + 31) >> 5;
     const int H = P.H, N = A.N;
@@ -162,18 +200,9 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         load_coords<RP, CH>(rv, rrow, H, tid, T, H);
         float nrm[2] = {0.f, 0.f};
         if constexpr (MODEL == KGE_INTERHT) {
-            float ss[2] = {0.f, 0.f};
-#pragma unroll
-            for (int j = 0; j < CH; ++j)
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    ss[0] = fmaf(fe[0][j][i], fe[0][j][i], ss[0]);
-                    ss[1] = fmaf(fe[1][j][i], fe[1][j][i], ss[1]);
-                }
-            block_reduce_vals<2>(ss, red);
-            float pj;
-            nrm[0] = inv_norm(ss[0], P.interht_eps, pj);
-            nrm[1] = inv_norm(ss[1], P.interht_eps, pj);
+            const float4 nv = __ldg(A.invn + (head ? t : h));
+            nrm[0] = nv.x;
+            nrm[1] = nv.y;
         }
 #pragma unroll
         for (int j = 0; j < CH; ++j)
@@ -236,32 +265,20 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
         float sg[(MODEL == KGE_INTERHT) ? RPI : 1][CH][4];
 #pragma unroll
         for (int rr = 0; rr < RPI; ++rr) load_coords<CP, CH>(c[rr], A.ent + (long long)cid[rr] * P.De, H, tid, T, H);
+        float cnv[(MODEL == KGE_INTERHT) ? RPI : 1][2];
+        if constexpr (MODEL == KGE_INTERHT) {  // the candidates' inverse norms: one broadcast load per row
+#pragma unroll
+            for (int rr = 0; rr < RPI; ++rr) {
+                const float4 nv = __ldg(A.invn + cid[rr]);
+                cnv[rr][0] = nv.x;
+                cnv[rr][1] = nv.y;
+            }
+        }
         // candidate ids of the NEXT row group: their latency hides behind this group's arithmetic
 #pragma unroll
         for (int rr = 0; rr < RPI; ++rr) {
             const int n = n0 + RPI + rr;
             cid[rr] = (n < N) ? (int)__ldg(A.neg + b * N + n) : 0;
-        }
-        if constexpr (MODEL == KGE_INTERHT) {  // candidate norms first
-            float ss[2 * RPI];
-#pragma unroll
-            for (int rr = 0; rr < RPI; ++rr) {
-                ss[2 * rr] = ss[2 * rr + 1] = 0.f;
-#pragma unroll
-                for (int j = 0; j < CH; ++j)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        ss[2 * rr] = fmaf(c[rr][0][j][i], c[rr][0][j][i], ss[2 * rr]);
-                        ss[2 * rr + 1] = fmaf(c[rr][1][j][i], c[rr][1][j][i], ss[2 * rr + 1]);
-                    }
-            }
-            block_reduce_vals<2 * RPI>(ss, red);
-            if (tid < RPI) {
-                float pj;
-                sh_cn[tid][0] = inv_norm(ss[2 * tid], P.interht_eps, pj);
-                sh_cn[tid][1] = inv_norm(ss[2 * tid + 1], P.interht_eps, pj);
-            }
-            __syncthreads();
         }
         // phase a: row sums; c is rewritten into the backward direction
         float* redp = red2[(n0 / RPI) & 1];
@@ -271,8 +288,8 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
             part[rr] = 0.f;
             float cn[2] = {0.f, 0.f};
             if constexpr (MODEL == KGE_INTERHT) {
-                cn[0] = sh_cn[rr][0];
-                cn[1] = sh_cn[rr][1];
+                cn[0] = cnv[rr][0];
+                cn[1] = cnv[rr][1];
             }
 #pragma unroll
             for (int j = 0; j < CH; ++j)
@@ -477,20 +494,10 @@ train_sweep_kernel(Params P, CoordConsts kc, int head_i, SweepArgs A) {
     load_coords<RP, CH>(rv, rrow, H, tid, T, H);
     float nh[2] = {0.f, 0.f}, nt[2] = {0.f, 0.f};
     float pjh[2] = {1.f, 1.f}, pjt[2] = {1.f, 1.f};  // InterHT: 0 where the F.normalize clamp is active (no projection)
-    if constexpr (MODEL == KGE_INTERHT) {
-        float ss[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int j = 0; j < CH; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                ss[0] = fmaf(he[0][j][i], he[0][j][i], ss[0]);
-                ss[1] = fmaf(he[1][j][i], he[1][j][i], ss[1]);
-                ss[2] = fmaf(te[0][j][i], te[0][j][i], ss[2]);
-                ss[3] = fmaf(te[1][j][i], te[1][j][i], ss[3]);
-            }
-        block_reduce_vals<4>(ss, red);
-        nh[0] = inv_norm(ss[0], P.interht_eps, pjh[0]); nh[1] = inv_norm(ss[1], P.interht_eps, pjh[1]);
-        nt[0] = inv_norm(ss[2], P.interht_eps, pjt[0]); nt[1] = inv_norm(ss[3], P.interht_eps, pjt[1]);
+    if constexpr (MODEL == KGE_INTERHT) {  // the same table values the staging above and the candidates use
+        const float4 vh = __ldg(A.invn + h), vt = __ldg(A.invn + t);
+        nh[0] = vh.x; nh[1] = vh.y; pjh[0] = vh.z; pjh[1] = vh.w;
+        nt[0] = vt.x; nt[1] = vt.y; pjt[0] = vt.z; pjt[1] = vt.w;
     }
     // q1 = planes in single form (fixed entity = head); equal to q in tail-batch mode
     float q1[QP][CH][4], crs[CH][4], srs[CH][4];
@@ -1059,6 +1066,53 @@ __device__ __forceinline__ void entity_use(float (&gc)[cand_planes_of(MODEL)][CH
     }
 }
 
+// InterHT: one use of the row.  v = +-(A (b_hat + 1) - a_hat B) + M with a_hat = a / |a|, b_hat = b / |b| of THIS row;
+// u = dL/dv; d a_hat, d b_hat; then the two row dots of the normalisation backward -- one block reduction per use, ONE
+// barrier: `red` alternates between two buffers from use to use, so the reads of use i are ordered before the writes of
+// use i + 2 by the barrier of use i + 1.
+template <int CH, bool HEAD>
+__device__ __forceinline__ void interht_entity_use(float (&gc)[2][CH][4], const float (&c)[2][CH][4], const float (&q)[3][CH][4],
+                                                   float g, const float (&cn)[2], const float (&cpj)[2], float* red, int tid,
+                                                   int T, int H) {
+    float dac[CH][4], dbc[CH][4], dots[2] = {0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float ac = c[0][j][k] * cn[0], bh = c[1][j][k] * cn[1], bc = bh + 1.0f;
+            const float Aq = q[0][j][k], Bv = q[1][j][k], Mq = q[2][j][k];
+            const float v = HEAD ? (ac * Bv - Aq * bc + Mq) : (Aq * bc - ac * Bv + Mq);
+            const float u = (4 * (tid + j * T) < H) ? -g * sgnf(v) : 0.f;
+            dac[j][k] = HEAD ? (u * Bv) : (-u * Bv);
+            dbc[j][k] = HEAD ? (-u * Aq) : (u * Aq);
+            dots[0] = fmaf(ac, dac[j][k], dots[0]);
+            dots[1] = fmaf(bh, dbc[j][k], dots[1]);
+        }
+    const int lane = tid & 31, warp = tid >> 5, nw = (T + 31) >> 5;
+    dots[0] = warp_sum(dots[0]);
+    dots[1] = warp_sum(dots[1]);
+    if (lane == 0) {
+        red[warp] = dots[0];
+        red[32 + warp] = dots[1];
+    }
+    __syncthreads();
+    float d0 = 0.f, d1 = 0.f;
+    for (int w = 0; w < nw; ++w) {
+        d0 += red[w];
+        d1 += red[32 + w];
+    }
+    d0 *= cpj[0];  // clamped half-row (F.normalize eps): y = x / eps, no projection term
+    d1 *= cpj[1];
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float ac = c[0][j][k] * cn[0], bh = c[1][j][k] * cn[1];
+            gc[0][j][k] += (dac[j][k] - ac * d0) * cn[0];
+            gc[1][j][k] += (dbc[j][k] - bh * d1) * cn[1];
+        }
+}
+
 // One CTA per entity row, each thread owning CH float4 chunks of every plane.  The uses of the row (bucket of the
 // row: negatives in ascending slot order, then the positives) are staged kUseChunk at a time into shared memory as
 // (dL/ds, source) pairs, so the loop over uses carries no dependent global loads: the q rows stream through a
@@ -1080,7 +1134,7 @@ __device__ __forceinline__ void cp_async_wait() {
 // parameter because the mere presence of the (empty) peer loop in the Adam epilogue cost the single-GPU kernel 13 %
 // (0.237 -> 0.269 ms: stores through unknown pointers between the m / v loads of consecutive chunks).
 template <int MODEL, int CH, bool HEAD, int TMAX, bool PEERS>
-__global__ void __launch_bounds__(TMAX, TMAX == 128 ? 6 : 2)
+__global__ void __launch_bounds__(TMAX, TMAX == 128 ? (MODEL == KGE_INTERHT ? 4 : 6) : 2)  // InterHT: 3 q planes, 48 KB ring
 train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ modulus, EntityArgs A, AdamScalars ad,
                          float l3, std::conditional_t<PEERS, EntityPeers, NoPeers> X) {
     pdl_enter();
@@ -1088,6 +1142,8 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
     __shared__ float red[2 * 32];
     __shared__ float use_g[kUseChunk];
     __shared__ int use_src[kUseChunk];  // >= 0: positive b whose q row applies; < 0: -1 - (compact gradient row)
+    __shared__ float red_ih[2][64];     // InterHT: the per-use reduction, double-buffered (interht_entity_use)
+    int ih_parity = 0;
     const int tid = threadIdx.x, T = blockDim.x, H = P.H;
     if (MODEL == KGE_PROTATE) kc.modulus = __ldg(modulus);
     extern __shared__ float4 ring[];  // [kRing][QP][CH][T]: slot (d, p, j) of thread tid -- only tid touches it
@@ -1109,7 +1165,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
         slot_s[k] = (uint32_t)__cvta_generic_to_shared(ring + k * T + tid);
         qbase[k] = reinterpret_cast<const char*>(A.Q + ((k / CH) * H + koff[k % CH]));
     }
-    if constexpr (MODEL != KGE_INTERHT) {  // chunks past H are never copied: they read as zeros
+    {  // chunks past H are never copied: they read as zeros
         for (int d = 0; d < kRing; ++d)
 #pragma unroll
             for (int k = 0; k < QP * CH; ++k)
@@ -1175,44 +1231,7 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
 #pragma unroll
                         for (int k = 0; k < 4; ++k) gc[p][j][k] += x[p][j][k];
             };
-            if constexpr (MODEL == KGE_INTERHT) {
-                for (int i = 0; i < n; ++i) {
-                    const int s0 = use_src[i];
-                    if (s0 < 0) {
-                        add_compact(s0);
-                        continue;
-                    }
-                    const float g = use_g[i];
-                    float q[QP][CH][4];
-                    load_coords<QP, CH>(q, A.Q + (long long)s0 * (QP * H), H, tid, T, H);
-                    // v, u = dL/dv, d a_hat, d b_hat, then the two row dots of the normalisation backward
-                    float dac[CH][4], dbc[CH][4], dots[2] = {0.f, 0.f};
-#pragma unroll
-                    for (int j = 0; j < CH; ++j)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float ac = c[0][j][k] * cn[0], bh = c[1][j][k] * cn[1], bc = bh + 1.0f;
-                            const float Aq = q[0][j][k], Bv = q[QP > 1 ? 1 : 0][j][k], Mq = q[QP > 2 ? 2 : 0][j][k];
-                            const float v = HEAD ? (ac * Bv - Aq * bc + Mq) : (Aq * bc - ac * Bv + Mq);
-                            const float u = (4 * (tid + j * T) < H) ? -g * sgnf(v) : 0.f;
-                            dac[j][k] = HEAD ? (u * Bv) : (-u * Bv);
-                            dbc[j][k] = HEAD ? (-u * Aq) : (u * Aq);
-                            dots[0] = fmaf(ac, dac[j][k], dots[0]);
-                            dots[1] = fmaf(bh, dbc[j][k], dots[1]);
-                        }
-                    block_reduce_vals<2>(dots, red);
-                    dots[0] *= cpj[0];  // clamped half-row (F.normalize eps): y = x / eps, no projection term
-                    dots[1] *= cpj[1];
-#pragma unroll
-                    for (int j = 0; j < CH; ++j)
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float ac = c[0][j][k] * cn[0], bh = c[1][j][k] * cn[1];
-                            gc[0][j][k] += (dac[j][k] - ac * dots[0]) * cn[0];
-                            gc[CP - 1][j][k] += (dbc[j][k] - bh * dots[1]) * cn[1];
-                        }
-                }
-            } else {
+            {
                 // q rows travel through a kRing-deep ring of thread-private shared-memory slots filled by cp.async:
                 // kRing - 1 rows are in flight while one is applied; uses stay in bucket order.  All addresses are
                 // thread constants (slot_s, goff) plus one per-use term.
@@ -1241,7 +1260,12 @@ train_entity_adam_kernel(Params P, CoordConsts kc, const float* __restrict__ mod
                         const uint32_t src = (i % kRing) * slot_bytes;
 #pragma unroll
                         for (int k = 0; k < QP * CH; ++k) lds128(q[k / CH][k % CH], slot_s[k] + src);
-                        entity_use<MODEL, CH, HEAD>(gc, c, q, use_g[i], kc);
+                        if constexpr (MODEL == KGE_INTERHT) {
+                            interht_entity_use<CH, HEAD>(gc, c, q, use_g[i], cn, cpj, red_ih[ih_parity], tid, T, H);
+                            ih_parity ^= 1;
+                        } else {
+                            entity_use<MODEL, CH, HEAD>(gc, c, q, use_g[i], kc);
+                        }
                     } else {
                         add_compact(sc);
                     }
@@ -1388,8 +1412,10 @@ struct FusedWs {
     int *counts, *offsets, *cursor, *items, *items_sorted, *items_b, *block_sums;
     float *PA, *PM;      // split sweep: per-item partial dL/dq and (running max, modulus partial)
     int* item_counter;
+    float4* invn;        // InterHT: inverse norms of every row of the table the sweep reads
     size_t total;
 };
+static inline size_t invn_bytes(const Params& P) { return P.model == KGE_INTERHT ? (size_t)P.E * sizeof(float4) : 0; }
 
 // split sweep (F1w): items per positive and rows per item
 static inline int f1w_parts(int64_t N) { return (int)std::max<int64_t>(1, std::min<int64_t>(8, (N + 31) / 32)); }
@@ -1430,6 +1456,7 @@ static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
     w.PA = (float*)take((size_t)B * f1w_parts(N) * qdim * sizeof(float));
     w.PM = (float*)take((size_t)B * f1w_parts(N) * 2 * sizeof(float));
     w.item_counter = (int*)take(64);
+    w.invn = (float4*)take(invn_bytes(P));
     w.total = off;
     return w;
 }
@@ -1437,7 +1464,8 @@ static FusedWs fused_carve(const Params& P, int64_t B, int64_t N, void* base) {
 size_t fused_step_workspace_bytes(const Params& P, int64_t B, int64_t N) { return fused_carve(P, B, N, nullptr).total; }
 size_t train_sweep_workspace_bytes(const Params& P, int64_t B, int64_t N) {
     const size_t qdim = (size_t)model_planes(P.model) * P.H;
-    return fz_align((size_t)B * f1w_parts(N) * qdim * sizeof(float)) + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)) + 512;
+    return fz_align((size_t)B * f1w_parts(N) * qdim * sizeof(float)) + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)) + 512 +
+           fz_align(invn_bytes(P));
 }
 
 bool fused_step_applicable(const Params& P, const kge_loss_opts& lo, int64_t B, int64_t N, const void* ent,
@@ -1528,7 +1556,7 @@ static cudaError_t launch_entity_inst(const Params& P, const CoordConsts& kc, co
                                       const EntityPeers& X, const AdamScalars& ad, float l3, int ethreads, cudaStream_t st) {
     cudaError_t e;
     auto kernel = train_entity_adam_kernel<MODEL, ECH, HEAD, TMAX, PEERS>;
-    const size_t ring_bytes = (MODEL == KGE_INTERHT) ? 0 : (size_t)kRing * model_planes(MODEL) * ECH * ethreads * sizeof(float4);
+    const size_t ring_bytes = (size_t)kRing * model_planes(MODEL) * ECH * ethreads * sizeof(float4);
     static size_t allowed = 0;
     if (ring_bytes > 40 * 1024 && allowed < ring_bytes) {  // static shared memory counts towards the 48 KB default
         if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes)) != cudaSuccess) return e;
@@ -1574,6 +1602,15 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         SweepArgs A{ent, rel, modulus, fc.pos, fc.neg, fc.w, (int)fc.B, (int)N, lo.negative_adversarial_sampling,
                     lo.uni_weight, lo.adversarial_temperature, fc.S, fc.Q, fc.GH, fc.GT, fc.GR, fc.GM, fc.stats,
                     fc.terms, fc.phase == 0 ? ws.counts : nullptr, fc.wsum, (int)fc.B_total};
+        if constexpr (MODEL == KGE_INTERHT) {
+            if (ws.invn == nullptr) return cudaErrorInvalidValue;
+            const int nb = (int)std::min<long long>((P.E + 7) / 8, 16LL * sm_count());
+            if ((e = launch_pdl(interht_inv_norm_kernel, dim3(nb), dim3(256), 0, st, (const float*)ent, (long long)P.E, P.H,
+                                P.interht_eps, ws.invn)) != cudaSuccess)
+                return e;
+            A.invn = ws.invn;
+            ps.launches(2);
+        }
         if (fc.phase != 2 && ws.PA != nullptr && f1w_applies(P, lo)) {
             if constexpr (MODEL != KGE_INTERHT) {
                 // split sweep: stage Q | one warp per candidate row | merge + positive score + chain rule
@@ -1723,6 +1760,9 @@ cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, cons
         ws.PA = (float*)base;
         ws.PM = (float*)(base + fz_align((size_t)B * f1w_parts(N) * qdim * sizeof(float)));
         ws.item_counter = (int*)((char*)ws.PM + fz_align((size_t)B * f1w_parts(N) * 2 * sizeof(float)));
+        ws.invn = (float4*)((char*)ws.item_counter + 256);
+    } else if (P.model == KGE_INTERHT) {
+        return cudaErrorInvalidValue;  // InterHT keeps its inverse-norm table in the sweep workspace
     }
     FusedCall fc{1, pos, neg, w, B, wsum, B_total, nullptr, nullptr, 0, 0, 0, o.S, o.Q, o.GH, o.GT, o.GR, o.GM, o.stats, o.terms};
     fc.stage_ev = stage_ev;
