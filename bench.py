@@ -206,6 +206,39 @@ def run_reference(a):
     emit(line)
 
 
+def l2_read_peak(lib, dev, timed, mbytes=32, iters=200):
+    """Measured L2 read bandwidth (GB/s): kge_probe_l2_read re-reads a 32 MB buffer (resident in the 126 MB L2) with every
+    SM touching every line, CUDA events around the launch, best of 3 (burst figure: a kernel timed alone)."""
+    import torch
+    buf = torch.ones(mbytes << 20, dtype=torch.uint8, device=dev)
+    sink = torch.zeros(1, dtype=torch.float32, device=dev)
+    nread = C.c_int64(0)
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    def run():
+        rc = lib.kge_probe_l2_read(C.c_void_p(buf.data_ptr()), buf.numel(), iters, C.c_void_p(sink.data_ptr()),
+                                   C.byref(nread), stream)
+        if rc != 0:
+            raise RuntimeError(lib.kge_last_error().decode())
+    run()
+    best = min(timed(run) for _ in range(3))
+    return nread.value / (best * 1e-3) / 1e9
+
+
+def l2_bytes(w):
+    """Bytes the two dominant stages request from L2 per launch (every candidate row / staged plane row is gathered once
+    per USE): what the L2 roofline is computed on."""
+    B, N, H = w["batch"], w["negatives"], w["hidden_dim"]
+    De, E = 2 * H, w["nentity"]
+    rows, parts = B * N, 8
+    return {
+        # candidate rows + ids + scores; Q rows per item; per-item partials written and read back; positives' rows
+        "fused_sweep(scores+loss+dL/dq)": rows * (De * 4 + 12) + 3 * B * parts * De * 4 + B * (3 * De + H) * 4 * 2,
+        # one staged plane row + (dL/ds, b) per use; p, m, v of every row read + written; compact rows of the positives
+        "entity_gather+adam": rows * (De * 4 + 12) + E * De * 24 + 2 * B * De * 4,
+    }
+
+
 def table_checksum(model):
     """Exact integer checksum of both tables (fp32 bit patterns summed as int64)."""
     import torch
@@ -358,6 +391,7 @@ def run_ours(a):
     lib.kge_profile_read(ms_sum, launches, 1)
     lib.kge_profile_enable(0)
     stages = {lib.kge_profile_stage_name(i).decode(): (ms_sum[i], launches[i]) for i in range(nst)}
+    l2_peak = l2_read_peak(lib, dev, timed) if rank == 0 else None
     # ---- e2e: the public API with the batch in pinned host memory ------------------------------------
     it = iter([host[(W + i) % nb] for i in range(K + 3)])
     for _ in range(3):
@@ -433,11 +467,19 @@ def run_ours(a):
                      "dram_frac": (traffic / (dom_ms * 1e-3) / 1e9 / peak) if (traffic and dom_ms > 0) else None,
                      "note": "algorithmic bytes are row gathers from the 116 MB entity table, most of which the 126 MB L2 "
                              "serves (traffic = DRAM bytes per launch from ncu is ~0.4x of them): frac can pass 1.0 and "
-                             "dram_frac is the share of the HBM peak the kernel really draws; what limits the kernel is "
-                             "shared-memory / issue throughput per row (profiles/r1_ncu_summary_final.md)",
+                             "dram_frac is the share of the HBM peak the kernel really draws; the binding roofline is the "
+                             "L2 slices' throughput: see `l2`",
                      "step": {"algorithmic_bytes": ab["step"], "achieved": ab["step"] / (step_ms * 1e-3) / 1e9,
                               "frac": ab["step"] / (step_ms * 1e-3) / 1e9 / peak,
-                              "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12}},
+                              "frac_of_8TBs": ab["step"] / (step_ms * 1e-3) / 8e12},
+                     # the roofline that actually binds the two dominant stages at this config: L2 slice throughput
+                     "l2": {"bound": "l2", "peak": l2_peak, "unit": "GB/s",
+                            "peak_source": "measured in this run: kge_probe_l2_read, 32 MB buffer re-read by every SM "
+                                           "(B300_MICROARCH.md: LTS cap ~6300 B/clk full chip)",
+                            "stages": {k: {"l2_bytes": v, "ms": stages[k][0] / K,
+                                           "achieved": v / (stages[k][0] / K * 1e-3) / 1e9,
+                                           "frac": v / (stages[k][0] / K * 1e-3) / 1e9 / l2_peak}
+                                       for k, v in l2_bytes(w).items() if world == 1 and stages.get(k, (0, 0))[0] > 0}}},
         "stages_ms_per_step": {k: v[0] / K for k, v in stages.items()},
         "profiled_region_ms_per_step": ms_prof / K,
         "dist_check": dist_check,
@@ -449,6 +491,29 @@ def run_ours(a):
         "eval_10m": ev_10m,
         "clocks": sampler.summary(),
     }
+    def _v(d, *path):
+        for k in path:
+            if not isinstance(d, dict) or k not in d:
+                return None
+            d = d[k]
+        return d
+    # the numbers of the other BASELINE configs in one compact object near the front of the line (the tail of a long
+    # line may be cut by whoever stores it)
+    extras = {
+        "eval_rotate_fb15k237_qps": _v(ev, "value"), "eval_rotate_sfu_frac": _v(ev, "roofline", "frac"),
+        "eval_gemm_complex_qps": _v(ev_gemm, "ComplEx", "value"), "eval_gemm_distmult_qps": _v(ev_gemm, "DistMult", "value"),
+        "eval_gemm_distmult_issued_frac": _v(ev_gemm, "DistMult", "roofline", "frac"),
+        "eval_10m_qps": _v(ev_10m, "value"), "eval_10m_checksum": _v(ev_10m, "checksum_n_greater"),
+        "train_interht_pytorch": _v(tr_interht, "pytorch", "value"), "train_interht_tf": _v(tr_interht, "tf", "value"),
+        "train_sharded_yago": _v(tr_sharded, "yago3-10", "value"),
+        "train_sharded_yago_ms": _v(tr_sharded, "yago3-10", "ms_per_step"),
+        "train_sharded_yago_check_ok": _v(tr_sharded, "yago3-10", "dist_check", "ok"),
+        "train_sharded_10m": _v(tr_sharded, "synthetic-10M", "value"),
+        "train_sharded_10m_ms": _v(tr_sharded, "synthetic-10M", "ms_per_step"),
+        "dist_check_ok": _v(dist_check, "ok"), "l2_peak_gbs": l2_peak,
+    }
+    line = {k: line[k] for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step")} | \
+        {"scaling_extras": extras} | {k: v for k, v in line.items() if k not in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step")}
     log("timing done; running the bounded CPU baseline sample ...")
     base = cpu_baseline(steps=2, warmup=1, budget_s=30.0) if not a.no_cpu_baseline else None
     line["cpu_baseline"] = ({k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "full_batch_extrapolated")}
@@ -660,11 +725,12 @@ def eval_bench(model, w, dev, timed, rank, world=1):
         from customknowledgegraphembedding_b200 import dist as kd
 
     def device_eval():
+        if world == 1:  # the two modes side by side on two streams (KGEModel.rank_queries_both_modes)
+            model.rank_queries_both_modes(q, csr)
+            return
         for mode in ("head-batch", "tail-batch"):
-            if world > 1:  # each rank scores its entity row range, one all-reduce of the integer counters
-                kd.rank_queries_sharded(model, q, mode, *csr[mode])
-            else:
-                model.rank_queries(q, mode, *csr[mode])
+            # each rank scores its entity row range, one all-reduce of the integer counters
+            kd.rank_queries_sharded(model, q, mode, *csr[mode])
     device_eval()
     ms = timed(device_eval)
     eargs = argparse.Namespace(nentity=w["nentity"], nrelation=w["nrelation"], countries=False)
@@ -677,8 +743,21 @@ def eval_bench(model, w, dev, timed, rank, world=1):
             metrics.update(kb.KGEModel.test_step(model, test_l, all_true, eargs))
     api_eval()
     ms_api = timed(api_eval)
+    sm_mhz = 1965.0
+    pk = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        with open(pk) as f:
+            sm_mhz = float(json.load(f).get("sm_max_mhz", sm_mhz))
+    coords = 2.0 * nq * w["nentity"] * w["hidden_dim"] / (ms * 1e-3) / max(world, 1)
+    sfu_peak = 148 * 16 * sm_mhz * 1e6
     return {"metric": "eval_queries_per_sec", "value": 2 * nq / (ms * 1e-3), "unit": "queries/s",
             "queries": 2 * nq, "candidates_per_query": w["nentity"], "ms": ms,
+            "roofline": {"bound": "sfu", "achieved": coords, "peak": sfu_peak, "unit": "pair-coordinates/s per GPU",
+                         "frac": coords / sfu_peak,
+                         "note": "RotatE needs one MUFU.SQRT per (query, candidate, complex coordinate); the SFU pipe "
+                                 "issues 16 per clock per SM: 148 SMs x 16 x %.0f MHz (max SM clock).  The whole call is "
+                                 "counted (staging, true scores, tiles, filter pass); the tile grid is 912 CTAs per mode = "
+                                 "6.16 waves on 148 SMs" % sm_mhz},
             "sharding": "none" if world == 1 else "entity rows over %d ranks, all-reduce of int64 counters" % world,
             "e2e": {"value": 2 * nq / (ms_api * 1e-3), "unit": "queries/s", "ms": ms_api,
                     "note": "KGEModel.test_step from Python triple lists: CSR filter build on host, H2D, D2H of ranks"},
@@ -749,6 +828,8 @@ def eval_10m_bench(dev, timed, world=1, nq=256):
     out = {"metric": "eval_queries_per_sec", "value": 2 * nq / (ms * 1e-3), "unit": "queries/s", "queries": 2 * nq,
            "candidates_per_query": E, "rows_per_gpu": hi - lo, "ms": ms, "scaling": "strong",
            "pair_coordinates_per_s": 2.0 * nq * E * H / (ms * 1e-3),
+           "roofline": {"bound": "sfu", "achieved": 2.0 * nq * E * H / (ms * 1e-3) / world, "peak": 148 * 16 * 1965e6,
+                        "unit": "pair-coordinates/s per GPU", "frac": 2.0 * nq * E * H / (ms * 1e-3) / world / (148 * 16 * 1965e6)},
            "checksum_n_greater": int(ng.sum().item()),  # identical for every N: the ranks do not depend on the sharding
            "sharding": "entity rows over %d ranks; query rows exchanged (all-reduce of [Q,2,De]); all-reduce of int64 "
                        "counters" % world}
@@ -798,6 +879,7 @@ def eval_gemm_bench(dev, timed, world=1):
                      "ms": ms, "roofline": {"bound": "tensor", "achieved": 3 * flops / (ms * 1e-3) / 1e12, "peak": peak,
                                             "unit": "TFLOP/s", "frac": 3 * flops / (ms * 1e-3) / 1e12 / peak,
                                             "peak_source": src, "useful_tflops": flops / (ms * 1e-3) / 1e12,
+                                            "useful_frac": flops / (ms * 1e-3) / 1e12 / peak,
                                             "note": "whole call: operand split, true-score tile, sort of the filter "
                                                     "lists and the counting tiles; 3 tf32 MMA passes per product"}}
         del m

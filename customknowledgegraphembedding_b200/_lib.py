@@ -118,6 +118,7 @@ PROTOTYPES = {
     "kge_shard_compact": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _I64, _P, _P, _SZ, _P]),
     "kge_shard_fetch_rows": (C.c_int, [_P, _P, _I64, _I64, C.POINTER(C.c_void_p), C.c_int, _I64, _P, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
+    "kge_probe_l2_read": (C.c_int, [_P, _SZ, C.c_int, _P, C.POINTER(C.c_int64), _P]),
     "kge_profile_enable": (C.c_int, [C.c_int]),
     "kge_profile_num_stages": (C.c_int, []),
     "kge_profile_stage_name": (C.c_char_p, [C.c_int]),

@@ -102,11 +102,12 @@ class KGEModel(nn.Module):
         self._ahead = {}     # id(iterator) -> (iterator, batch, staged device copy or None); holding the iterator pins its id
         self._stage = None   # copy stream and the pool of staging buffer sets
         self._hot = None     # argument cache of the staged train step (pointers, structs, step counters)
+        self._eval_streams = None  # two side streams: the head-batch and tail-batch rankings of a chunk run concurrently
 
     def __getstate__(self):
         # streams, events, staged batches and workspaces are per-process scratch: never pickled / deep-copied
         d = self.__dict__.copy()
-        d.update(_ahead={}, _stage=None, _ws={}, _hot=None)
+        d.update(_ahead={}, _stage=None, _ws={}, _hot=None, _eval_streams=None)
         return d
 
     # ------------------------------------------------------------------------------------
@@ -458,6 +459,31 @@ class KGEModel(nn.Module):
                              None if self._modulus() is None else self._modulus().detach(), to(queries),
                              entity_lo, entity_hi, to(filter_indptr), to(filter_idx))
 
+    @torch.no_grad()
+    def rank_queries_both_modes(self, queries: torch.Tensor, filters: Dict[str, tuple]):
+        """``{mode: rank_queries(queries, mode, *filters[mode])}`` for head-batch and tail-batch with the two rankings on
+        two side streams: the tile kernel holds one CTA per SM and a ranking of Q x E is a whole number of 148-CTA waves
+        plus a partial one (FB15k-237, 1024 queries: 6.16) -- run together, the partial wave of one mode fills with tiles
+        of the other, and the small staging / true-score / filter kernels of one hide under the tiles of the other."""
+        dev = self.entity_embedding.device
+        cur = torch.cuda.current_stream(dev)
+        if self._eval_streams is None or self._eval_streams[0].device != dev:
+            self._eval_streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+        queries = queries.to(dev, non_blocking=True)
+        filters = {m: tuple(None if t is None else t.to(dev, non_blocking=True) for t in f) for m, f in filters.items()}
+        start = torch.cuda.Event()
+        start.record(cur)
+        out = {}
+        for side, mode in zip(self._eval_streams, ("head-batch", "tail-batch")):
+            side.wait_event(start)
+            with torch.cuda.stream(side):
+                out[mode] = self.rank_queries(queries, mode, *filters[mode])
+        for side, mode in zip(self._eval_streams, ("head-batch", "tail-batch")):
+            cur.wait_stream(side)
+            for t in out[mode]:
+                t.record_stream(cur)  # produced on the side stream, consumed on the caller's
+        return out
+
     @staticmethod
     def test_step(model, test_triples, all_true_triples, args, rank_fn=None):
         """Evaluate the model on test or valid datasets: filtered MRR / MR / HITS@1,3,10 over
@@ -480,21 +506,28 @@ class KGEModel(nn.Module):
             return {"auc_pr": average_precision_score(np.array(y_true), y_score)}
         if dev.type != "cuda" and rank_fn is None:
             raise RuntimeError("KGEModel.test_step: model is on %s; move it to a CUDA device (no CPU fallback)" % dev)
-        if rank_fn is None:
-            rank_fn = model.rank_queries
         nentity = getattr(args, "nentity", None) or model.nentity
         T = np.asarray(test_triples, dtype=np.int64).reshape(-1, 3)
         maps = model._filter_maps(all_true_triples)
         chunk = int(getattr(model, "eval_chunk", 4096))
-        ranks, ties = [], 0
-        for mode in ("head-batch", "tail-batch"):
-            for lo in range(0, len(T), chunk):
-                q = T[lo:lo + chunk]
-                indptr, idx = KGEModel.build_filter_csr(maps, q, mode, nentity)
-                _, n_greater, n_equal = rank_fn(torch.from_numpy(q), mode, torch.from_numpy(indptr),
-                                                torch.from_numpy(idx))
-                ranks.append((1 + n_greater).cpu().numpy())
+        ranks, ties = {"head-batch": [], "tail-batch": []}, 0
+        both = rank_fn is None and dev.type == "cuda" and getattr(model, "eval_two_streams", True)
+        if rank_fn is None:
+            rank_fn = model.rank_queries
+        for lo in range(0, len(T), chunk):
+            q = T[lo:lo + chunk]
+            csr = {mode: tuple(torch.from_numpy(a) for a in KGEModel.build_filter_csr(maps, q, mode, nentity))
+                   for mode in ("head-batch", "tail-batch")}
+            if both:  # the two modes of a chunk side by side on two streams (same integers either way)
+                res = model.rank_queries_both_modes(torch.from_numpy(q), csr)
+            else:
+                res = {mode: rank_fn(torch.from_numpy(q), mode, *csr[mode]) for mode in ("head-batch", "tail-batch")}
+            for mode in ("head-batch", "tail-batch"):
+                _, n_greater, n_equal = res[mode]
+                ranks[mode].append((1 + n_greater).cpu().numpy())
                 ties += int(n_equal.sum().item())
+        # upstream's query order: every head-batch query, then every tail-batch query
+        ranks = ranks["head-batch"] + ranks["tail-batch"]
         ranks = np.concatenate(ranks) if ranks else np.zeros(0, dtype=np.int64)
         model.last_eval = {"ranks": ranks, "n_tied_candidates": ties}
         if ties:

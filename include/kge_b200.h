@@ -490,6 +490,11 @@ KGE_API int kge_profile_num_stages(void);
 KGE_API const char *kge_profile_stage_name(int stage);
 KGE_API int kge_profile_read(float *ms_sum, int64_t *launches, int reset);
 
+/* Measurement probe (bench.py `roofline.l2`; no reference counterpart): a persistent grid re-reads `bytes` of `buf`
+ * (device, 16-byte aligned, should fit L2: 32 MB) `iters` times with L2-only 128-bit loads; *bytes_read (host) = bytes
+ * requested from L2 in total.  The caller times the call with events on `stream`.  sink: one device float. */
+KGE_API int kge_probe_l2_read(const void *buf, size_t bytes, int iters, float *sink, int64_t *bytes_read, void *stream);
+
 typedef enum {
     KGE_WS_BACKWARD = 0, /* kge_score_backward (deterministic) */
     KGE_WS_LOSS = 1,

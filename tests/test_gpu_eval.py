@@ -163,3 +163,28 @@ def test_countries_auc_pr():
         y_score = om(sample).squeeze(1).numpy()
     want = average_precision_score(y_true, y_score)
     assert set(got) == {"auc_pr"} and abs(got["auc_pr"] - want) < 1e-6
+
+
+def test_both_modes_on_two_streams_equal_sequential():
+    """rank_queries_both_modes (head-batch and tail-batch rankings side by side on two streams) gives the integers of
+    the two sequential calls; test_step takes that path by default and `eval_two_streams = False` turns it off."""
+    import customknowledgegraphembedding_b200 as kb
+    E, R, H = 3000, 5, 200
+    om, gm = _pair("RotatE", E, R, H, seed=4)
+    true, test = _graph(E, R, n_true=4000, n_test=300, seed=9)
+    q = torch.tensor(test, dtype=torch.int64)
+    maps = gm._filter_maps(true)
+    csr = {m: tuple(torch.from_numpy(a) for a in kb.KGEModel.build_filter_csr(maps, q.numpy(), m, E))
+           for m in ("head-batch", "tail-batch")}
+    for _ in range(3):
+        both = gm.rank_queries_both_modes(q, csr)
+        for mode in ("head-batch", "tail-batch"):
+            want = gm.rank_queries(q, mode, *csr[mode])
+            for a, b in zip(both[mode], want):
+                assert torch.equal(a, b), mode
+    args = ko.Args(nentity=E, nrelation=R, test_batch_size=16)
+    m1 = type(gm).test_step(gm, test, true, args)
+    r1 = gm.last_eval["ranks"].copy()
+    gm.eval_two_streams = False
+    m2 = type(gm).test_step(gm, test, true, args)
+    assert np.array_equal(r1, gm.last_eval["ranks"]) and m1 == m2
