@@ -230,7 +230,7 @@ def l2_bytes(w):
     per USE): what the L2 roofline is computed on."""
     B, N, H = w["batch"], w["negatives"], w["hidden_dim"]
     De, E = 2 * H, w["nentity"]
-    rows, parts = B * N, 8
+    rows, parts = B * N, max(1, min(8, (N + 127) // 128))  # partials per positive of the CTA-cooperative rows kernel
     return {
         # candidate rows + ids + scores; Q rows per item; per-item partials written and read back; positives' rows
         "fused_sweep(scores+loss+dL/dq)": rows * (De * 4 + 12) + 3 * B * parts * De * 4 + B * (3 * De + H) * 4 * 2,
@@ -297,7 +297,9 @@ def run_ours(a):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a collective that some rank never joins aborts after 3 minutes instead of hanging the whole run
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     lib = _lib.load()
     w = WORKLOAD
     K, W = a.steps, max(a.warmup, 3)
@@ -391,7 +393,7 @@ def run_ours(a):
     lib.kge_profile_read(ms_sum, launches, 1)
     lib.kge_profile_enable(0)
     stages = {lib.kge_profile_stage_name(i).decode(): (ms_sum[i], launches[i]) for i in range(nst)}
-    l2_peak = l2_read_peak(lib, dev, timed) if rank == 0 else None
+    l2_peak = l2_read_peak(lib, dev, timed)  # on every rank: `timed` is collective (barrier + max over ranks)
     # ---- e2e: the public API with the batch in pinned host memory ------------------------------------
     it = iter([host[(W + i) % nb] for i in range(K + 3)])
     for _ in range(3):
@@ -418,6 +420,8 @@ def run_ours(a):
             dist_check["ok"] = bool(dist_check["ok_before_timing"] and spread == [0, 0])
             if not dist_check["ok"]:
                 log("DIST CHECK FAILED: %s" % json.dumps(dist_check))
+    if rank == 0:
+        log("train sections done (%.3f ms/step); eval / sharded sections ..." % (ms_value / K))
     # ---- eval: filtered ranking of 2048 queries against all entities --------------------------------
     if a.train_only:
         smp = ev = ev_gemm = None
@@ -427,8 +431,14 @@ def run_ours(a):
         tr_interht = train_config_bench(CONFIG3, dev, timed, min(K, 50)) if world == 1 else None
         smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
         ev = eval_bench(model, w, dev, timed, rank, world)
+        if rank == 0:
+            log("eval done; eval_gemm ...")
         ev_gemm = eval_gemm_bench(dev, timed, world)
+        if rank == 0:
+            log("eval_gemm done; eval_10m ...")
         ev_10m = eval_10m_bench(dev, timed, world) if not a.no_eval10m else {"skipped": "--no-eval10m"}
+        if rank == 0:
+            log("eval_10m done; train_sharded ...")
     tr_sharded = None
     if a.sharded or not a.train_only:
         tr_sharded = {"yago3-10": train_sharded_bench("yago3-10", dev, timed, rank, world, dist, min(K, 20))}

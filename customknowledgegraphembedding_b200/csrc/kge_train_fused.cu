@@ -679,17 +679,33 @@ struct RowsArgs {
 // Candidate rows reach the warp through a warp-private ring of R shared-memory slots filled by 1-D bulk copies (TMA,
 // one instruction per 8 KB row, completion on an mbarrier): the copy of row n + R starts as soon as row n has been
 // lifted into registers, so it overlaps the reduction and the accumulation pass of rows n .. n + R - 1.
+//
+// Round 2: a work item belongs to a CTA, not to a warp.  Item = (positive b, part p) = up to 128 consecutive candidates
+// of b (fewer, larger parts than before: ceil(N / 128), at most 8); the 4 warps of the CTA take a quarter each.  q_b is
+// staged ONCE per item for the four warps (8 kB per CTA instead of per warp), which leaves room for R = 2 row slots per
+// warp at the same 3 CTAs per SM: two rows in flight per warp.  At the end of the item the four partial dL/dq (each
+// relative to its warp's running max) are merged in fixed order through the row slots, so one partial per 128 rows
+// leaves the SM instead of one per 32: a quarter of the PA traffic, of the Q re-reads and of the merge pass's work.
+__host__ __device__ constexpr uint32_t rows_warp_region(uint32_t slot_bytes, int R, int QP, int CH) {
+    return (R * slot_bytes > (uint32_t)(QP * CH * 512)) ? R * slot_bytes : (uint32_t)(QP * CH * 512);
+}
+
 template <int MODEL, int CH, bool HEAD, int R>
 __global__ void __launch_bounds__(128, 3)
 train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
     pdl_enter();
     constexpr int QP = model_planes(MODEL), CP = cand_planes_of(MODEL);
-    extern __shared__ float4 f1w_q[];  // [warp][QP][CH][32] | [warp][R][slot_bytes] | [warp][R] mbarriers
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float4* myq = f1w_q + warp * (QP * CH * 32);
+    constexpr int QV = QP * CH * 32;     // float4 per staged q_b (and per partial dL/dq)
+    extern __shared__ float4 f1w_q[];    // [QP][CH][32] q_b | [warp] region (R row slots / merge scratch) | [warp][R] mbarriers
+    __shared__ int sh_item;
+    __shared__ float sh_pm[4][2];        // per warp: running max, modulus partial
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float4* myq = f1w_q;
     const uint32_t row_bytes = (uint32_t)P.De * 4u, slot_bytes = (row_bytes + 127u) & ~127u;
-    const uint32_t ring_s = smem_u32(f1w_q + 4 * (QP * CH * 32)) + warp * R * slot_bytes;
-    const uint32_t bars_s = smem_u32(f1w_q + 4 * (QP * CH * 32)) + 4 * R * slot_bytes + warp * R * 8;
+    const uint32_t region = rows_warp_region(slot_bytes, R, QP, CH);
+    const uint32_t regions_s = smem_u32(f1w_q + QV);
+    const uint32_t ring_s = regions_s + warp * region;
+    const uint32_t bars_s = regions_s + 4 * region + warp * R * 8;
     if (lane == 0) {
 #pragma unroll
         for (int r = 0; r < R; ++r) mbar_init(bars_s + 8 * r, 1);
@@ -702,26 +718,25 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
     const int total = A.B * A.parts;
     const int jfull = H / 128;  // chunks whose 32 lanes all hold live coordinates
     const float cn[2] = {0.f, 0.f};
+    const int rpw = (A.rpp + 3) / 4;  // rows of a part per warp
 
     for (;;) {
-        int item = 0;
-        if (lane == 0) item = atomicAdd(A.counter, 1);
-        item = __shfl_sync(0xffffffffu, item, 0);
+        __syncthreads();  // the previous item is over: q_b and the merge scratch may be rewritten
+        if (tid == 0) sh_item = atomicAdd(A.counter, 1);
+        __syncthreads();
+        const int item = sh_item;
         if (item >= total) break;
         const long long b = item / A.parts;
-        const int n0 = (item % A.parts) * A.rpp, n1 = min(N, n0 + A.rpp);
+        const int p0 = (item % A.parts) * A.rpp, p1 = min(N, p0 + A.rpp);
+        const int n0 = min(p1, p0 + warp * rpw), n1 = min(p1, n0 + rpw);  // this warp's quarter (may be empty)
 
-        __syncwarp();  // the previous item's reads of myq are done
-#pragma unroll
-        for (int pl = 0; pl < QP; ++pl)
-#pragma unroll
-            for (int j = 0; j < CH; ++j) {
-                const int k0 = 4 * (lane + 32 * j);
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);  // padding coordinates: q = 0 and c = 0 give a zero term
-                if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(A.Q + (b * QP + pl) * H + k0));
-                myq[(pl * CH + j) * 32 + lane] = v;
-            }
-        __syncwarp();
+        for (int idx = tid; idx < QV; idx += 128) {
+            const int pl = idx / (CH * 32), k0 = 4 * ((idx & 31) + 32 * ((idx >> 5) % CH));
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);  // padding coordinates: q = 0 and c = 0 give a zero term
+            if (k0 < H) v = __ldg(reinterpret_cast<const float4*>(A.Q + (b * QP + pl) * H + k0));
+            f1w_q[idx] = v;
+        }
+        __syncthreads();
 
         float acc[QP][CH][4];
 #pragma unroll
@@ -859,19 +874,54 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
                     if (QP > 1) acc[QP > 1 ? 1 : 0][j][i] = aa[1];
                 }
         }
+        // ---- merge of the four warps' partials, fixed order (warp 0, 1, 2, 3) --------------------------------------
+        // every copy into this warp's slots has landed and has been read (each row was waited for and lifted): the
+        // region is free to hold the warp's partial, lane-owned layout [(pl, j)][lane]
+        {
+            float4* mine = f1w_q + QV + warp * (region / 16);
 #pragma unroll
-        for (int pl = 0; pl < QP; ++pl)
+            for (int pl = 0; pl < QP; ++pl)
 #pragma unroll
-            for (int j = 0; j < CH; ++j) {
-                const int k0 = 4 * (lane + 32 * j);
-                if (k0 < H)
-                    *reinterpret_cast<float4*>(A.PA + ((long long)item * QP + pl) * H + k0) =
-                        make_float4(acc[pl][j][0], acc[pl][j][1], acc[pl][j][2], acc[pl][j][3]);
+                for (int j = 0; j < CH; ++j)
+                    mine[(pl * CH + j) * 32 + lane] = make_float4(acc[pl][j][0], acc[pl][j][1], acc[pl][j][2], acc[pl][j][3]);
+            if (lane == 0) {
+                sh_pm[warp][0] = m_run;
+                sh_pm[warp][1] = g_run;
             }
-        if (lane == 0) {
-            A.PM[2 * (long long)item] = m_run;
-            A.PM[2 * (long long)item + 1] = g_run;
         }
+        __syncthreads();
+        {
+            float m = -INFINITY, f[4], g = 0.f;
+            if (A.adv) {
+#pragma unroll
+                for (int w = 0; w < 4; ++w) m = fmaxf(m, sh_pm[w][0]);
+            }
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                f[w] = A.adv ? ((sh_pm[w][0] == -INFINITY) ? 0.f : expf(sh_pm[w][0] - m)) : 1.0f;
+                g = fmaf(sh_pm[w][1], f[w], g);
+            }
+            for (int idx = tid; idx < QV; idx += 128) {
+                const int pl = idx / (CH * 32), k0 = 4 * ((idx & 31) + 32 * ((idx >> 5) % CH));
+                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const float4 v = f1w_q[QV + w * (region / 16) + idx];
+                    o.x = fmaf(v.x, f[w], o.x);
+                    o.y = fmaf(v.y, f[w], o.y);
+                    o.z = fmaf(v.z, f[w], o.z);
+                    o.w = fmaf(v.w, f[w], o.w);
+                }
+                if (k0 < H) *reinterpret_cast<float4*>(A.PA + ((long long)item * QP + pl) * H + k0) = o;
+            }
+            if (tid == 0) {
+                A.PM[2 * (long long)item] = m;
+                A.PM[2 * (long long)item + 1] = g;
+            }
+        }
+        // the regions were written and read through the generic proxy; the next item's row copies (async proxy) come
+        // after this fence and the barrier at the top of the loop
+        fence_proxy_async();
     }
 }
 
@@ -1418,7 +1468,7 @@ struct FusedWs {
 static inline size_t invn_bytes(const Params& P) { return P.model == KGE_INTERHT ? (size_t)P.E * sizeof(float4) : 0; }
 
 // split sweep (F1w): items per positive and rows per item
-static inline int f1w_parts(int64_t N) { return (int)std::max<int64_t>(1, std::min<int64_t>(8, (N + 31) / 32)); }
+static inline int f1w_parts(int64_t N) { return (int)std::max<int64_t>(1, std::min<int64_t>(8, (N + 127) / 128)); }
 static int g_sweep_variant = 1;  // 1 = warp per row (F1w) where it applies, 0 = row groups per CTA
 void train_set_sweep_variant(int v) { g_sweep_variant = v ? 1 : 0; }
 static inline bool att_weights(const kge_loss_opts& lo) { return !lo.detach_weights && lo.negative_adversarial_sampling; }
@@ -1516,9 +1566,10 @@ struct FusedCall {
 template <int MODEL, int CHW, bool HEAD, int R>
 static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc, const RowsArgs& A, cudaStream_t st) {
     auto kernel = train_sweep_rows_kernel<MODEL, CHW, HEAD, R>;
-    // per warp: the staged q planes, R row slots (128-byte aligned) and their mbarriers
-    const size_t slot_bytes = ((size_t)P.De * 4 + 127) & ~(size_t)127;
-    const size_t smem = (size_t)4 * model_planes(MODEL) * CHW * 32 * sizeof(float4) + 4 * R * slot_bytes + 4 * R * 8;
+    // per CTA: the staged q planes; per warp: a region of R row slots (128-byte aligned) and R mbarriers
+    const uint32_t slot_bytes = ((uint32_t)P.De * 4u + 127u) & ~127u;
+    const size_t smem = (size_t)model_planes(MODEL) * CHW * 32 * sizeof(float4) +
+                        4 * (size_t)rows_warp_region(slot_bytes, R, model_planes(MODEL), CHW) + 4 * R * 8;
     static size_t grid_for = 0;
     static int grid = 0;  // persistent: every CTA the device can hold
     if (grid_for != smem) {
@@ -1532,7 +1583,7 @@ static cudaError_t launch_sweep_rows_inst(const Params& P, const CoordConsts& kc
         grid_for = smem;
     }
     const int items = A.B * A.parts;
-    return launch_pdl(kernel, dim3(std::min(grid, (items + 3) / 4)), dim3(128), smem, st, P, kc, A);
+    return launch_pdl(kernel, dim3(std::min(grid, items)), dim3(128), smem, st, P, kc, A);
 }
 
 template <int MODEL>
@@ -1540,10 +1591,11 @@ static cudaError_t launch_sweep_rows(const Params& P, const CoordConsts& kc, boo
     if constexpr (MODEL == KGE_INTERHT) {
         return cudaErrorInvalidValue;
     } else {
-        // R = 1: 16 KB per warp keeps 12 warps on an SM; R = 2 (8 warps) measured slower (0.367 vs 0.311 ms)
+        // R = 2 row slots per warp: with q_b staged once per CTA, 8 + 4 * 16 kB per CTA still keeps 3 CTAs (12 warps) on
+        // an SM at H = 1000
 #define KGE_ROWS(CHW)                                                                                                   \
-    return head ? launch_sweep_rows_inst<MODEL, CHW, true, 1>(P, kc, R, st)                                             \
-                : launch_sweep_rows_inst<MODEL, CHW, false, 1>(P, kc, R, st)
+    return head ? launch_sweep_rows_inst<MODEL, CHW, true, 2>(P, kc, R, st)                                             \
+                : launch_sweep_rows_inst<MODEL, CHW, false, 2>(P, kc, R, st)
         if (P.H <= 256) { KGE_ROWS(2); }
         if (P.H <= 512) { KGE_ROWS(4); }
         KGE_ROWS(8);
