@@ -928,21 +928,57 @@ train_sweep_rows_kernel(Params P, CoordConsts kc, RowsArgs A) {
 // ------------------------------------------------------------------------------------------------
 // F2: per-bucket sort (one warp per entity): ascending item order whatever order the fill produced
 // ------------------------------------------------------------------------------------------------
+// Buckets of up to kSortSmem uses are staged in a warp-private shared-memory strip and sorted there (bitonic network on
+// the strip padded to a power of two: O(n log^2 n) instead of the n^2 rank counting of round 1, which read the bucket
+// from global memory once per item -- at 8 ranks a row of the global batch has 8x the uses and the quadratic pass was the
+// largest part of the apply's bucket build).  Item ids are unique, so the order is total.  Longer buckets keep the
+// rank-counting path (correct for any length).
+constexpr int kSortSmem = 1024;
 __global__ void __launch_bounds__(256)
 bucket_sort_kernel(const int* __restrict__ offsets, const int* __restrict__ in, int* __restrict__ out,
                    int* __restrict__ out_b, long long E, int N) {
     pdl_enter();
+    __shared__ int strip_all[8][kSortSmem];
     const int lane = threadIdx.x & 31;
+    int* strip = strip_all[threadIdx.x >> 5];
     const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     for (long long e = warp; e < E; e += nwarps) {
-        const int beg = offsets[e], end = offsets[e + 1];
-        for (int idx = beg + lane; idx < end; idx += 32) {
-            const int it = in[idx];
-            int rank = 0;
-            for (int j = beg; j < end; ++j) rank += (in[j] < it) ? 1 : 0;
-            out[beg + rank] = it;
-            out_b[beg + rank] = it / N;  // positive index of a candidate use (unused for head / tail uses)
+        const int beg = offsets[e], end = offsets[e + 1], len = end - beg;
+        if (len <= 0) continue;
+        if (len <= kSortSmem) {
+            int P = 32;
+            while (P < len) P <<= 1;
+            for (int i = lane; i < P; i += 32) strip[i] = (i < len) ? in[beg + i] : 0x7fffffff;
+            __syncwarp();
+            for (int k = 2; k <= P; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = lane; i < P; i += 32) {
+                        const int ixj = i ^ j;
+                        if (ixj > i) {
+                            const int a = strip[i], b = strip[ixj];
+                            if ((a > b) == ((i & k) == 0)) {
+                                strip[i] = b;
+                                strip[ixj] = a;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+            for (int i = lane; i < len; i += 32) {
+                const int it = strip[i];
+                out[beg + i] = it;
+                out_b[beg + i] = it / N;  // positive index of a candidate use (unused for head / tail uses)
+            }
+            __syncwarp();  // the strip is reused by the warp's next bucket
+        } else {
+            for (int idx = beg + lane; idx < end; idx += 32) {
+                const int it = in[idx];
+                int rank = 0;
+                for (int j = beg; j < end; ++j) rank += (in[j] < it) ? 1 : 0;
+                out[beg + rank] = it;
+                out_b[beg + rank] = it / N;
+            }
         }
     }
 }

@@ -354,3 +354,11 @@ def test_sweep_variants_agree_at_config2():
             worst[k] = max(worst.get(k, 0.0), rowerr)
     print("sweep variants, worst row-relative difference over 6 batches:", {k: "%.2e" % v for k, v in worst.items()})
     assert all(v <= 2e-5 for v in worst.values()), worst
+
+
+@pytest.mark.parametrize("name", ["TransE", "RotatE"])
+def test_very_hot_rows_long_buckets(name):
+    """E = 48, B = 512, N = 256: ~2750 uses per entity row -- buckets longer than the 1024-entry shared-memory strip of the
+    bucket sort (rank-counting path) and 22 chunks of 128 uses per row in the entity kernel."""
+    _one_step_case(name, 48, 2, 64, 512, 256, "head-batch", seed=21)
+    _one_step_case(name, 48, 2, 64, 512, 256, "tail-batch", seed=22, uni=True, adv=False)
