@@ -11,9 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 11
-APPLY_PREPARE, APPLY_ROWS, APPLY_FINISH, APPLY_ALL = 1, 2, 4, 7  # kge_train_apply_parts
-EXCHANGE_EARLY, EXCHANGE_LATE, EXCHANGE_ALL = 1, 2, 3  # kge_train_exchange_parts
+ABI_VERSION = 12
 
 # kge_model_id / kge_mode / kge_ws_kind
 MODEL_IDS = {"TransE": 0, "DistMult": 1, "ComplEx": 2, "RotatE": 3, "pRotatE": 4, "InterHT": 5}
@@ -90,27 +88,14 @@ PROTOTYPES = {
     "kge_stream_wait_event": (C.c_int, [_P, _P]),
     "kge_train_sweep": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
                                   C.POINTER(StepBuffers), _P, _SZ, _P]),
-    "kge_train_sweep_staged": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, C.POINTER(LossOpts), _P, _I64,
-                                         C.POINTER(StepBuffers), _P, _SZ, _P, _P]),
     "kge_train_apply": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                   C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P, _P,
                                   _P, _SZ, _P]),
-    "kge_train_apply_parts": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
-                                        C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64,
-                                        C.c_int, _P, _P, _P, _SZ, _P]),
     "kge_train_apply_peers": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                         C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64,
-                                        C.c_int, C.c_int, C.POINTER(C.c_void_p), _P, _P, _P, _SZ, _P]),
-    "kge_train_apply_multicast": (C.c_int, [_DESC, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
-                                            C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64,
-                                            C.c_int, C.c_int, C.POINTER(C.c_void_p), _P, _P, _P, _P, _SZ, _P]),
+                                        C.c_int, C.POINTER(C.c_void_p), _P, _P, _P, _P, _SZ, _P]),
     "kge_train_exchange": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
                                      C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _P]),
-    "kge_train_exchange_parts": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
-                                           C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, _P]),
-    "kge_train_exchange_multicast": (C.c_int, [_DESC, _P, _P, _I64, _I64, C.POINTER(StepBuffers), C.c_int, C.c_int,
-                                               C.POINTER(StepBuffers), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int,
-                                               C.POINTER(StepBuffers), _P, _P, _P]),
     "kge_train_apply_shard": (C.c_int, [_DESC, C.c_int, _P, _I64, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64,
                                         C.POINTER(LossOpts), C.POINTER(AdamOpts), C.POINTER(StepBuffers), _I64, _I64, _P,
                                         _P, _P, _SZ, _P]),

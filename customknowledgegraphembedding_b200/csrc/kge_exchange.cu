@@ -50,32 +50,9 @@ __device__ __forceinline__ void copy_row4(float* __restrict__ dst, const float* 
 }
 
 // one row of n 4-byte elements to the same offset of every rank's buffer: each 16-byte chunk is loaded ONCE and stored
-// to all `world` destinations (independent fire-and-forget stores, constant indices into the parameter bank) -- the
-// per-peer loop around a load/store pair read the local row once per peer and kept one store in flight per thread
-// the same row through ONE NVSwitch multicast address: the switch replicates every store to all ranks
-__device__ __forceinline__ void mc_row4(void* dst_base, long long dst_off, const float* __restrict__ src, int n) {
-    float* dst = reinterpret_cast<float*>(dst_base) + dst_off;
-    const bool vec = ((n & 3) == 0) && (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0);
-    if (vec) {
-        const float4* s4 = reinterpret_cast<const float4*>(src);
-        for (int i = threadIdx.x; i < n / 4; i += blockDim.x) {
-            const float4 v = s4[i];
-            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * i), "f"(v.x), "f"(v.y),
-                         "f"(v.z), "f"(v.w)
-                         : "memory");
-        }
-    } else {
-        for (int i = threadIdx.x; i < n; i += blockDim.x)
-            asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(dst + i), "f"(src[i]) : "memory");
-    }
-}
-
+// to all `world` destinations (independent fire-and-forget stores, constant indices into the parameter bank)
 template <typename PtrArray>
 __device__ __forceinline__ void fan_row4(const PtrArray& dst, long long dst_off, const float* __restrict__ src, int n, int world) {
-    if (world < 0) {  // multicast: entry 0 is the multicast mapping of the buffer
-        mc_row4(dst[0], dst_off, src, n);
-        return;
-    }
     bool vec = ((n & 3) == 0) && ((dst_off & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
 #pragma unroll
     for (int p = 0; p < kMaxPeers; ++p)
@@ -100,19 +77,17 @@ __device__ __forceinline__ void fan_row4(const PtrArray& dst, long long dst_off,
 
 __global__ void __launch_bounds__(256)
 exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos, const int64_t* __restrict__ neg, int B,
-                int N, int q_row, int De, int Dr, int rank, int world, long long rows_per_rank, int early, int mc) {
+                int N, int q_row, int De, int Dr, int rank, int world, long long rows_per_rank) {
     pdl_enter();
     const long long b = blockIdx.x, g = (long long)rank * B + b;
     const long long h = pos[3 * b], t = pos[3 * b + 2];
     const int own_h = (int)(h / rows_per_rank), own_t = (int)(t / rows_per_rank);
-    const int fan = mc ? -1 : world;  // mc: the all-rank tables hold ONE multicast pointer each (entry 0)
+    const int fan = world;
     fan_row4(T.S, g * N, L.S + b * N, N, fan);
     fan_row4(T.GR, g * Dr, L.GR + b * Dr, Dr, fan);
-    if (early) {  // (otherwise ids and Q went ahead as copy-engine copies: KGE_EXCHANGE_EARLY)
-        fan_row4(T.Q, g * q_row, L.Q + b * q_row, q_row, fan);
-        fan_row4(T.neg, 2 * g * N, reinterpret_cast<const float*>(neg + b * N), 2 * N, fan);  // int64 ids as float pairs
-        fan_row4(T.pos, 6 * g, reinterpret_cast<const float*>(pos + 3 * b), 6, fan);
-    }
+    fan_row4(T.Q, g * q_row, L.Q + b * q_row, q_row, fan);
+    fan_row4(T.neg, 2 * g * N, reinterpret_cast<const float*>(neg + b * N), 2 * N, fan);  // int64 ids as float pairs
+    fan_row4(T.pos, 6 * g, reinterpret_cast<const float*>(pos + 3 * b), 6, fan);
     fan_row4(T.stats, 2 * g, L.stats + 2 * b, 2, fan);
     fan_row4(T.terms, 2 * g, L.terms + 2 * b, 2, fan);
     fan_row4(T.GM, g, L.GM + b, 1, fan);
@@ -126,41 +101,18 @@ exchange_kernel(PeerTable T, kge_step_buffers L, const int64_t* __restrict__ pos
 
 cudaError_t launch_exchange(const Params& P, const int64_t* pos, const int64_t* neg, int64_t B, int64_t N,
                             const kge_step_buffers& local, int rank, int world, const kge_step_buffers* peers,
-                            int64_t* const* peer_pos, int64_t* const* peer_neg, int parts, const kge_step_buffers* mcb,
-                            int64_t* mc_pos, int64_t* mc_neg, cudaStream_t st) {
+                            int64_t* const* peer_pos, int64_t* const* peer_neg, cudaStream_t st) {
     if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return cudaErrorInvalidValue;
     if (B == 0) return cudaSuccess;
-    const size_t q_row = (size_t)model_planes(P.model) * P.H;
-    if (parts == KGE_EXCHANGE_EARLY) {
-        // What is final as soon as the staging pass of the sweep has run -- the ids and Q, 58 % of the bytes of an exchange
-        // -- goes out as plain copies (contiguous B-row blocks at slot rank * B of every rank's gathered buffers): copy
-        // engines, no SM, so they run under the candidate sweep.  The own slot first, then round the ring.
-        const size_t g0 = (size_t)rank * B;
-        for (int k = 0; k < world; ++k) {
-            const int p = (rank + k) % world;
-            cudaError_t e = cudaMemcpyAsync(peers[p].Q + g0 * q_row, local.Q, (size_t)B * q_row * sizeof(float), cudaMemcpyDeviceToDevice, st);
-            if (e == cudaSuccess)
-                e = cudaMemcpyAsync(peer_neg[p] + g0 * N, neg, (size_t)B * N * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
-            if (e == cudaSuccess)
-                e = cudaMemcpyAsync(peer_pos[p] + g0 * 3, pos, (size_t)B * 3 * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
-            if (e != cudaSuccess) return e;
-        }
-        return cudaSuccess;
-    }
     PeerTable T{};
     for (int p = 0; p < world; ++p) {
         T.S[p] = peers[p].S; T.Q[p] = peers[p].Q; T.GH[p] = peers[p].GH; T.GT[p] = peers[p].GT;
         T.GR[p] = peers[p].GR; T.GM[p] = peers[p].GM; T.stats[p] = peers[p].stats; T.terms[p] = peers[p].terms;
         T.pos[p] = peer_pos[p]; T.neg[p] = peer_neg[p];
     }
-    const int mc = (mcb != nullptr && mc_pos != nullptr && mc_neg != nullptr) ? 1 : 0;
-    if (mc) {  // what goes to every rank goes through the multicast mappings; GH / GT keep their per-owner pointers
-        T.S[0] = mcb->S; T.Q[0] = mcb->Q; T.GR[0] = mcb->GR; T.GM[0] = mcb->GM; T.stats[0] = mcb->stats; T.terms[0] = mcb->terms;
-        T.pos[0] = mc_pos; T.neg[0] = mc_neg;
-    }
     const long long rows_per_rank = (P.E + world - 1) / world;  // dist.shard_range
     return launch_pdl(exchange_kernel, dim3((unsigned)B), dim3(256), 0, st, T, local, pos, neg, (int)B, (int)N,
-                      model_planes(P.model) * P.H, P.De, P.Dr, rank, world, rows_per_rank, parts == KGE_EXCHANGE_ALL ? 1 : 0, mc);
+                      model_planes(P.model) * P.H, P.De, P.Dr, rank, world, rows_per_rank);
 }
 
 }  // namespace kge

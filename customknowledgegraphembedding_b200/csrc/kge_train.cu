@@ -253,15 +253,6 @@ int kge_train_sweep(const kge_model_desc* desc, int mode, const float* entity, c
                     const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
                     const float* wsum, int64_t B_total, const kge_step_buffers* out, void* ws, size_t ws_bytes,
                     void* stream) {
-    return kge_train_sweep_staged(desc, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
-                                  loss_opts, wsum, B_total, out, ws, ws_bytes, nullptr, stream);
-}
-
-int kge_train_sweep_staged(const kge_model_desc* desc, int mode, const float* entity, const float* relation,
-                           const float* modulus, const int64_t* positive, const int64_t* negative,
-                           const float* subsampling_weight, int64_t B, int64_t N, const kge_loss_opts* loss_opts,
-                           const float* wsum, int64_t B_total, const kge_step_buffers* out, void* ws, size_t ws_bytes,
-                           void* stage_event, void* stream) {
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -276,7 +267,7 @@ int kge_train_sweep_staged(const kge_model_desc* desc, int mode, const float* en
     if (!fused_step_applicable(P, *loss_opts, B_total, N, entity, relation))
         return fail(KGE_ERR_UNSUPPORTED, "kge_train_sweep: the fused step does not apply to this configuration");
     cudaError_t e = launch_train_sweep(P, mode, entity, relation, modulus, positive, negative, subsampling_weight, B, N,
-                                       *loss_opts, wsum, B_total, *out, ws, ws_bytes, (cudaEvent_t)stage_event,
+                                       *loss_opts, wsum, B_total, *out, ws, ws_bytes,
                                        (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_sweep");
 }
@@ -287,22 +278,9 @@ int kge_train_apply(const kge_model_desc* desc, int mode, float* entity, float* 
                     const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
                     const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
                     int64_t entity_hi, float* loss3, float* reg1, void* ws, size_t ws_bytes, void* stream) {
-    return kge_train_apply_parts(desc, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
-                                 adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
-                                 loss_opts, adam_opts, gathered, entity_lo, entity_hi, KGE_APPLY_ALL, loss3, reg1, ws,
-                                 ws_bytes, stream);
-}
-
-int kge_train_apply_parts(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
-                          float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
-                          float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
-                          const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
-                          const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
-                          int64_t entity_hi, int parts, float* loss3, float* reg1, void* ws, size_t ws_bytes,
-                          void* stream) {
     return kge_train_apply_peers(desc, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                                  adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
-                                 loss_opts, adam_opts, gathered, entity_lo, entity_hi, parts, 0, nullptr, loss3, reg1, ws,
+                                 loss_opts, adam_opts, gathered, entity_lo, entity_hi, 0, nullptr, nullptr, loss3, reg1, ws,
                                  ws_bytes, stream);
 }
 
@@ -311,25 +289,10 @@ int kge_train_apply_peers(const kge_model_desc* desc, int mode, float* entity, f
                           float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
                           const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
                           const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
-                          int64_t entity_hi, int parts, int npeers, float* const* peer_entity, float* loss3, float* reg1,
-                          void* ws, size_t ws_bytes, void* stream) {
-    return kge_train_apply_multicast(desc, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
-                                     adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
-                                     loss_opts, adam_opts, gathered, entity_lo, entity_hi, parts, npeers, peer_entity, nullptr,
-                                     loss3, reg1, ws, ws_bytes, stream);
-}
-
-int kge_train_apply_multicast(const kge_model_desc* desc, int mode, float* entity, float* relation, float* modulus,
-                              float* adam_m_entity, float* adam_v_entity, float* adam_m_relation, float* adam_v_relation,
-                              float* adam_m_modulus, float* adam_v_modulus, const int64_t* positive_all,
-                              const int64_t* negative_all, int64_t B_all, int64_t N, const kge_loss_opts* loss_opts,
-                              const kge_adam_opts* adam_opts, const kge_step_buffers* gathered, int64_t entity_lo,
-                              int64_t entity_hi, int parts, int npeers, float* const* peer_entity,
-                              float* multicast_entity, float* loss3, float* reg1, void* ws, size_t ws_bytes,
-                              void* stream) {
+                          int64_t entity_hi, int npeers, float* const* peer_entity, float* multicast_entity, float* loss3,
+                          float* reg1, void* ws, size_t ws_bytes, void* stream) {
     if (npeers < 0 || npeers > 15 || (npeers > 0 && !peer_entity))
         return fail(KGE_ERR_INVALID_ARGUMENT, "npeers must be 0..15 with a pointer table");
-    if (parts <= 0 || (parts & ~KGE_APPLY_ALL)) return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be a non-empty subset of KGE_APPLY_*");
     Params P;
     int rc = check_train_args(desc, &P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                               adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all,
@@ -345,10 +308,9 @@ int kge_train_apply_multicast(const kge_model_desc* desc, int mode, float* entit
     float* small = nullptr;
     cudaError_t e = launch_train_apply(P, mode, entity, relation, modulus, adam_m_entity, adam_v_entity, adam_m_relation,
                                        adam_v_relation, adam_m_modulus, adam_v_modulus, positive_all, negative_all, B_all, N,
-                                       *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, parts, npeers, peer_entity,
+                                       *loss_opts, *adam_opts, *gathered, entity_lo, entity_hi, npeers, peer_entity,
                                        multicast_entity, ws, ws_bytes, &small, st);
     if (e != cudaSuccess) return fail_cuda(e, "kge_train_apply");
-    if (!(parts & KGE_APPLY_PREPARE)) return KGE_OK;  // the loss belongs to the piece that computes it
     if (reg1 == loss3 + 3) {
         e = cudaMemcpyAsync(loss3, small, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st);
     } else {
@@ -361,25 +323,6 @@ int kge_train_apply_multicast(const kge_model_desc* desc, int mode, float* entit
 int kge_train_exchange(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B, int64_t N,
                        const kge_step_buffers* local, int rank, int world, const kge_step_buffers* peer_gathered,
                        int64_t* const* peer_positive, int64_t* const* peer_negative, void* stream) {
-    return kge_train_exchange_parts(desc, positive, negative, B, N, local, rank, world, peer_gathered, peer_positive,
-                                    peer_negative, KGE_EXCHANGE_ALL, stream);
-}
-
-int kge_train_exchange_parts(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B,
-                             int64_t N, const kge_step_buffers* local, int rank, int world,
-                             const kge_step_buffers* peer_gathered, int64_t* const* peer_positive,
-                             int64_t* const* peer_negative, int parts, void* stream) {
-    return kge_train_exchange_multicast(desc, positive, negative, B, N, local, rank, world, peer_gathered, peer_positive,
-                                        peer_negative, parts, nullptr, nullptr, nullptr, stream);
-}
-
-int kge_train_exchange_multicast(const kge_model_desc* desc, const int64_t* positive, const int64_t* negative, int64_t B,
-                                 int64_t N, const kge_step_buffers* local, int rank, int world,
-                                 const kge_step_buffers* peer_gathered, int64_t* const* peer_positive,
-                                 int64_t* const* peer_negative, int parts, const kge_step_buffers* multicast_gathered,
-                                 int64_t* multicast_positive, int64_t* multicast_negative, void* stream) {
-    if (parts != KGE_EXCHANGE_EARLY && parts != KGE_EXCHANGE_LATE && parts != KGE_EXCHANGE_ALL)
-        return fail(KGE_ERR_INVALID_ARGUMENT, "parts must be KGE_EXCHANGE_EARLY, _LATE or _ALL");
     Params P;
     int rc = make_params(desc, &P);
     if (rc) return rc;
@@ -389,8 +332,7 @@ int kge_train_exchange_multicast(const kge_model_desc* desc, const int64_t* posi
     if (world < 1 || world > 16 || rank < 0 || rank >= world)
         return fail(KGE_ERR_INVALID_ARGUMENT, "rank %d / world %d (at most 16 peers)", rank, world);
     cudaError_t e = launch_exchange(P, positive, negative, B, N, *local, rank, world, peer_gathered, peer_positive,
-                                    peer_negative, parts, multicast_gathered, multicast_positive, multicast_negative,
-                                    (cudaStream_t)stream);
+                                    peer_negative, (cudaStream_t)stream);
     return e == cudaSuccess ? KGE_OK : fail_cuda(e, "kge_train_exchange");
 }
 

@@ -1588,15 +1588,10 @@ struct FusedCall {
     long long e_lo, e_hi;
     // per-positive buffers (sweep: written for the local batch; apply: read for the global batch)
     float *S, *Q, *GH, *GT, *GR, *GM, *stats, *terms;
-    // apply in pieces (kge_train_apply_parts): 1 = buckets + dL/ds + loss, 2 = entity rows [e_lo, e_hi), 4 = relation
-    // rows + modulus.  One piece-1 call, any number of piece-2 calls over disjoint ranges, one piece-4 call.
-    int parts = 7;
-    // kge_train_apply_rows_peers: replicas of the entity table on the other ranks
+    // kge_train_apply_peers: replicas of the entity table on the other ranks
     int npeers = 0;
     float* const* peers = nullptr;  // host array of npeers device pointers
-    float* mc = nullptr;            // multicast mapping of the entity table (kge_train_apply_multicast)
-    // kge_train_sweep_staged: recorded on the stream as soon as Q[b] of every local positive is final
-    cudaEvent_t stage_ev = nullptr;
+    float* mc = nullptr;            // NVSwitch multicast mapping of the entity table (NULL: per-peer stores)
 };
 
 template <int MODEL, int CHW, bool HEAD, int R>
@@ -1706,7 +1701,6 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
                 A.part = 1;
                 A.item_counter = ws.item_counter;
                 if ((e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 1>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A)) != cudaSuccess) return e;
-                if (fc.stage_ev != nullptr && (e = cudaEventRecord(fc.stage_ev, st)) != cudaSuccess) return e;
                 const int parts = f1w_parts(N);
                 RowsArgs R{ent, fc.neg, fc.Q, modulus, fc.S, ws.PA, ws.PM, ws.item_counter, (int)fc.B, (int)N, parts,
                            (int)((N + parts - 1) / parts), lo.negative_adversarial_sampling, lo.adversarial_temperature};
@@ -1723,7 +1717,6 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
             else
                 e = launch_pdl(train_sweep_kernel<MODEL, CH, RPI, 0, false>, dim3((unsigned)fc.B), dim3(threads), 0, st, P, kc, head, A);
             if (e != cudaSuccess) return e;
-            if (fc.stage_ev != nullptr && (e = cudaEventRecord(fc.stage_ev, st)) != cudaSuccess) return e;  // (Q is final with the kernel)
         }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if (fc.phase == 1) return cudaSuccess;
@@ -1731,7 +1724,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
     const int64_t B = fc.B_all;
     const long long BN = B * N;
     const float l3 = lo.regularization;
-    if (fc.parts & 1) {
+    {
         {
             ProfScope ps(ST_BUCKETS, st);
             // apply-only calls build the buckets of the rows [e_lo, e_hi) alone; a full step counted every use in F1
@@ -1764,7 +1757,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
         }
     }
-    if ((fc.parts & 2) && fc.e_hi > fc.e_lo) {
+    if (fc.e_hi > fc.e_lo) {
         ProfScope ps(ST_ENTITY, st);
         EntityArgs A{ent, m_ent, v_ent, fc.Q, fc.S, fc.GH, fc.GT, ws.offsets, ws.items_sorted, ws.items_b, (int)N, BN, B,
                      fc.e_lo, fc.e_hi};
@@ -1773,7 +1766,7 @@ static cudaError_t fused_launch(const Params& P, int mode, float* ent, float* re
         // wider per-thread tiles than the sweep: the per-use overhead is paid once per ECH float4 chunks
         if ((e = launch_entity<MODEL, (CH == 1) ? 2 : CH>(P, kc, head, modulus, A, X, ad, l3, st)) != cudaSuccess) return e;
     }
-    if (fc.parts & 4) {
+    {
         // relation rows and the modulus are replicated: every rank applies the same fixed-order update.  (Folding the
         // relation rows into the tail of the entity kernel was tried: the extra code slowed that kernel by more than
         // the launch it saves.)
@@ -1839,7 +1832,7 @@ cudaError_t launch_train_step_fused(const Params& P, int mode, float* ent, float
 cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, const float* rel, const float* modulus,
                                const int64_t* pos, const int64_t* neg, const float* w, int64_t B, int64_t N,
                                const kge_loss_opts& lo, const float* wsum, int64_t B_total, const kge_step_buffers& o,
-                               void* wsp, size_t ws_bytes, cudaEvent_t stage_ev, cudaStream_t st) {
+                               void* wsp, size_t ws_bytes, cudaStream_t st) {
     // the sweep alone needs a workspace only for the split (warp-per-row) variant: per-item partials + item counter
     FusedWs ws{};
     if (wsp != nullptr && ws_bytes >= train_sweep_workspace_bytes(P, B, N)) {
@@ -1853,7 +1846,6 @@ cudaError_t launch_train_sweep(const Params& P, int mode, const float* ent, cons
         return cudaErrorInvalidValue;  // InterHT keeps its inverse-norm table in the sweep workspace
     }
     FusedCall fc{1, pos, neg, w, B, wsum, B_total, nullptr, nullptr, 0, 0, 0, o.S, o.Q, o.GH, o.GT, o.GR, o.GM, o.stats, o.terms};
-    fc.stage_ev = stage_ev;
     kge_adam_opts ao{0.f, 0.9f, 0.999f, 1e-8f, 1, 0};
     return fused_dispatch(P, mode, const_cast<float*>(ent), const_cast<float*>(rel), const_cast<float*>(modulus), nullptr,
                           nullptr, nullptr, nullptr, nullptr, nullptr, fc, N, lo, adam_scalars(ao), ws, st);
@@ -1863,14 +1855,14 @@ cudaError_t launch_train_apply(const Params& P, int mode, float* ent, float* rel
                                float* v_ent, float* m_rel, float* v_rel, float* m_mod, float* v_mod,
                                const int64_t* pos_all, const int64_t* neg_all, int64_t B_all, int64_t N,
                                const kge_loss_opts& lo, const kge_adam_opts& ao, const kge_step_buffers& in, int64_t e_lo,
-                               int64_t e_hi, int parts, int npeers, float* const* peers, float* mc, void* wsp,
+                               int64_t e_hi, int npeers, float* const* peers, float* mc, void* wsp,
                                size_t ws_bytes, float** out_small, cudaStream_t st) {
     if (npeers < 0 || npeers > kMaxRowPeers) return cudaErrorInvalidValue;
     if (ws_bytes < fused_step_workspace_bytes(P, B_all, N)) return cudaErrorInvalidValue;
     const FusedWs ws = fused_carve(P, B_all, N, wsp);
     *out_small = ws.small;
     FusedCall fc{2, nullptr, nullptr, nullptr, 0, nullptr, B_all, pos_all, neg_all, B_all, e_lo, e_hi,
-                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, parts, npeers, peers};
+                 in.S, in.Q, in.GH, in.GT, in.GR, in.GM, in.stats, in.terms, npeers, peers};
     fc.mc = mc;
     return fused_dispatch(P, mode, ent, rel, modulus, m_ent, v_ent, m_rel, v_rel, m_mod, v_mod, fc, N, lo, adam_scalars(ao),
                           ws, st);

@@ -103,19 +103,11 @@ class DataParallelStep:
         self._gathered: Dict[str, torch.Tensor] = {}
         self._ws: Optional[torch.Tensor] = None
         self._shape = None
-        # pieces of the owned row range whose broadcast overlaps the next piece's update (1 = apply, then broadcast)
-        self.overlap_chunks = int(os.environ.get("KGE_DP_OVERLAP_CHUNKS", "1"))
         # per-positive buffers exchanged by peer stores (symmetric memory) instead of an NCCL all-gather
         self.peer_exchange = os.environ.get("KGE_DP_PEER_EXCHANGE", "1") != "0"
         self._peer = None
         self._rows_peer = None  # entity table in symmetric memory: updated rows are stored into the other replicas
         self._wsum_ahead = {}   # id(staged batch) -> all-reduced weight sum queued one step early
-        # ids and Q exchanged by copy engines while the candidate sweep runs (kge_train_exchange_parts).  Measured SLOWER
-        # than the one-kernel exchange (2 GPUs 0.669 vs 0.652 ms, 8 GPUs 1.004 vs 0.912 ms per step: 3 * G small peer
-        # copies on one copy-engine stream do not reach the rate of SM stores, and the event between the staging pass and
-        # the rows kernel undoes their programmatic overlap) -- off by default, kept for larger batches / tables.
-        self.early_exchange = os.environ.get("KGE_DP_EARLY_EXCHANGE", "0") != "0"
-        self._early_state = None
 
     # ---- buffers -----------------------------------------------------------------------------------
     def _row_sizes(self, N):
@@ -186,17 +178,7 @@ class DataParallelStep:
         tables = (StepBuffers * G)(*[StepBuffers(*[C.c_void_p(b + offsets[k]) for k in _BUFFERS]) for b in bases])
         pos_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["pos"]) for b in bases])
         neg_ptrs = (C.c_void_p * G)(*[C.c_void_p(b + offsets["neg"]) for b in bases])
-        out = {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs, "mc": None}
-        # NVSwitch multicast mapping of the block: what goes to every rank leaves as one multimem.st per chunk
-        mc = int(getattr(hdl, "multicast_ptr", 0) or 0) if os.environ.get("KGE_DP_MULTICAST", "1") != "0" else 0
-        # Measured SLOWER than the per-rank stores for the exchange (2 GPUs 0.637 vs 0.623 ms, 4 GPUs 0.703 vs 0.691): the
-        # exchange is bound by what ARRIVES at a rank (the same bytes either way) and the own copy takes the trip through
-        # the switch too -- unlike the row stores of the entity kernel, where the SM-side cost of 7 remote stores per chunk
-        # was the problem.  Off unless KGE_DP_MULTICAST_EXCHANGE=1.
-        if mc and os.environ.get("KGE_DP_MULTICAST_EXCHANGE", "0") == "1":
-            out["mc"] = (StepBuffers(*[C.c_void_p(mc + offsets[k]) for k in _BUFFERS]), C.c_void_p(mc + offsets["pos"]),
-                         C.c_void_p(mc + offsets["neg"]))
-        return out
+        return {"hdl": hdl, "block": block, "tables": tables, "pos": pos_ptrs, "neg": neg_ptrs}
 
     def _peer_table(self):
         """Move the (replicated) entity table into symmetric memory, once: every rank can then store the rows it
@@ -214,43 +196,27 @@ class DataParallelStep:
         return {"hdl": hdl, "block": block, "ptrs": (C.c_void_p * len(others))(*[C.c_void_p(b) for b in others]),
                 "mc": C.c_void_p(mc) if mc else None}
 
-    def _exchange(self, pos, neg, parts=_lib.EXCHANGE_ALL, stream=None):
-        """kge_train_exchange(_parts) on the current stream (or ``stream``); the caller follows it with the barrier that
-        orders every rank's apply after every rank's stores."""
+    def _exchange(self, pos, neg):
+        """kge_train_exchange on the current stream; the caller follows it with the barrier that orders every rank's
+        apply after every rank's stores."""
         B, N = neg.shape
         local = self._bufs("local")
         with _on(pos.device):
-            mc = self._peer["mc"]
-            _lib.check(_lib.load().kge_train_exchange_multicast(
+            _lib.check(_lib.load().kge_train_exchange(
                 C.byref(self.model._desc()), ops._ptr(pos), ops._ptr(neg), B, N, C.byref(local), self.rank, self.world,
-                self._peer["tables"], self._peer["pos"], self._peer["neg"], int(parts),
-                None if mc is None else C.byref(mc[0]), None if mc is None else mc[1], None if mc is None else mc[2],
-                ops._stream() if stream is None else stream), "kge_train_exchange")
-
-    def _early(self, dev):
-        """Side stream + the two events of the early exchange (ids and Q as copy-engine copies under the sweep)."""
-        if self._early_state is None:
-            side = torch.cuda.Stream(dev)
-            ev_stage, ev_done = torch.cuda.Event(), torch.cuda.Event()
-            ev_stage.record(side)  # (creates the raw handles)
-            ev_done.record(side)
-            self._early_state = {"side": side, "side_ptr": C.c_void_p(side.cuda_stream), "ev_stage": ev_stage,
-                                 "ev_stage_ptr": C.c_void_p(ev_stage.cuda_event), "ev_done": ev_done,
-                                 "ev_done_ptr": C.c_void_p(ev_done.cuda_event)}
-        return self._early_state
+                self._peer["tables"], self._peer["pos"], self._peer["neg"], ops._stream()), "kge_train_exchange")
 
     # ---- the two kernel calls (overridable: tests/test_dist_cpu.py) ------------------------------------
-    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts, stage_event=None):
+    def _sweep(self, mode, pos, neg, w, wsum, B_total, loss_opts):
         m = self.model
         B, N = neg.shape
         bufs = self._bufs("local")
         sws = self._sweep_ws(m._desc(), B, N, pos.device)
         with _on(pos.device):
-            _lib.check(_lib.load().kge_train_sweep_staged(
+            _lib.check(_lib.load().kge_train_sweep(
                 C.byref(m._desc()), ops.mode_id(mode), ops._ptr(m.entity_embedding), ops._ptr(m.relation_embedding),
                 ops._ptr(m._modulus()), ops._ptr(pos), ops._ptr(neg), ops._ptr(w), B, N, C.byref(loss_opts),
-                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), stage_event, ops._stream()),
-                "kge_train_sweep")
+                ops._ptr(wsum), B_total, C.byref(bufs), ops._ptr(sws), sws.numel(), ops._stream()), "kge_train_sweep")
 
     def _sweep_ws(self, desc, B, N, dev):
         """Workspace of the split (warp-per-row) sweep: per-item partial dL/dq + item counter."""
@@ -261,10 +227,9 @@ class DataParallelStep:
             self._sws = ws
         return ws
 
-    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None,
-               row_peers=None, multicast=None):
-        """kge_train_apply_peers on the rows ``[lo, hi)`` (default: everything this rank owns, all parts);
-        ``row_peers``: ctypes array of the other ranks' table pointers -- updated rows are stored there too."""
+    def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, row_peers=None, multicast=None):
+        """kge_train_apply_peers on the rows this rank owns; ``row_peers``: ctypes array of the other ranks' table
+        pointers / ``multicast``: the NVSwitch multicast mapping of the table -- updated rows are stored there too."""
         m, opt = self.model, self.optimizer
         B_all, N = neg_all.shape
         ent, rel, mod = m.entity_embedding, m.relation_embedding, m._modulus()
@@ -277,43 +242,13 @@ class DataParallelStep:
         bufs = self._bufs("gathered")
         P = ops._ptr
         with _on(ent.device):
-            _lib.check(_lib.load().kge_train_apply_multicast(
+            _lib.check(_lib.load().kge_train_apply_peers(
                 C.byref(desc), ops.mode_id(mode), P(ent), P(rel), P(mod), P(st_e["exp_avg"]), P(st_e["exp_avg_sq"]),
                 P(st_r["exp_avg"]), P(st_r["exp_avg_sq"]), P(st_m["exp_avg"]) if st_m else None,
                 P(st_m["exp_avg_sq"]) if st_m else None, P(pos_all), P(neg_all), B_all, N, C.byref(loss_opts),
-                C.byref(adam), C.byref(bufs), self.lo if lo is None else lo, self.hi if hi is None else hi, int(parts),
-                0 if row_peers is None else len(row_peers), row_peers, multicast, P(out),
-                C.c_void_p(out.data_ptr() + 12), P(self._ws), self._ws.numel(), ops._stream()), "kge_train_apply_peers")
-
-    def _apply_overlapped(self, mode, pos_all, neg_all, loss_opts, adam, out):
-        """Owner-parallel apply with the broadcast of the updated rows hidden behind it: the owned range is cut into
-        ``overlap_chunks`` pieces; as soon as the kernel of piece c is queued, every rank's piece c is broadcast
-        asynchronously (NCCL's stream waits for the kernels queued so far, ours goes on with piece c + 1)."""
-        K, world, E = self.overlap_chunks, self.world, self.model.nentity
-        ent = self.model.entity_embedding.data
-
-        def piece(r, c):
-            lo, hi = shard_range(E, r, world)
-            n = hi - lo
-            return lo + (n * c) // K, lo + (n * (c + 1)) // K
-
-        self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_PREPARE)
-        pending = []
-        for c in range(K):
-            lo, hi = piece(self.rank, c)
-            if hi > lo:
-                self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ROWS, lo=lo, hi=hi)
-            with _coalesced(self.group, ent.device, async_ops=True) as cm:
-                for r in range(world):
-                    rlo, rhi = piece(r, c)
-                    if rhi > rlo:
-                        src = dist.get_global_rank(self.group, r) if self.group is not None else r
-                        dist.broadcast(ent[rlo:rhi], src=src, group=self.group)
-            pending.append(cm)
-        self._apply(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_FINISH)
-        for cm in pending:
-            if cm is not None:
-                cm.wait()  # the current stream waits for the broadcasts: the next sweep reads every row
+                C.byref(adam), C.byref(bufs), self.lo, self.hi, 0 if row_peers is None else len(row_peers), row_peers,
+                multicast, P(out), C.c_void_p(out.data_ptr() + 12), P(self._ws), self._ws.numel(), ops._stream()),
+                "kge_train_apply_peers")
 
     # ---- one global step -----------------------------------------------------------------------------
     def train_step(self, train_iterator, args, sync: bool = True):
@@ -356,20 +291,7 @@ class DataParallelStep:
             wsum = w.sum().reshape(1)
             if self.world > 1:
                 dist.all_reduce(wsum, op=dist.ReduceOp.SUM, group=self.group)
-        plain_sweep = type(self)._sweep is DataParallelStep._sweep
-        if self.world > 1 and self._peer is not None and self.early_exchange and plain_sweep:
-            # ids and Q leave on a side stream (copy engines) as soon as the staging pass has run, under the candidate
-            # sweep; the kernel sends the rest after the sweep; the barrier is ordered after both
-            lib, es, main = _lib.load(), self._early(dev), ops._stream()
-            self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts, stage_event=es["ev_stage_ptr"])
-            _lib.check(lib.kge_stream_wait_event(es["side_ptr"], es["ev_stage_ptr"]), "kge_stream_wait_event")
-            self._exchange(pos, neg, _lib.EXCHANGE_EARLY, stream=es["side_ptr"])
-            es["ev_done"].record(es["side"])
-            self._exchange(pos, neg, _lib.EXCHANGE_LATE)
-            _lib.check(lib.kge_stream_wait_event(main, es["ev_done_ptr"]), "kge_stream_wait_event")
-            self._peer["hdl"].barrier()
-            pos_all, neg_all = self._gathered["pos"], self._gathered["neg"]
-        elif self.world > 1 and self._peer is not None:
+        if self.world > 1 and self._peer is not None:
             self._sweep(mode, pos, neg, w, wsum, self.world * B, loss_opts)
             self._exchange(pos, neg)  # peer stores over NVLink: GH / GT rows go to their owners only
             self._peer["hdl"].barrier()
@@ -401,8 +323,6 @@ class DataParallelStep:
             self._apply(mode, pos_all, neg_all, loss_opts, adam, out, row_peers=self._rows_peer["ptrs"],
                         multicast=self._rows_peer["mc"])
             self._rows_peer["hdl"].barrier()
-        elif self.world > 1 and self.overlap_chunks > 1 and dev.type == "cuda" and plain:
-            self._apply_overlapped(mode, pos_all, neg_all, loss_opts, adam, out)
         else:
             self._apply(mode, pos_all, neg_all, loss_opts, adam, out)
             self._share_rows()

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 11
+#define KGE_B200_ABI_VERSION 12
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -308,52 +308,24 @@ KGE_API int kge_train_apply(const kge_model_desc *desc, int mode, float *entity,
                             const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, float *loss3,
                             float *reg1, void *ws, size_t ws_bytes, void *stream);
 
-/* kge_train_apply in pieces, so that the caller can put communication between them (dist.DataParallelStep broadcasts
- * the rows of one chunk while the next chunk is being updated).  `parts` is a subset of:
- *   KGE_APPLY_PREPARE  bucket build for the rows [entity_lo, entity_hi) (must cover every later ROWS range),
- *                      loss3 / reg1 (exactly once, first);
- *   KGE_APPLY_ROWS     gradient gather + Adam for the entity rows [entity_lo, entity_hi) (any number of calls over
- *                      disjoint ranges; needs the workspace PREPARE left behind);
- *   KGE_APPLY_FINISH   relation rows + pRotatE modulus (exactly once, after the last ROWS call: pRotatE's entity
- *                      gradient reads the modulus of the step's start).
- * kge_train_apply == parts = KGE_APPLY_ALL.  Replaces the same `apply_gradients` as kge_train_apply (supervisor.py:26). */
-enum { KGE_APPLY_PREPARE = 1, KGE_APPLY_ROWS = 2, KGE_APPLY_FINISH = 4, KGE_APPLY_ALL = 7 };
-KGE_API int kge_train_apply_parts(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
-                                  float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
-                                  float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus,
-                                  const int64_t *positive_all, const int64_t *negative_all, int64_t B_all, int64_t N,
-                                  const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
-                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
-                                  float *loss3, float *reg1, void *ws, size_t ws_bytes, void *stream);
-
-/* kge_train_apply_parts that ALSO stores every updated entity row into `npeers` replicas of the table on other GPUs
- * (`peer_entity`: HOST array of device pointers to the peers' tables, peer mappings valid on this GPU): the broadcast of
- * the owned rows that has to follow kge_train_apply under data parallelism rides on the Adam epilogue as NVLink
- * stores.  The caller puts a barrier across the ranks on the stream before anything reads the replicas.  With a
- * non-zero `regularization` the L3 sum of PREPARE reads the whole local table, so the caller must keep the ranks from
- * writing into it before every rank's PREPARE is done (dist.DataParallelStep falls back to a broadcast then). */
+/* kge_train_apply that ALSO stores every updated entity row into the replicas of the table on the other GPUs, so that the
+ * broadcast of the owned rows that has to follow kge_train_apply under data parallelism rides on the Adam epilogue:
+ *   multicast_entity != NULL: ONE NVSwitch multicast mapping of the table (the multicast address of the symmetric-memory
+ *     block that holds it on every rank): every 16-byte chunk of an updated row leaves the SM as one `multimem.st`, the
+ *     switch replicates it to all ranks, the local replica included (`npeers` / `peer_entity` are ignored);
+ *   else `peer_entity`: HOST array of `npeers` (<= 15) device pointers to the peers' tables (peer mappings valid on this
+ *     GPU): one NVLink store per peer and chunk.
+ * The caller puts a barrier across the ranks on the stream before anything reads the replicas.  With a non-zero
+ * `regularization` the L3 sum reads the whole local table while peers would be writing it: use kge_train_apply and a
+ * broadcast then (dist.DataParallelStep does). */
 KGE_API int kge_train_apply_peers(const kge_model_desc *desc, int mode, float *entity, float *relation, float *modulus,
                                   float *adam_m_entity, float *adam_v_entity, float *adam_m_relation,
                                   float *adam_v_relation, float *adam_m_modulus, float *adam_v_modulus,
                                   const int64_t *positive_all, const int64_t *negative_all, int64_t B_all, int64_t N,
                                   const kge_loss_opts *loss_opts, const kge_adam_opts *adam_opts,
-                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int parts,
-                                  int npeers, float *const *peer_entity, float *loss3, float *reg1, void *ws,
-                                  size_t ws_bytes, void *stream);
-
-/* kge_train_apply_peers with the replicas reached through ONE NVSwitch multicast mapping of the table instead of a
- * pointer per peer (`multicast_entity`: the multicast address of the symmetric-memory block that holds the table on
- * every rank; NULL = per-peer stores): every 16-byte chunk of an updated row leaves the SM as one `multimem.st`, the
- * switch replicates it to all ranks (the local replica included).  `npeers` / `peer_entity` are ignored when it is set. */
-KGE_API int kge_train_apply_multicast(const kge_model_desc *desc, int mode, float *entity, float *relation,
-                                      float *modulus, float *adam_m_entity, float *adam_v_entity,
-                                      float *adam_m_relation, float *adam_v_relation, float *adam_m_modulus,
-                                      float *adam_v_modulus, const int64_t *positive_all, const int64_t *negative_all,
-                                      int64_t B_all, int64_t N, const kge_loss_opts *loss_opts,
-                                      const kge_adam_opts *adam_opts, const kge_step_buffers *gathered,
-                                      int64_t entity_lo, int64_t entity_hi, int parts, int npeers,
-                                      float *const *peer_entity, float *multicast_entity, float *loss3, float *reg1,
-                                      void *ws, size_t ws_bytes, void *stream);
+                                  const kge_step_buffers *gathered, int64_t entity_lo, int64_t entity_hi, int npeers,
+                                  float *const *peer_entity, float *multicast_entity, float *loss3, float *reg1,
+                                  void *ws, size_t ws_bytes, void *stream);
 
 /*
  * Between kge_train_sweep and kge_train_apply: the exchange of the per-positive buffers over NVLink peer memory,
@@ -368,40 +340,6 @@ KGE_API int kge_train_exchange(const kge_model_desc *desc, const int64_t *positi
                                int64_t N, const kge_step_buffers *local, int rank, int world,
                                const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
                                int64_t *const *peer_negative, void *stream);
-
-/* The exchange in two pieces, so that the larger one hides behind the candidate sweep:
- *   KGE_EXCHANGE_EARLY  ids and Q -- final as soon as the staging pass of the sweep has run (the event of
- *                       kge_train_sweep_staged) -- as plain device-to-device copies of contiguous B-row blocks: copy
- *                       engines, no SM; the caller issues them on a side stream that waits for that event;
- *   KGE_EXCHANGE_LATE   S, GR, GM, stats, terms to every rank and GH / GT to their owners (the kernel), after the sweep;
- *   KGE_EXCHANGE_ALL    == kge_train_exchange.
- * The barrier before kge_train_apply has to be ordered after both pieces. */
-enum { KGE_EXCHANGE_EARLY = 1, KGE_EXCHANGE_LATE = 2, KGE_EXCHANGE_ALL = 3 };
-KGE_API int kge_train_exchange_parts(const kge_model_desc *desc, const int64_t *positive, const int64_t *negative,
-                                     int64_t B, int64_t N, const kge_step_buffers *local, int rank, int world,
-                                     const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
-                                     int64_t *const *peer_negative, int parts, void *stream);
-
-/* kge_train_exchange_parts with everything that goes to EVERY rank (ids, S, Q, GR, GM, stats, terms) sent through the
- * NVSwitch multicast mappings of the gathered buffers (`multicast_gathered`, `multicast_positive`, `multicast_negative`:
- * multicast addresses of the same symmetric-memory block the peer pointers address; all NULL = per-rank stores): one
- * `multimem.st` per 16-byte chunk instead of `world` stores.  GH / GT rows still go to their owners through
- * `peer_gathered`. */
-KGE_API int kge_train_exchange_multicast(const kge_model_desc *desc, const int64_t *positive, const int64_t *negative,
-                                         int64_t B, int64_t N, const kge_step_buffers *local, int rank, int world,
-                                         const kge_step_buffers *peer_gathered, int64_t *const *peer_positive,
-                                         int64_t *const *peer_negative, int parts,
-                                         const kge_step_buffers *multicast_gathered, int64_t *multicast_positive,
-                                         int64_t *multicast_negative, void *stream);
-
-/* kge_train_sweep that records `stage_event` (a cudaEvent_t, may be NULL) on `stream` as soon as Q[b] of every local
- * positive is final: after the staging pass of the split sweep, after the whole kernel for the row-group variant. */
-KGE_API int kge_train_sweep_staged(const kge_model_desc *desc, int mode, const float *entity, const float *relation,
-                                   const float *modulus, const int64_t *positive, const int64_t *negative,
-                                   const float *subsampling_weight, int64_t B, int64_t N,
-                                   const kge_loss_opts *loss_opts, const float *wsum, int64_t B_total,
-                                   const kge_step_buffers *out, void *ws, size_t ws_bytes, void *stage_event,
-                                   void *stream);
 
 /*
  * kge_train_apply over a ROW-SHARDED entity table: `entity_shard`, `adam_m_shard`, `adam_v_shard` hold only the rows

@@ -174,60 +174,9 @@ def test_emulated_ranks_equal_plain_step(name, world, kernels=False):
                 assert torch.equal(s.modulus, ref.modulus)
 
 
-@pytest.mark.parametrize("name", ["RotatE", "pRotatE", "InterHT", "ComplEx"])
-def test_apply_in_pieces_equals_one_apply(name):
-    """kge_train_apply_parts: PREPARE, the owned rows in three ROWS calls, FINISH == kge_train_apply, bit for bit
-    (pRotatE: the entity gradient must see the modulus of the step's start, so FINISH comes last)."""
-    import customknowledgegraphembedding_b200 as kb
-    from customknowledgegraphembedding_b200 import _lib, dist as kd
-    E, R, H, B, N, lr = 157, 4, 32, 10, 21, 1e-3
-    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
-    ref, cut = _model(name, E, R, H, seed=9), _model(name, E, R, H, seed=9)
-    ref_opt, cut_opt = _adam(ref, lr), _adam(cut, lr)
-
-    class Pieces(kd.DataParallelStep):
-        def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ALL, lo=None, hi=None):
-            base = super()._apply
-            base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_PREPARE)
-            for a, b in ((0, 50), (50, 51), (51, E)):
-                base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_ROWS, lo=a, hi=b)
-            base(mode, pos_all, neg_all, loss_opts, adam, out, parts=_lib.APPLY_FINISH)
-
-    step = Pieces(cut, cut_opt)
-    for s in range(3):
-        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=20 + s)
-        batch = (pos.cuda(), neg.cuda(), w.cuda(), mode)
-        want = kb.KGEModel.train_step(ref, ref_opt, iter([batch]), args)
-        got = step.train_step(iter([batch]), args)
-        assert got["loss"] == want["loss"], (s, got, want)
-        assert torch.equal(cut.entity_embedding, ref.entity_embedding), s
-        assert torch.equal(cut.relation_embedding, ref.relation_embedding), s
-        if name == "pRotatE":
-            assert torch.equal(cut.modulus, ref.modulus), s
-
-
-def test_apply_parts_argument_checks():
-    from customknowledgegraphembedding_b200 import _lib, dist as kd
-    E, R, H, B, N = 40, 3, 16, 4, 6
-    m = _model("RotatE", E, R, H, seed=1)
-    step = kd.DataParallelStep(m, _adam(m, 1e-3))
-    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
-    pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=3)
-    step.train_step(iter([(pos.cuda(), neg.cuda(), w.cuda(), mode)]), args)  # builds the buffers
-    from customknowledgegraphembedding_b200._lib import AdamOpts, LossOpts
-    out = torch.zeros(4, device="cuda")
-    for bad in (0, 8, -1):
-        with pytest.raises(ValueError):
-            step._apply(mode, pos.cuda(), neg.cuda(), LossOpts(1, 0, 1, 0, 1.0, 0.0), AdamOpts(1e-3, 0.9, 0.999, 1e-8, 2, 0),
-                        out, parts=bad)
-
-
-@pytest.mark.parametrize("pieces", [False, True])
 @pytest.mark.parametrize("world", [1, 2, 3])
-def test_peer_exchange_places_every_row_where_it_is_needed(world, pieces):
-    """``pieces``: kge_train_exchange_parts EARLY (ids + Q as copies, on a side stream) + LATE (the kernel) instead of
-    the one-kernel exchange -- the same bytes land in the same places.
-    kge_train_exchange with the ranks emulated on one GPU (every "peer" block is a plain tensor here; over real
+def test_peer_exchange_places_every_row_where_it_is_needed(world):
+    """kge_train_exchange with the ranks emulated on one GPU (every "peer" block is a plain tensor here; over real
     ranks the same pointers come from symmetric memory -- scratch/dist_check.py): ids, S, Q, GR and the scalars land
     in every rank's gathered buffers at slot rank * B + b; GH / GT rows only at the owner of the head / tail."""
     import ctypes as C
@@ -252,18 +201,8 @@ def test_peer_exchange_places_every_row_where_it_is_needed(world, pieces):
     lib = _lib.load()
     for r in range(world):
         loc = StepBuffers(*[C.c_void_p(local[r][k].data_ptr()) for k in names])
-        if pieces:
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            _lib.check(lib.kge_train_exchange_parts(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r,
-                                                    world, tables, ppos, pneg, _lib.EXCHANGE_EARLY,
-                                                    C.c_void_p(side.cuda_stream)), "kge_train_exchange_parts")
-            _lib.check(lib.kge_train_exchange_parts(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r,
-                                                    world, tables, ppos, pneg, _lib.EXCHANGE_LATE, ops._stream()),
-                       "kge_train_exchange_parts")
-        else:
-            _lib.check(lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r, world,
-                                              tables, ppos, pneg, ops._stream()), "kge_train_exchange")
+        _lib.check(lib.kge_train_exchange(C.byref(m._desc()), ops._ptr(pos[r]), ops._ptr(neg[r]), B, N, C.byref(loc), r, world,
+                                          tables, ppos, pneg, ops._stream()), "kge_train_exchange")
     torch.cuda.synchronize()
     rows = (E + world - 1) // world
     for p in range(world):
@@ -299,9 +238,10 @@ def test_updated_rows_are_stored_into_the_replicas():
     class Peers(kd.DataParallelStep):
         def _apply(self, mode, pos_all, neg_all, loss_opts, adam, out, **kw):
             ptrs = (C.c_void_p * 2)(*[C.c_void_p(r.data_ptr()) for r in replicas])
-            super()._apply(mode, pos_all, neg_all, loss_opts, adam, out, lo=lo, hi=hi, row_peers=ptrs)
+            super()._apply(mode, pos_all, neg_all, loss_opts, adam, out, row_peers=ptrs)
 
     step = Peers(m, _adam(m, lr))
+    step.lo, step.hi = lo, hi  # the rows this "rank" owns
     pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=8)
     step.train_step(iter([(pos.cuda(), neg.cuda(), w.cuda(), mode)]), args)
     now = m.entity_embedding.detach()
