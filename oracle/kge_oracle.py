@@ -8,6 +8,7 @@ Every function cites the reference lines it restates.  ``/root/reference`` paths
 * ``tensorflow_codes/model.py:49-112``   ``TFKGEModel.__init__``  (dims, init range)
 * ``tensorflow_codes/model.py:114-205``  ``TFKGEModel.call``  (modes 0/1/3, fused terms)
 * ``tensorflow_codes/model.py:207-224``  ``InterHT``
+* ``tensorflow_codes/model.py:96-106,226-235`` ``TranSparse`` (``OracleTranSparse``)
 * ``tensorflow_codes/supervisor.py:13-30`` ``Trainer.train_step``
 * SURVEY.md section 8(a) rows U1-U11 -- the absent PyTorch submodule
   (``KnowledgeGraphEmbedding`` @ 2e440e0f, "parity unpinned").
@@ -195,6 +196,60 @@ class OracleKGEModel(nn.Module):
         b_tail = b_tail + self.u                                 # model.py:220
         score = a_head * b_tail - a_tail * b_head + re_mid      # model.py:222
         return self.gamma.item() - score.abs().sum(dim=2)       # model.py:223 (tf.norm ord=1)
+
+
+class OracleTranSparse(nn.Module):
+    """``TFKGEModel('TranSparse', ...)`` (``tensorflow_codes/model.py:96-106`` variables, ``:139-142,161-164,187-190``
+    gathers, ``:226-235`` score): per-relation projection ``W [R, D, D]`` under a fixed 0/1 ``mask``.
+
+    ``project_tail=False`` is the reference AS WRITTEN: ``:229`` projects ``head`` a second time, so ``p_tail`` is
+    ``p_head`` and the tail entity is never read -- the score is ``gamma - sum_j |p_j| * |r_j - 1|`` with ``p`` the
+    normalised projected head and ``r`` the normalised relation row; in tail-batch mode the result is ``[B, 1]``
+    (the head side has one row per positive).  ``project_tail=True`` projects the tail (what ``:229`` evidently meant).
+    ``mask`` follows ``:97-103`` in distribution only (0/1 with rate 0.5, drawn here with torch's generator): tests
+    copy the tensor they compare on, as the Checker does for every variable."""
+
+    def __init__(self, nentity, nrelation, hidden_dim, gamma, project_tail=False, dtype=torch.float32):
+        super().__init__()
+        self.model_name = "TranSparse"
+        self.nentity, self.nrelation, self.hidden_dim = nentity, nrelation, hidden_dim
+        self.entity_dim = self.relation_dim = hidden_dim
+        self.epsilon = 2.0
+        self.project_tail = bool(project_tail)
+        self.gamma = nn.Parameter(torch.tensor([gamma], dtype=torch.float32), requires_grad=False)
+        rng = (float(gamma) + self.epsilon) / hidden_dim
+        self.embedding_range = nn.Parameter(torch.tensor([rng], dtype=torch.float32), requires_grad=False)
+        self.entity_embedding = nn.Parameter(torch.empty(nentity, hidden_dim, dtype=dtype).uniform_(-rng, rng))
+        self.relation_embedding = nn.Parameter(torch.empty(nrelation, hidden_dim, dtype=dtype).uniform_(-rng, rng))
+        self.W = nn.Parameter(torch.empty(nrelation, hidden_dim, hidden_dim, dtype=dtype).uniform_(-rng, rng))
+        prob = torch.empty(nrelation, hidden_dim, hidden_dim).uniform_(1, 100)           # model.py:101
+        self.register_buffer("mask", (prob >= 50).to(dtype))                            # model.py:99-103
+
+    gather = OracleKGEModel.gather
+
+    @staticmethod
+    def _l2_normalize(x):
+        return x / torch.sqrt((x * x).sum(dim=-1, keepdim=True))                         # tf.linalg.normalize(ord=2)
+
+    def forward(self, sample, mode="single"):
+        head, relation, tail = self.gather(sample, mode)
+        rel_ids = (sample if mode == "single" else sample[0])[:, 1]
+        m = self.mask[rel_ids] * self.W[rel_ids]                                          # model.py:139-141, 227
+        p_head = self._l2_normalize(torch.matmul(head, m))                                # model.py:227-228
+        p_tail = self._l2_normalize(torch.matmul(tail if self.project_tail else head, m))  # model.py:229-230
+        relation = self._l2_normalize(relation)                                           # model.py:231
+        score = p_head * relation - p_tail                                                # model.py:233
+        return self.gamma.item() - score.abs().sum(dim=2)                                 # model.py:234
+
+
+def transparse_to_double(model: "OracleTranSparse") -> "OracleTranSparse":
+    twin = OracleTranSparse(model.nentity, model.nrelation, model.hidden_dim, model.gamma.item(),
+                            model.project_tail, dtype=torch.float64)
+    with torch.no_grad():
+        for k in ("entity_embedding", "relation_embedding", "W"):
+            getattr(twin, k).copy_(getattr(model, k).double())
+        twin.mask.copy_(model.mask.double())
+    return twin
 
 
 # ------------------------------------------------------------------------------------------
@@ -444,6 +499,8 @@ def tf_train_step(model: OracleKGEModel, optimizer: KerasAdam, batch):
     """supervisor.py:15-28 for one replica."""
     positive_sample, negative_sample, subsampling_weight, mode = batch
     params = [model.entity_embedding, model.relation_embedding]
+    if hasattr(model, "W"):
+        params.append(model.W)  # TranSparse: model.py:105 (trainable); the mask is not (model.py:103)
     loss = tf_train_loss(model, positive_sample, negative_sample, subsampling_weight, mode)
     grads = torch.autograd.grad(loss, params)
     optimizer.apply_gradients(zip(grads, params))

@@ -16,6 +16,9 @@ with ``import tensorflow`` resolved to the torch-backed shim.  What is recorded:
                          fused ``call`` outputs for modes 0 / 1 / 3 (model.py:114-224).
 ``ref_tf_trainstep.npz`` 3 consecutive ``Trainer.train_step`` calls (supervisor.py:13-30) with the
                          Keras-Adam shim: per-step loss and the tables after each step.
+``ref_tf_transparse.npz`` the same three things for ``TFKGEModel('TranSparse', ...)`` (model.py:96-106,226-235):
+                         variables incl. ``W`` and the 0/1 ``mask``, raw scores of the three gathers, ``call`` outputs,
+                         3 ``Trainer.train_step`` calls (entity / relation / W after each).
 ``ref_tf_loss.npz``      the eager ``loss()`` (model.py:4-44) evaluated on recorded score matrices for
                          adv / non-adv x uni / subsampling x reg / no-reg.
 
@@ -121,6 +124,53 @@ def golden_trainstep(ref_model, ref_sup, tf):
     return out
 
 
+def golden_transparse(ref_model, ref_sup, tf):
+    E, R, H, B, N, gamma, lr = 61, 5, 22, 6, 9, 12.0, 1e-2
+    torch.manual_seed(2468)
+    m = ref_model.TFKGEModel("TranSparse", E, R, H, gamma)
+    pos, neg, w = _batch(E, R, B, N, 11)
+    out = {"E": E, "R": R, "H": H, "gamma": gamma, "lr": lr,
+           "entity_embedding": m.entity_embedding.numpy().copy(),
+           "relation_embedding": m.relation_embedding.numpy().copy(),
+           "W": m.W.numpy().copy(), "mask": m.mask.numpy().copy(),
+           "positive_sample": pos.numpy(), "negative_sample": neg.numpy()}
+    ent, rel = m.entity_embedding, m.relation_embedding
+    h1 = tf.expand_dims(tf.gather(ent, pos[:, 0]), 1)
+    r1 = tf.expand_dims(tf.gather(rel, pos[:, 1]), 1)
+    t1 = tf.expand_dims(tf.gather(ent, pos[:, 2]), 1)
+    hN = tf.reshape(tf.gather(ent, tf.reshape(neg, [-1])), [B, N, -1])
+    tN = tf.reshape(tf.gather(ent, tf.reshape(neg, [-1])), [B, N, -1])
+    bW, bM = tf.gather(m.W, pos[:, 1]), tf.gather(m.mask, pos[:, 1])
+    out["score_single"] = m.TranSparse(h1, r1, t1, 3, bW, bM).numpy()
+    out["score_head_batch"] = m.TranSparse(hN, r1, t1, 0, bW, bM).numpy()
+    out["score_tail_batch"] = m.TranSparse(h1, r1, tN, 1, bW, bM).numpy()   # [B, 1]: model.py:229 never reads tN
+    for mode in (0, 1, 3):
+        out["call_mode%d" % mode] = m(((pos, neg), torch.tensor(mode))).numpy()
+    # three train steps (supervisor.py:13-30) on the same model
+    opt = tf.keras.optimizers.Adam(learning_rate=lr)
+    metric = tf.keras.metrics.Sum("training_loss")
+    batches = []
+    for step in range(3):
+        p, n, sw = _batch(E, R, B, N, 200 + step)
+        batches.append((p, n, sw, torch.full((B,), (step + 1) % 2, dtype=torch.int64)))
+    trainer = ref_sup.Trainer(tf.distribute.get_strategy(), batches, m, opt, metric)
+    it = iter(batches)
+    for step in range(3):
+        p, n, sw, mode = batches[step]
+        metric.reset_states()
+        trainer.train_step(it)
+        out["positive_sample_%d" % step] = p.numpy()
+        out["negative_sample_%d" % step] = n.numpy()
+        out["subsampling_weight_%d" % step] = sw.numpy()
+        out["mode_%d" % step] = mode.numpy()
+        out["loss_%d" % step] = np.float32(metric.result())
+        out["entity_embedding_%d" % (step + 1)] = m.entity_embedding.numpy().copy()
+        out["relation_embedding_%d" % (step + 1)] = m.relation_embedding.numpy().copy()
+        out["W_%d" % (step + 1)] = m.W.numpy().copy()
+    np.savez_compressed(os.path.join(GOLDEN, "ref_tf_transparse.npz"), **out)
+    return out
+
+
 class _ScoreTable:
     """Callable with the PyTorch ``model(sample, mode=...)`` signature the eager ``loss()`` expects
     (model.py:11,20), answering from recorded score matrices."""
@@ -169,6 +219,8 @@ def main():
     a = golden_interht(ref_model, tf)
     b = golden_trainstep(ref_model, ref_sup, tf)
     c = golden_loss(ref_model, tf)
+    d = golden_transparse(ref_model, ref_sup, tf)
+    print("ref_tf_transparse: call_mode0", d["call_mode0"].ravel()[:3], "losses", [float(d["loss_%d" % i]) for i in range(3)])
     print("ref_tf_interht: call_mode0", a["call_mode0"].ravel()[:3])
     print("ref_tf_trainstep: losses", [float(b["loss_%d" % i]) for i in range(3)])
     print("ref_tf_loss: cases", c["cases"].shape)

@@ -152,3 +152,54 @@ def test_validation_errors():
     m = ko.make_model("TransE", 4, 2, 4, 1.0)
     with pytest.raises(ValueError):
         m(torch.zeros(1, 3, dtype=torch.int64), "bad-mode")
+
+
+# ---- TranSparse (tensorflow_codes/model.py:96-106,226-235) ---------------------------------------------
+def _transparse_from_golden(g, suffix=""):
+    m = ko.OracleTranSparse(int(g["E"]), int(g["R"]), int(g["H"]), float(g["gamma"]))
+    with torch.no_grad():
+        m.entity_embedding.copy_(torch.from_numpy(g["entity_embedding" + suffix]))
+        m.relation_embedding.copy_(torch.from_numpy(g["relation_embedding" + suffix]))
+        m.W.copy_(torch.from_numpy(g["W" + suffix]))
+        m.mask.copy_(torch.from_numpy(g["mask"]))
+    return m
+
+
+def test_transparse_scores_and_call_match_reference_source():
+    g = _load("ref_tf_transparse.npz")
+    m = _transparse_from_golden(g)
+    pos, neg = torch.from_numpy(g["positive_sample"]), torch.from_numpy(g["negative_sample"])
+    with torch.no_grad():
+        np.testing.assert_allclose(m(pos, "single").numpy(), g["score_single"], rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(m((pos, neg), "head-batch").numpy(), g["score_head_batch"], rtol=RTOL, atol=ATOL)
+        tb = m((pos, neg), "tail-batch").numpy()
+        assert tb.shape == g["score_tail_batch"].shape == (pos.shape[0], 1)  # model.py:229: the tail is never read
+        np.testing.assert_allclose(tb, g["score_tail_batch"], rtol=RTOL, atol=ATOL)
+        for mode in (0, 1, 3):
+            np.testing.assert_allclose(ko.tf_call(m, (pos, neg), mode).numpy(), g["call_mode%d" % mode], rtol=RTOL, atol=ATOL)
+
+
+def test_transparse_train_steps_match_reference_source():
+    g = _load("ref_tf_transparse.npz")
+    m = _transparse_from_golden(g)
+    opt = ko.KerasAdam([m.entity_embedding, m.relation_embedding, m.W], lr=float(g["lr"]))
+    for step in range(3):
+        batch = tuple(torch.from_numpy(g["%s_%d" % (k, step)]) for k in
+                      ("positive_sample", "negative_sample", "subsampling_weight", "mode"))
+        loss = ko.tf_train_step(m, opt, batch)
+        np.testing.assert_allclose(loss.item(), float(g["loss_%d" % step]), rtol=RTOL, atol=ATOL)
+        for k in ("entity_embedding", "relation_embedding", "W"):
+            np.testing.assert_allclose(getattr(m, k).detach().numpy(), g["%s_%d" % (k, step + 1)], rtol=RTOL, atol=ATOL)
+    # masked-out weights never move (their gradient is mask * dM = 0 and Adam's update of a zero history is 0)
+    off = g["mask"] == 0
+    assert np.array_equal(m.W.detach().numpy()[off], g["W"][off])
+
+
+def test_transparse_projected_tail_variant_reads_the_tail():
+    """project_tail=True (what model.py:229 evidently meant): the tail-batch scores depend on the candidates."""
+    torch.manual_seed(3)
+    m = ko.OracleTranSparse(31, 3, 12, 9.0, project_tail=True)
+    pos, neg, _, _ = ko.synthetic_batch(31, 3, 4, 6, seed=1)
+    with torch.no_grad():
+        s = m((pos, neg), "tail-batch")
+    assert s.shape == (4, 6) and float(s.std(dim=1).min()) > 0
