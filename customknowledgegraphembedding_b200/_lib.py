@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkge_b200.so")
 
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 # kge_model_id / kge_mode / kge_ws_kind
 MODEL_IDS = {"TransE": 0, "DistMult": 1, "ComplEx": 2, "RotatE": 3, "pRotatE": 4, "InterHT": 5}
@@ -45,6 +45,11 @@ class AdamOpts(C.Structure):
         ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
         ("step", C.c_int32), ("keras_epsilon_mode", C.c_int32),
     ]
+
+
+class TranSparseDesc(C.Structure):
+    _fields_ = [("nentity", C.c_int64), ("nrelation", C.c_int64), ("dim", C.c_int64), ("gamma", C.c_float),
+                ("project_tail", C.c_int32)]
 
 
 class StepBuffers(C.Structure):
@@ -103,6 +108,12 @@ PROTOTYPES = {
     "kge_shard_compact": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _I64, _P, _P, _SZ, _P]),
     "kge_shard_fetch_rows": (C.c_int, [_P, _P, _I64, _I64, C.POINTER(C.c_void_p), C.c_int, _I64, _P, _P]),
     "kge_workspace_bytes": (_SZ, [C.c_int, _DESC, _I64, _I64]),
+    "kge_transparse_nout": (C.c_int64, [C.POINTER(TranSparseDesc), C.c_int, _I64]),
+    "kge_transparse_workspace_bytes": (_SZ, [C.POINTER(TranSparseDesc), C.c_int, _I64, _I64, C.c_int]),
+    "kge_transparse_forward": (C.c_int, [C.POINTER(TranSparseDesc), C.c_int, _P, _P, _P, _P, _P, _P, _I64, _I64, _P, _P,
+                                         C.c_int, _P, _SZ, _P]),
+    "kge_transparse_backward": (C.c_int, [C.POINTER(TranSparseDesc), C.c_int, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _P,
+                                          _P, _SZ, _P]),
     "kge_probe_l2_read": (C.c_int, [_P, _SZ, C.c_int, _P, C.POINTER(C.c_int64), _P]),
     "kge_profile_enable": (C.c_int, [C.c_int]),
     "kge_profile_num_stages": (C.c_int, []),

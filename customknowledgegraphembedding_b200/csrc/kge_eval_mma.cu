@@ -22,103 +22,15 @@
 //               candidate with an identical row ties exactly (n_equal keeps its meaning).
 //   schedule    persistent CTAs (one per SM), tile = (entity tile, query tile) with the query tile fastest so
 //               that concurrently running CTAs share the B tile in L2.
-#include <cuda.h>
-
-#include <algorithm>
 #include <climits>
 
-#include "kge_internal.h"
-#include "kge_ptx.cuh"
+#include "kge_umma.cuh"
 
 namespace kge {
 namespace mma {
 
-constexpr int BM = 128;      // queries per tile (TMEM lanes)
-constexpr int BN = 256;      // entities per tile (TMEM columns per accumulator)
-constexpr int BK = 32;       // fp32 coordinates per stage row = 128 bytes = one swizzle span
-constexpr int UMMA_K = 8;    // K of one tcgen05.mma.kind::tf32
-constexpr int STAGES = 2;
 constexpr int kThreads = 192;  // warp 0 TMA producer, warp 1 MMA issuer + TMEM owner, warps 2..5 epilogue
-constexpr uint32_t A_BYTES = BM * BK * 4;                    // 16 KB
-constexpr uint32_t B_BYTES = BN * BK * 4;                    // 32 KB
-constexpr uint32_t STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;  // hi + lo of both = 96 KB
-constexpr uint32_t SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + 128;
-constexpr uint32_t TMEM_COLS = 512;
 constexpr long long kEntityChunk = 32768;  // rows of the split B workspace per pass
-
-// ---- PTX wrappers ------------------------------------------------------------------------------
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-        "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-
-// Shared-memory matrix descriptor, K-major operand, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart.
-// bits [0,14) start >> 4 | [16,30) LBO >> 4 (unused with swizzle, 1) | [32,46) SBO >> 4 | [46,48) version 1 |
-// [61,64) layout 2 = SWIZZLE_128B.  Advancing K by 8 tf32 = 32 B adds 2 to the start field.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
-           ((uint64_t)2 << 61);
-}
-// Instruction descriptor kind::tf32: D fp32 (bits [4,6) = 1), A/B tf32 (bits [7,10) = [10,13) = 2), both K-major,
-// N >> 3 at bit 17, M >> 4 at bit 24.
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-// 32 lanes x 32 consecutive columns -> 32 registers per thread (thread = lane = accumulator row)
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
-        "tcgen05.wait::ld.sync.aligned;"  // same asm statement: no consumer can be scheduled before the wait
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// ---- operand split ------------------------------------------------------------------------------
-// round-to-nearest-even onto the tf32 grid (10 explicit mantissa bits); inputs are finite table values
-__device__ __forceinline__ float tf32_rne(float x) {
-    uint32_t u = __float_as_uint(x);
-    u += 0xFFFu + ((u >> 13) & 1u);
-    return __uint_as_float(u & 0xFFFFE000u);
-}
-__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-    hi = tf32_rne(x);
-    lo = tf32_rne(x - hi);  // x - hi is exact in fp32
-}
 
 // rows of `src` (pitch floats apart; row = gather ? row named by the query : row0 + r * row_stride) -> hi / lo [rows, Kpad]
 __global__ void __launch_bounds__(256)
@@ -391,35 +303,6 @@ static Layout layout(const Params& P, int64_t Q, int64_t nfilter) {
     L.sidx = o; o += al((size_t)std::max<int64_t>(nfilter, 1) * sizeof(int));
     L.total = o + 1024;  // slack to align the caller's pointer
     return L;
-}
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    return fn;
-}
-
-// [rows, Kpad] fp32 row-major, box = box_rows x 32 floats (128 B), 128-byte swizzle, out-of-range rows read as 0
-static bool make_tmap(CUtensorMap* tm, const float* ptr, long long rows, int Kpad, int box_rows) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return false;
-    const cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)std::max<long long>(rows, 1)};
-    const cuuint64_t strides[1] = {(cuuint64_t)Kpad * sizeof(float)};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
-    const cuuint32_t estr[2] = {1, 1};
-    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 }  // namespace mma

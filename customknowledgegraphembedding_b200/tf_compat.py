@@ -27,6 +27,7 @@ import torch
 import torch.nn.functional as F
 
 from .model import KGEModel
+from .transparse import TranSparseModel
 
 TF_MODE_HEAD_BATCH, TF_MODE_TAIL_BATCH, TF_MODE_SINGLE = 0, 1, 3
 
@@ -34,9 +35,17 @@ TF_MODE_HEAD_BATCH, TF_MODE_TAIL_BATCH, TF_MODE_SINGLE = 0, 1, 3
 class TFKGEModel:
     def __init__(self, model_name, nentity, nrelation, hidden_dim, gamma,
                  double_entity_embedding=False, double_relation_embedding=False,
-                 triple_relation_embedding=False, device="cuda", **kwargs):
-        self.kge = KGEModel(model_name, nentity, nrelation, hidden_dim, gamma, double_entity_embedding,
-                            double_relation_embedding, triple_relation_embedding).to(device)
+                 triple_relation_embedding=False, device="cuda", project_tail=False, **kwargs):
+        if model_name == "TranSparse":
+            # model.py:96-106: W [R, D, D] + the fixed 0/1 mask; :227 needs entity_dim == relation_dim.
+            # project_tail=False keeps model.py:229 as written (the head is projected twice; see transparse.py)
+            if double_entity_embedding or double_relation_embedding or triple_relation_embedding:
+                raise ValueError("TranSparse multiplies [.., entity_dim] by [relation_dim, relation_dim] (model.py:227): "
+                                 "no -de / -dr / -tr")
+            self.kge = TranSparseModel(nentity, nrelation, hidden_dim, gamma, project_tail=project_tail).to(device)
+        else:
+            self.kge = KGEModel(model_name, nentity, nrelation, hidden_dim, gamma, double_entity_embedding,
+                                double_relation_embedding, triple_relation_embedding).to(device)
         self.model_name, self.nentity, self.nrelation, self.hidden_dim = model_name, nentity, nrelation, hidden_dim
         self.epsilon = 2.0
         self.entity_dim, self.relation_dim = self.kge.entity_dim, self.kge.relation_dim
@@ -51,6 +60,14 @@ class TFKGEModel:
     @property
     def relation_embedding(self):
         return self.kge.relation_embedding
+
+    @property
+    def W(self):
+        return self.kge.W          # TranSparse only (model.py:105)
+
+    @property
+    def mask(self):
+        return self.kge.mask       # TranSparse only (model.py:103)
 
     @property
     def gamma(self):
@@ -146,6 +163,12 @@ class Trainer:
         name = TFKGEModel.mode_name(mode.reshape(-1)[0] if hasattr(mode, "reshape") else mode)
         if name == "single":
             raise ValueError("mode %s not supported" % name)
+        if self.model.model_name == "TranSparse":
+            loss = kge.tf_train_step(self.optimizer, positive_sample, negative_sample, subsampling_weight, name)
+            self.optimizer.iterations += 1
+            if self.metrics is not None:
+                self.metrics.update_state(loss * self.strategy.num_replicas_in_sync)
+            return {"loss": loss}
         group = self.optimizer.param_groups[0]
         out = kge._fused_step(self.optimizer, group, positive_sample, negative_sample,
                               subsampling_weight.reshape(-1), name, True, 1.0, False, 0.0,

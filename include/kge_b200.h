@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KGE_B200_ABI_VERSION 12
+#define KGE_B200_ABI_VERSION 13
 
 #if defined(__GNUC__)
 #define KGE_API __attribute__((visibility("default")))
@@ -427,6 +427,48 @@ KGE_API int kge_profile_enable(int on);
 KGE_API int kge_profile_num_stages(void);
 KGE_API const char *kge_profile_stage_name(int stage);
 KGE_API int kge_profile_read(float *ms_sum, int64_t *launches, int reset);
+
+/*
+ * TranSparse.  Replaces TFKGEModel('TranSparse', ...) of /root/reference/tensorflow_codes/model.py:
+ * the variables of :96-106 (W [R, D, D] trainable, mask [R, D, D] fixed 0/1, both float), the gathers of
+ * :139-142,161-164,187-190 and the score of :226-235:
+ *     score = gamma - sum_j | ph_j * rh_j - pt_j |
+ *     ph = normalize(head @ (mask_r o W_r)),  pt = normalize(X @ (mask_r o W_r)),  rh = normalize(relation_r)
+ * project_tail = 0: X = head, the reference AS WRITTEN (:229 projects `head` a second time; the tail entity is never
+ *   read and tail-batch yields ONE score per positive, [B, 1]);  project_tail = 1: X = tail.
+ * entity_dim == relation_dim == dim (the matmul of :227 needs it).  The projections run as 3xTF32 tiles on tcgen05.
+ *
+ * kge_transparse_forward: mode SINGLE -> positive_score [B];  HEAD_BATCH / TAIL_BATCH -> positive_score [B] AND
+ *   negative_score [B, kge_transparse_nout(desc, mode, N)] in one pass (the TF train step calls the model twice per
+ *   batch, supervisor.py:17-20: both calls are answered here).  negative [B, N] may be NULL when no candidate row is
+ *   read (SINGLE; TAIL_BATCH without project_tail).  Ids must lie in range (not checked on the device).
+ *   with_backward != 0 also prepares what kge_transparse_backward needs, in `ws`.
+ * kge_transparse_backward: gradients of sum(dpositive * positive_score) + sum(dnegative * negative_score);
+ *   grad_entity [E, D], grad_relation [R, D], grad_W [R, D, D] are OVERWRITTEN (dense; rows / relations the batch does
+ *   not touch get zeros; grad_W is already multiplied by the mask).  `ws` must be the workspace of the preceding
+ *   kge_transparse_forward(with_backward = 1) with the same desc / mode / positive / B / N, untouched in between.
+ *   The entity gradient is accumulated with float atomics (order of a row's uses not fixed); everything else is
+ *   summed in a fixed order.
+ */
+typedef struct {
+    int64_t nentity;
+    int64_t nrelation;
+    int64_t dim;
+    float gamma;
+    int32_t project_tail;
+} kge_transparse_desc;
+
+KGE_API int64_t kge_transparse_nout(const kge_transparse_desc *desc, int mode, int64_t N);
+KGE_API size_t kge_transparse_workspace_bytes(const kge_transparse_desc *desc, int mode, int64_t B, int64_t N,
+                                              int with_backward);
+KGE_API int kge_transparse_forward(const kge_transparse_desc *desc, int mode, const float *entity, const float *relation,
+                                   const float *W, const float *mask, const int64_t *positive, const int64_t *negative,
+                                   int64_t B, int64_t N, float *positive_score, float *negative_score, int with_backward,
+                                   void *ws, size_t ws_bytes, void *stream);
+KGE_API int kge_transparse_backward(const kge_transparse_desc *desc, int mode, const float *relation, const float *mask,
+                                    const int64_t *positive, int64_t B, int64_t N, const float *dpositive,
+                                    const float *dnegative, float *grad_entity, float *grad_relation, float *grad_W,
+                                    void *ws, size_t ws_bytes, void *stream);
 
 /* Measurement probe (bench.py `roofline.l2`; no reference counterpart): a persistent grid re-reads `bytes` of `buf`
  * (device, 16-byte aligned, should fit L2: 32 MB) `iters` times with L2-only 128-bit loads; *bytes_read (host) = bytes

@@ -1,0 +1,200 @@
+"""GPU: TranSparse (csrc/kge_transparse.cu through the C-ABI: TranSparseModel / TFKGEModel('TranSparse') / Trainer)
+against (a) the golden vectors produced by the reference's own tensorflow_codes/model.py + supervisor.py
+(oracle/run_reference_tf.py -> tests/golden/ref_tf_transparse.npz) and (b) the CPU oracle (OracleTranSparse, fp32
+with its fp64 twin) on seeded inputs that exercise the tile geometry: D below / across the 32-wide K stage and the
+256-wide column tile, more than 128 rows per relation, relations absent from the batch, more relations than positives.
+
+Tolerances: scores and losses 1e-5 (Checker/trainer_checker.py:91); gradients 2e-5 of the largest entry (3xTF32
+products carry ~2^-22 per term, the fp32 oracle's own summation order is of the same size -- the fp64 twin adjudicates).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import kge_oracle as ko
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+MODES = {"single": 3, "head-batch": 0, "tail-batch": 1}
+
+
+def _pair(E, R, D, gamma, project_tail, seed):
+    """(oracle model, CUDA model) with identical variables."""
+    from customknowledgegraphembedding_b200.transparse import TranSparseModel
+    torch.manual_seed(seed)
+    o = ko.OracleTranSparse(E, R, D, gamma, project_tail=project_tail)
+    m = TranSparseModel(E, R, D, gamma, project_tail=project_tail)
+    m.load_state_dict(o.state_dict())
+    return o, m.cuda()
+
+
+def _batch(E, R, B, N, seed, rel_pool=None):
+    pos, neg, w, _ = ko.synthetic_batch(E, R, B, N, seed=seed)
+    if rel_pool is not None:  # only some relations occur
+        pos[:, 1] = torch.tensor(rel_pool)[torch.randint(0, len(rel_pool), (B,), generator=torch.Generator().manual_seed(seed))]
+    return pos, neg, w
+
+
+CASES = [
+    # E, R, D, B, N, relation pool
+    (61, 5, 22, 6, 9, None),          # the golden geometry: D < one K stage
+    (90, 3, 100, 7, 20, None),        # D across K stages, one column tile
+    (150, 4, 300, 5, 130, [0, 2]),    # two column tiles, > 128 rows per relation, relations 1 and 3 absent
+    (40, 37, 33, 9, 3, None),         # more relations than positives, odd D (scalar stores)
+]
+
+
+@pytest.mark.parametrize("project_tail", [False, True])
+@pytest.mark.parametrize("case", CASES)
+def test_scores_match_oracle(case, project_tail):
+    E, R, D, B, N, pool = case
+    o, m = _pair(E, R, D, 12.0, project_tail, seed=E + D)
+    pos, neg, _ = _batch(E, R, B, N, seed=D, rel_pool=pool)
+    o64 = ko.transparse_to_double(o)
+    with torch.no_grad():
+        for mode in ("single", "head-batch", "tail-batch"):
+            sample = pos if mode == "single" else (pos, neg)
+            want = o(sample, mode).numpy()
+            want64 = o64(sample, mode).numpy()
+            got = m(pos.cuda() if mode == "single" else (pos.cuda(), neg.cuda()), mode).cpu().numpy()
+            assert got.shape == want.shape, (mode, got.shape, want.shape)
+            err, ref = np.abs(got - want64).max(), np.abs(want - want64).max()
+            assert err <= max(2e-5 * np.abs(want64).max(), 4 * ref), (mode, err, ref)
+            np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * np.abs(want).max())
+
+
+@pytest.mark.parametrize("project_tail", [False, True])
+@pytest.mark.parametrize("mode", ["head-batch", "tail-batch"])
+@pytest.mark.parametrize("case", CASES)
+def test_gradients_match_oracle(case, mode, project_tail):
+    """One autograd node answers the positive and the negative scores; random upstream gradients on both."""
+    E, R, D, B, N, pool = case
+    o, m = _pair(E, R, D, 9.0, project_tail, seed=3 * E + D)
+    pos, neg, _ = _batch(E, R, B, N, seed=D + 1, rel_pool=pool)
+    o64 = ko.transparse_to_double(o)
+    g = torch.Generator().manual_seed(5)
+    ps, ns = m.both((pos.cuda(), neg.cuda()), mode)
+    up_p, up_n = torch.randn(ps.shape, generator=g), torch.randn(ns.shape, generator=g)
+    (ps * up_p.cuda()).sum().add((ns * up_n.cuda()).sum()).backward()
+    for model, dt in ((o, torch.float32), (o64, torch.float64)):
+        l = (model(pos, "single") * up_p.to(dt)).sum() + (model((pos, neg), mode) * up_n.to(dt)).sum()
+        l.backward()
+    for name in ("entity_embedding", "relation_embedding", "W"):
+        got = getattr(m, name).grad.cpu().double().numpy()
+        want = getattr(o, name).grad.double().numpy()
+        want64 = getattr(o64, name).grad.numpy()
+        scale = np.abs(want64).max()
+        err, ref = np.abs(got - want64).max(), np.abs(want - want64).max()
+        assert err <= max(2e-5 * scale, 4 * ref), (name, err, ref, scale)
+    # the mask is applied to the W gradient, relations absent from the batch get exactly zero
+    gW = m.W.grad.cpu()
+    assert bool((gW[m.mask.cpu() == 0] == 0).all())
+    absent = sorted(set(range(R)) - set(pos[:, 1].tolist()))
+    if absent:
+        assert bool((gW[absent] == 0).all()) and bool((m.relation_embedding.grad.cpu()[absent] == 0).all())
+
+
+def _tf_model(g, suffix="", project_tail=False):
+    from customknowledgegraphembedding_b200.tf_compat import TFKGEModel
+    m = TFKGEModel("TranSparse", int(g["E"]), int(g["R"]), int(g["H"]), float(g["gamma"]), project_tail=project_tail)
+    with torch.no_grad():
+        m.entity_embedding.copy_(torch.from_numpy(g["entity_embedding" + suffix]))
+        m.relation_embedding.copy_(torch.from_numpy(g["relation_embedding" + suffix]))
+        m.W.copy_(torch.from_numpy(g["W" + suffix]))
+        m.mask.copy_(torch.from_numpy(g["mask"]))
+    return m
+
+
+def test_scores_and_call_match_reference_source():
+    g = np.load(os.path.join(GOLDEN, "ref_tf_transparse.npz"))
+    m = _tf_model(g)
+    pos, neg = torch.from_numpy(g["positive_sample"]).cuda(), torch.from_numpy(g["negative_sample"]).cuda()
+    with torch.no_grad():
+        np.testing.assert_allclose(m.kge(pos, "single").cpu().numpy(), g["score_single"], rtol=1e-5, atol=1e-5)
+        np.testing.assert_allclose(m.kge((pos, neg), "head-batch").cpu().numpy(), g["score_head_batch"], rtol=1e-5, atol=1e-5)
+        tb = m.kge((pos, neg), "tail-batch").cpu().numpy()
+        assert tb.shape == g["score_tail_batch"].shape  # [B, 1]: model.py:229
+        np.testing.assert_allclose(tb, g["score_tail_batch"], rtol=1e-5, atol=1e-5)
+        for mode in (0, 1, 3):
+            got = m(((pos, neg), torch.tensor(mode))).cpu().numpy()
+            assert got.shape == g["call_mode%d" % mode].shape
+            np.testing.assert_allclose(got, g["call_mode%d" % mode], rtol=1e-5, atol=1e-5)
+
+
+def test_trainer_train_steps_match_reference_source():
+    from customknowledgegraphembedding_b200.tf_compat import KerasAdam, SumMetric, Trainer
+    g = np.load(os.path.join(GOLDEN, "ref_tf_transparse.npz"))
+    m = _tf_model(g)
+    opt = KerasAdam(learning_rate=float(g["lr"]))
+    metric = SumMetric()
+    batches = [tuple(torch.from_numpy(g["%s_%d" % (k, s)]) for k in
+                     ("positive_sample", "negative_sample", "subsampling_weight", "mode")) for s in range(3)]
+    trainer = Trainer(None, batches, m, opt, metric)
+    it = iter(batches)
+    for step in range(3):
+        metric.reset_states()
+        trainer.train_step(it)
+        np.testing.assert_allclose(metric.result(), float(g["loss_%d" % step]), rtol=1e-5, atol=1e-5)
+        for k in ("entity_embedding", "relation_embedding", "W"):
+            np.testing.assert_allclose(getattr(m, k).detach().cpu().numpy(), g["%s_%d" % (k, step + 1)], rtol=1e-5, atol=1e-5)
+    off = g["mask"] == 0
+    assert np.array_equal(m.W.detach().cpu().numpy()[off], g["W"][off])  # masked-out weights never move
+
+
+@pytest.mark.parametrize("project_tail", [False, True])
+def test_tf_train_steps_match_oracle_at_a_wider_shape(project_tail):
+    """D = 200, 150 candidates, 16 positives over 3 of 6 relations, alternating modes, Keras Adam on all three variables."""
+    from customknowledgegraphembedding_b200.tf_compat import KerasAdam
+    E, R, D, B, N, lr = 300, 6, 200, 16, 150, 1e-3
+    o, m = _pair(E, R, D, 12.0, project_tail, seed=77)
+    oopt = ko.KerasAdam([o.entity_embedding, o.relation_embedding, o.W], lr=lr)
+    opt = KerasAdam(learning_rate=lr)
+    for step in range(3):
+        pos, neg, w = _batch(E, R, B, N, seed=40 + step, rel_pool=[1, 4, 5])
+        mode = "head-batch" if step % 2 == 0 else "tail-batch"
+        before = {k: getattr(o, k).detach().clone() for k in ("entity_embedding", "relation_embedding", "W")}
+        want = ko.tf_train_step(o, oopt, (pos, neg, w.view(-1, 1), torch.full((B,), MODES[mode])))
+        got = m.tf_train_step(opt, pos, neg, w, mode)
+        opt.iterations += 1
+        assert abs(got.item() - want.item()) <= 1e-5 * abs(want.item()), (step, got.item(), want.item())
+        for k in ("entity_embedding", "relation_embedding", "W"):
+            a, b = getattr(m, k).detach().cpu(), getattr(o, k).detach()
+            moved = (b - before[k]).abs().max().item()
+            # Adam normalises the step to ~lr: compare the update, not the value (bulk 1e-3 of lr; sign flips of
+            # near-zero gradients can move single entries by up to 2 lr in the first steps)
+            diff = (a - b).abs()
+            assert float((diff > 2e-2 * lr).float().mean()) < 2e-3, (step, k, float(diff.max()), moved)
+            assert float(diff.max()) <= 2.5 * lr, (step, k, float(diff.max()))
+
+
+def test_torch_optimizer_train_step_matches_oracle():
+    """KGEModel.train_step contract with torch.optim.Adam (PyTorch loss semantics: detached softmax weights)."""
+    from customknowledgegraphembedding_b200.transparse import TranSparseModel
+    E, R, D, B, N, lr = 120, 4, 64, 8, 40, 1e-3
+    o, m = _pair(E, R, D, 12.0, True, seed=9)
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=0.5, cuda=True)
+    oopt, opt = torch.optim.Adam(o.parameters(), lr=lr), torch.optim.Adam(m.parameters(), lr=lr)
+    for step in range(2):
+        pos, neg, w = _batch(E, R, B, N, seed=60 + step)
+        mode = "tail-batch" if step % 2 == 0 else "head-batch"
+        want = ko.train_step(o, oopt, iter([(pos, neg, w, mode)]), args)
+        got = TranSparseModel.train_step(m, opt, iter([(pos.cuda(), neg.cuda(), w.cuda(), mode)]), args)
+        for k in ("positive_sample_loss", "negative_sample_loss", "loss"):
+            assert abs(got[k] - want[k]) <= 1e-5 * abs(want[k]), (step, k, got[k], want[k])
+
+
+def test_argument_checks():
+    from customknowledgegraphembedding_b200.tf_compat import TFKGEModel
+    from customknowledgegraphembedding_b200.transparse import TranSparseModel
+    with pytest.raises(ValueError):
+        TFKGEModel("TranSparse", 10, 2, 8, 12.0, double_entity_embedding=True)
+    m = TranSparseModel(10, 2, 8, 12.0)
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(2, 3, dtype=torch.int64))  # no CPU path
+    m = m.cuda()
+    with pytest.raises(ValueError):
+        m((torch.zeros(2, 3, dtype=torch.int64), None), "head-batch")
+    with pytest.raises(ValueError):
+        m(torch.zeros(2, 3, dtype=torch.int64), "both")
