@@ -432,8 +432,10 @@ def run_ours(a):
         smp = ev = ev_gemm = None
         ev_10m = {"skipped": "--train-only"}
         tr_interht = train_config_bench(CONFIG3, dev, timed, min(K, 50)) if (world == 1 and a.interht) else None
+        tr_transparse = train_transparse_bench(dev, timed, min(K, 10)) if (world == 1 and a.transparse) else None
     else:
         tr_interht = train_config_bench(CONFIG3, dev, timed, min(K, 50)) if world == 1 else None
+        tr_transparse = train_transparse_bench(dev, timed, min(K, 10)) if world == 1 else None
         smp = sampler_bench(model, opt, group, w, dev, timed, K) if world == 1 else None
         ev = eval_bench(model, w, dev, timed, rank, world)
         if rank == 0:
@@ -500,6 +502,7 @@ def run_ours(a):
         "dist_check": dist_check,
         "train_interht": tr_interht,
         "train_sharded": tr_sharded,
+        "train_transparse": tr_transparse,
         "gpu_sampler": smp,
         "eval": ev,
         "eval_gemm": ev_gemm,
@@ -520,6 +523,9 @@ def run_ours(a):
         "eval_gemm_distmult_issued_frac": _v(ev_gemm, "DistMult", "roofline", "frac"),
         "eval_10m_qps": _v(ev_10m, "value"), "eval_10m_checksum": _v(ev_10m, "checksum_n_greater"),
         "train_interht_pytorch": _v(tr_interht, "pytorch", "value"), "train_interht_tf": _v(tr_interht, "tf", "value"),
+        "train_transparse_as_written": _v(tr_transparse, "as_written", "value"),
+        "train_transparse_head_batch_ms": _v(tr_transparse, "as_written", "head-batch", "ms_per_step"),
+        "train_transparse_issued_frac": _v(tr_transparse, "as_written", "head-batch", "roofline", "frac"),
         "train_sharded_yago": _v(tr_sharded, "yago3-10", "value"),
         "train_sharded_yago_ms": _v(tr_sharded, "yago3-10", "ms_per_step"),
         "train_sharded_yago_check_ok": _v(tr_sharded, "yago3-10", "dist_check", "ok"),
@@ -536,6 +542,69 @@ def run_ours(a):
     emit(line)
     if dist is not None:
         dist.destroy_process_group()
+
+
+TRANSPARSE = dict(nentity=14541, nrelation=237, dim=500, gamma=12.0, batch=1024, negatives=256, lr=1e-4)
+
+
+def train_transparse_bench(dev, timed, K):
+    """the reference's second TF model, TFKGEModel('TranSparse') under Trainer.train_step
+    (tensorflow_codes/model.py:96-106,226-235; supervisor.py:15-28), FB15k-237 sizes with dim 500, batch 1024, 256
+    negatives.  Head-batch steps carry the work (B * (N + 1) rows through three D x D GEMMs: P = X M_r, dX = dP M_r^T,
+    dW_r = X^T dP); as the reference wrote the score (model.py:229) a tail-batch step projects the B heads only.
+    Roofline: tensor pipe, kind::tf32 = half the measured bf16 rate; `frac` counts the 3 MMA passes of 3xTF32."""
+    import torch
+    from customknowledgegraphembedding_b200.tf_compat import KerasAdam
+    from customknowledgegraphembedding_b200.transparse import TranSparseModel
+    c = TRANSPARSE
+    E, R, D, B, N = c["nentity"], c["nrelation"], c["dim"], c["batch"], c["negatives"]
+    bf16 = None
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            bf16 = float(json.load(f).get("bf16_tflops", 0)) or None
+    peak, src = (bf16 / 2, "measured bf16_tflops / 2 (MEASURED_PEAKS.json)") if bf16 else (795.0, "fallback 1.59 PF bf16 / 2")
+    out = {"workload": "TranSparse E=%d R=%d D=%d gamma=%g B=%d N=%d, TF loss (attached softmax), Keras Adam on entity / "
+                       "relation / W" % (E, R, D, c["gamma"], B, N), "unit": "triples*neg/s"}
+    batches = []
+    for s in range(4):
+        p, n, sw, _ = synthetic_batch(E, R, B, N, seed=9000 + s)
+        batches.append((p.to(dev), n.to(dev), sw.to(dev)))
+    for variant, tail in (("as_written", False), ("projected_tail", True)):
+        torch.manual_seed(0)
+        m = TranSparseModel(E, R, D, c["gamma"], project_tail=tail).to(dev)
+        opt = KerasAdam(learning_rate=c["lr"])
+        res = {}
+        for mode in ("head-batch", "tail-batch"):
+            def steps(n):
+                for i in range(n):
+                    p, ng, sw = batches[i % len(batches)]
+                    m.tf_train_step(opt, p, ng, sw, mode)
+                    opt.iterations += 1
+
+            def forwards(n):
+                with torch.no_grad():
+                    for i in range(n):
+                        p, ng, _ = batches[i % len(batches)]
+                        m.both((p, ng), mode)
+            steps(2)
+            ms = timed(lambda: steps(K)) / K
+            fwd_ms = timed(lambda: forwards(K)) / K
+            big = mode == "head-batch" or tail
+            rows = B * ((N if big else 0) + 1 + (1 if tail else 0))
+            flops = 3 * 2.0 * rows * D * D
+            res[mode] = {"ms_per_step": ms, "forward_only_ms": fwd_ms, "value": B * N / (ms * 1e-3), "rows_projected": rows,
+                         "roofline": {"bound": "tensor", "achieved": 3 * flops / (ms * 1e-3) / 1e12, "peak": peak,
+                                      "unit": "TFLOP/s", "frac": 3 * flops / (ms * 1e-3) / 1e12 / peak, "peak_source": src,
+                                      "useful_tflops": flops / (ms * 1e-3) / 1e12,
+                                      "useful_frac": flops / (ms * 1e-3) / 1e12 / peak,
+                                      "note": "whole step: plan, operand splits of W and the rows, 3 grouped GEMMs, score / "
+                                              "dscore, scatter, dense Keras Adam over E*D + R*D + R*D*D parameters"}}
+        res["value"] = 2 * B * N / ((res["head-batch"]["ms_per_step"] + res["tail-batch"]["ms_per_step"]) * 1e-3)
+        out[variant] = res
+        del m, opt
+        torch.cuda.empty_cache()
+    return out
 
 
 CONFIG3 = dict(model="InterHT", nentity=40943, nrelation=11, hidden_dim=1000, gamma=24.0, batch=1024, negatives=512,
@@ -930,6 +999,7 @@ def main():
     ap.add_argument("--no-eval10m", action="store_true", help="skip the 10M-entity sharded eval section (80 GB table)")
     ap.add_argument("--train-only", action="store_true", help="tuning loops: only the headline train step sections")
     ap.add_argument("--sharded", action="store_true", help="with --train-only: also the row-sharded train sections (configs[4])")
+    ap.add_argument("--transparse", action="store_true", help="with --train-only: also time the TranSparse train step (8(f) N4)")
     ap.add_argument("--interht", action="store_true", help="with --train-only: also time BASELINE configs[2] (InterHT)")
     ap.add_argument("--no-dist-check", action="store_true", help="N > 1: skip the correctness check around the timed region")
     a = ap.parse_args()

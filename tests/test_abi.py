@@ -59,3 +59,25 @@ def test_no_cpu_fallback():
     import sys
     src = open(os.path.join(REPO, "customknowledgegraphembedding_b200", "model.py")).read()
     assert "oracle" not in src and "oracle" not in open(os.path.join(REPO, "customknowledgegraphembedding_b200", "ops.py")).read()
+
+
+def test_transparse_host_logic_without_gpu():
+    """Sizes, the output shape rule and argument validation of the TranSparse entry points need no device."""
+    from customknowledgegraphembedding_b200 import _lib
+    lib = _lib.load()
+    as_written = _lib.TranSparseDesc(100, 7, 48, 12.0, 0)
+    projected = _lib.TranSparseDesc(100, 7, 48, 12.0, 1)
+    assert lib.kge_transparse_nout(ctypes.byref(as_written), _lib.MODE_IDS["head-batch"], 9) == 9
+    assert lib.kge_transparse_nout(ctypes.byref(as_written), _lib.MODE_IDS["tail-batch"], 9) == 1   # model.py:229
+    assert lib.kge_transparse_nout(ctypes.byref(projected), _lib.MODE_IDS["tail-batch"], 9) == 9
+    assert lib.kge_transparse_nout(ctypes.byref(as_written), _lib.MODE_IDS["single"], 9) == 0
+    fwd = lib.kge_transparse_workspace_bytes(ctypes.byref(as_written), 1, 8, 16, 0)
+    bwd = lib.kge_transparse_workspace_bytes(ctypes.byref(as_written), 1, 8, 16, 1)
+    assert 0 < fwd < bwd
+    assert lib.kge_transparse_workspace_bytes(ctypes.byref(_lib.TranSparseDesc(100, 0, 48, 12.0, 0)), 1, 8, 16, 0) == 0
+    rc = lib.kge_transparse_forward(ctypes.byref(as_written), 1, None, None, None, None, None, None, 8, 16, None, None, 0,
+                                    None, 0, None)
+    assert rc == _lib.KGE_ERR_INVALID_ARGUMENT
+    rc = lib.kge_transparse_forward(ctypes.byref(as_written), 7, None, None, None, None, None, None, 8, 16, None, None, 0,
+                                    None, 0, None)
+    assert rc == _lib.KGE_ERR_INVALID_ARGUMENT and b"mode" in lib.kge_last_error()
