@@ -328,6 +328,22 @@ rows_split_kernel(const float* __restrict__ src, long long pitch, const int64_t*
     }
 }
 
+// Zeros in the K padding of the transposed workspaces: columns [padoff[r] + rows_r, padoff[r + 1]) of every row k.
+// (The GEMM over K = rows reads whole 32-column stages; everything else in a segment is written by rows_split_kernel.)
+__global__ void __launch_bounds__(256)
+pad_zero_kernel(const int* __restrict__ cnt, const int* __restrict__ padoff, Dims d, float* __restrict__ Thi,
+                float* __restrict__ Tlo) {
+    const int r = blockIdx.x;
+    const int c0 = padoff[r] + cnt[r] * d.rpp, c1 = padoff[r + 1];
+    if (c0 >= c1) return;
+    const int n = c1 - c0;  // < 32
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < d.D * n; i += gridDim.y * blockDim.x) {
+        const int k = i / n, c = c0 + (i - k * n);
+        Thi[(long long)k * d.rows_pad + c] = 0.f;
+        Tlo[(long long)k * d.rows_pad + c] = 0.f;
+    }
+}
+
 // ---- the grouped GEMM ----------------------------------------------------------------------------------------------
 // Persistent CTAs over a device-built tile list.  Per tile: C[c_row .. +rows, c_col .. +cols] = (cmask o) A . B^T
 // (+ C when beta), A rows [a_row, +128) and B rows [b_row, +256) of the K-major split workspaces, K columns
@@ -744,11 +760,7 @@ static cudaError_t forward(const Dims& d, const Ws& w, const float* ent, const f
     weight_split_kernel<<<dim3(kt, kt, d.R), 256, 0, st>>>(W, mask, w.cnt, d.D, d.Kpad, backward ? w.Mhi : nullptr, w.Mlo,
                                                            w.Mthi, w.Mtlo);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    if (backward) {
-        const size_t tk = (size_t)d.D * d.rows_pad * sizeof(float);
-        if ((e = cudaMemsetAsync(w.XThi, 0, tk, st)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(w.XTlo, 0, tk, st)) != cudaSuccess) return e;
-    }
+    if (backward) pad_zero_kernel<<<dim3(d.R, 8), 256, 0, st>>>(w.cnt, w.padoff, d, w.XThi, w.XTlo);
     rows_split_kernel<true><<<dim3((unsigned)((d.rows + 31) / 32), kt), 256, 0, st>>>(
         ent, d.D, pos, neg, w.perm, w.off, w.padoff, d, w.row_ent, w.Xhi, w.Xlo, backward ? w.XThi : nullptr, w.XTlo);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
@@ -776,9 +788,7 @@ static cudaError_t backward(const Dims& d, const Ws& w, int64_t E, const float* 
     dscore_kernel<<<d.B, 32 * nw, smem_for(nw), st>>>(d, a);
     relation_grad_kernel<<<d.R, 256, 0, st>>>(w.GR, w.off, d.D, g_rel);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    const size_t tk = (size_t)d.D * d.rows_pad * sizeof(float);
-    if ((e = cudaMemsetAsync(w.dPThi, 0, tk, st)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(w.dPTlo, 0, tk, st)) != cudaSuccess) return e;
+    pad_zero_kernel<<<dim3(d.R, 8), 256, 0, st>>>(w.cnt, w.padoff, d, w.dPThi, w.dPTlo);
     const int kt = d.Kpad / 32;
     rows_split_kernel<false><<<dim3((unsigned)((d.rows + 31) / 32), kt), 256, 0, st>>>(
         w.P, d.Kpad, pos, nullptr, w.perm, w.off, w.padoff, d, nullptr, w.dPhi, w.dPlo, w.dPThi, w.dPTlo);
