@@ -91,6 +91,7 @@ class KGEModel(nn.Module):
         # B200 knobs (not in the reference API)
         self.deterministic = False  # fixed-order backward (exact-check runs)
         self.interht_eps = 0.0      # 0: tf.linalg.normalize; 1e-12: F.normalize
+        self.check_ids = False      # range-check every batch's ids (IndexError like index_select); synchronises
         self._ws: Dict[tuple, torch.Tensor] = {}
         self._scalars: Dict[str, tuple] = {}
         self._plan_key, self._plan_ok = None, False
@@ -140,6 +141,15 @@ class KGEModel(nn.Module):
             self._ws[key] = ws
         return ws
 
+    def _check_batch_ids(self, positive, negative):
+        """``check_ids``: ids against the table sizes -- on the host for host tensors (no copy, no sync), by
+        ``kge_check_ids`` for device tensors (synchronises the stream)."""
+        if positive.is_cuda:
+            ops.check_ids(positive, negative, self.nentity, self.nrelation)
+        else:
+            from .wire import check_id_ranges
+            check_id_ranges(positive, negative if negative is not None else positive[:, :1], self.nentity, self.nrelation)
+
     def forward(self, sample, mode="single"):
         """Raw scores ``[B,1]`` ('single') or ``[B,N]`` ('head-batch' / 'tail-batch') -- U2."""
         if mode == "single":
@@ -152,6 +162,8 @@ class KGEModel(nn.Module):
         if dev.type != "cuda":
             raise RuntimeError("KGEModel is on %s: the B200 kernels need the model on a CUDA device "
                                "(no CPU fallback)" % dev)
+        if self.check_ids:
+            self._check_batch_ids(positive, negative)
         positive = positive.to(dev, non_blocking=True)
         if negative is not None:
             negative = negative.to(dev, non_blocking=True)
@@ -201,6 +213,8 @@ class KGEModel(nn.Module):
             positive_sample, negative_sample, subsampling_weight, mode = next(train_iterator)
         if mode not in ("head-batch", "tail-batch"):
             raise ValueError("mode %s not supported" % mode)
+        if model.check_ids:
+            model._check_batch_ids(positive_sample, negative_sample)
         adv = bool(getattr(args, "negative_adversarial_sampling", False))
         alpha = float(getattr(args, "adversarial_temperature", 1.0))
         uni = bool(getattr(args, "uni_weight", False))

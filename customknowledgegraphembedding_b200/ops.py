@@ -122,6 +122,24 @@ def loss_forward_backward(negative_score, positive_score, subsampling_weight, *,
     return loss3, dneg, dpos
 
 
+def check_ids(positive, negative, nentity: int, nrelation: int) -> None:
+    """Device-side range check of a batch (kge_check_ids): IndexError as ``index_select`` / ``tf.gather`` would raise.
+    Synchronises the stream -- a debugging switch (``model.check_ids = True``), not part of the timed path."""
+    lib = _lib.load()
+    positive = _need_cuda("positive_sample", positive, torch.int64)
+    B = positive.shape[0]
+    N = 0
+    if negative is not None:
+        negative = _need_cuda("negative_sample", negative, torch.int64)
+        N = negative.shape[1]
+    scratch = torch.empty(4, dtype=torch.int64, device=positive.device)
+    with torch.cuda.device(positive.device):
+        rc = lib.kge_check_ids(_ptr(positive), _ptr(negative), B, N, int(nentity), int(nrelation), _ptr(scratch), _stream())
+    if rc == _lib.KGE_ERR_INVALID_ARGUMENT:
+        raise IndexError(lib.kge_last_error().decode())
+    _lib.check(rc, "kge_check_ids")
+
+
 def l3_sum_cubes(x: torch.Tensor) -> torch.Tensor:
     lib = _lib.load()
     x = _need_cuda("x", x, torch.float32)

@@ -72,6 +72,7 @@ class TranSparseModel(nn.Module):
         prob = torch.empty(nrelation, hidden_dim, hidden_dim).uniform_(1, 100)                           # model.py:101
         self.register_buffer("mask", (prob >= 50).float())                                              # model.py:99-103
         self._gamma_py = float(gamma)
+        self.check_ids = False  # range-check every batch's ids on the device (kge_check_ids; synchronises)
         self._free = {}      # (mode, B, N, with_backward) -> workspaces not in use
         self._grads = None   # persistent dense gradient buffers of the fused train steps
 
@@ -112,6 +113,8 @@ class TranSparseModel(nn.Module):
                 raise ValueError("negative_sample must be [B, N]")
         else:
             negative = None
+        if self.check_ids:
+            ops.check_ids(positive, negative, self.nentity, self.nrelation)
         return positive, negative
 
     def _forward_raw(self, positive, negative, mode, with_backward):

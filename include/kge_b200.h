@@ -470,6 +470,14 @@ KGE_API int kge_transparse_backward(const kge_transparse_desc *desc, int mode, c
                                     const float *dnegative, float *grad_entity, float *grad_relation, float *grad_W,
                                     void *ws, size_t ws_bytes, void *stream);
 
+/* Optional device-side range check of a batch (no reference counterpart as a call: tf.gather / index_select raise on an
+ * out-of-range id, the row gathers here would read -- and the Adam bucket build write -- out of bounds).  positive
+ * [B,3], negative [B,N] (may be NULL with N = 0) on the device; scratch32: 32 device bytes.  SYNCHRONOUS: waits for the
+ * stream and returns KGE_ERR_INVALID_ARGUMENT with the count and an example id in kge_last_error().  Switched on per
+ * model (KGEModel.check_ids / TranSparseModel.check_ids) while a data pipeline is brought up; off by default. */
+KGE_API int kge_check_ids(const int64_t *positive, const int64_t *negative, int64_t B, int64_t N, int64_t nentity,
+                          int64_t nrelation, void *scratch32, void *stream);
+
 /* Measurement probe (bench.py `roofline.l2`; no reference counterpart): a persistent grid re-reads `bytes` of `buf`
  * (device, 16-byte aligned, should fit L2: 32 MB) `iters` times with L2-only 128-bit loads; *bytes_read (host) = bytes
  * requested from L2 in total.  The caller times the call with events on `stream`.  sink: one device float. */

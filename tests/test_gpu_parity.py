@@ -369,3 +369,33 @@ def test_train_step_input_lookahead():
         want = type(ref).train_step(ref, ropt, iter([batches[k // 2 if it is it_a else 3 + k // 2]]), args)
         assert got == want
     assert torch.equal(gm.entity_embedding, ref.entity_embedding)
+
+
+def test_check_ids_switch_raises_like_index_select():
+    """ids are range-checked on request -- on the device for device batches (kge_check_ids), on the host for
+    host batches; the message names the table size, the count and an offending id."""
+    import customknowledgegraphembedding_b200 as kb
+    from customknowledgegraphembedding_b200 import ops
+    E, R = 50, 4
+    pos, neg, w, mode = ko.synthetic_batch(E, R, 8, 16, seed=4)
+    ops.check_ids(pos.cuda(), neg.cuda(), E, R)          # in range: returns
+    ops.check_ids(pos.cuda(), None, E, R)
+    bad_neg = neg.clone()
+    bad_neg[3, 5], bad_neg[7, 0] = E, -1
+    with pytest.raises(IndexError, match=r"entity id out of range \[0, 50\): 2 ids"):
+        ops.check_ids(pos.cuda(), bad_neg.cuda(), E, R)
+    bad_pos = pos.clone()
+    bad_pos[2, 1] = R + 3
+    with pytest.raises(IndexError, match=r"relation id out of range \[0, 4\): 1 ids of the batch, e.g. 7"):
+        ops.check_ids(bad_pos.cuda(), neg.cuda(), E, R)
+    m = kb.KGEModel("TransE", E, R, 8, 12.0).cuda()
+    m.check_ids = True
+    m((pos.cuda(), neg.cuda()), "head-batch")
+    with pytest.raises(IndexError):
+        m((pos.cuda(), bad_neg.cuda()), "head-batch")
+    with pytest.raises(IndexError):
+        m((bad_pos, neg), "tail-batch")              # host batch: checked on the host
+    args = ko.Args(negative_adversarial_sampling=True, adversarial_temperature=1.0, cuda=True)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    with pytest.raises(IndexError):
+        kb.KGEModel.train_step(m, opt, iter([(pos.cuda(), bad_neg.cuda(), w.cuda(), mode)]), args)
