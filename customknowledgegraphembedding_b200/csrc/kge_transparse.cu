@@ -23,6 +23,7 @@
 //
 // No CPU path; fp32 in and out; the three GEMMs keep fp32-level accuracy through the operand split.
 #include <climits>
+#include <cstdlib>
 
 #include "kge_umma.cuh"
 
@@ -74,7 +75,8 @@ static bool make_dims(const kge_transparse_desc& d, int mode, int64_t B, int64_t
     x.rows_pad = ((x.rows + 31) / 32) * 32 + 32 * nseg + 32;
     x.nct = ceil_div(x.D, BN);
     x.nkt = ceil_div(x.D, BM);
-    const long long t1 = ((x.rows + BM - 1) / BM + nseg) * x.nct, t3 = nseg * x.nkt * x.nct;
+    // tile lists are padded to PAIRS of tiles that share their B tile (the CTA pair of gemm3x_pair_kernel)
+    const long long t1 = ((x.rows + BM - 1) / BM + 2 * nseg) * x.nct, t3 = nseg * (x.nkt + 1) * x.nct;
     if (x.rows_pad >= INT_MAX || (long long)x.R * x.D >= INT_MAX || t1 >= INT_MAX || t3 >= INT_MAX) return false;
     x.max_tiles1 = (int)t1;
     x.max_tiles3 = (int)t3;
@@ -134,7 +136,8 @@ __device__ __forceinline__ int4 add4(int4 a, int4 b) { return make_int4(a.x + b.
 
 __device__ __forceinline__ int4 seg_values(int c, int rpp) {
     const long long rows = (long long)c * rpp;
-    return make_int4(c, (int)((rows + BM - 1) / BM), (int)(((rows + 31) / 32) * 32), c > 0 ? 1 : 0);
+    const int nrt = (int)((rows + BM - 1) / BM);
+    return make_int4(c, (nrt + 1) & ~1, (int)(((rows + 31) / 32) * 32), c > 0 ? 1 : 0);
 }
 
 // One CTA.  off[r]: first sorted positive of relation r; rtoff[r]: first row tile; padoff[r]: first column of the
@@ -173,7 +176,7 @@ plan_kernel(const int64_t* __restrict__ pos, Dims d, int* cnt, int* off, int* pa
         const int4 tot = s_scan[tid];
         off[d.R] = tot.x, rtoff[d.R] = tot.y, padoff[d.R] = tot.z, g3off[d.R] = tot.w;
         ntiles[0] = tot.y * d.nct;
-        ntiles[1] = tot.w * d.nkt * d.nct;
+        ntiles[1] = tot.w * ((d.nkt + 1) & ~1) * d.nct;
     }
     __syncthreads();
     // stable counting sort of the positives by relation, 1024 at a time
@@ -202,35 +205,38 @@ plan_kernel(const int64_t* __restrict__ pos, Dims d, int* cnt, int* off, int* pa
         const int c = cnt[r];
         if (c == 0) continue;
         const long long rows = (long long)c * d.rpp, row0 = (long long)off[r] * d.rpp;
-        const int nrt = (int)((rows + BM - 1) / BM);
+        const int nrt = (int)((rows + BM - 1) / BM), nrt2 = (nrt + 1) & ~1;
         Tile* t1 = tiles1 + (long long)rtoff[r] * d.nct;
         for (int ct = 0; ct < d.nct; ++ct)
-            for (int rt = 0; rt < nrt; ++rt) {  // row tile fastest: concurrent CTAs share the B tile
+            for (int rt = 0; rt < nrt2; ++rt) {  // row tile fastest: tiles 2p, 2p + 1 share the B tile
+                const int rr = min(rt, nrt - 1);  // (odd count: the pair's second tile repeats the first and stores nothing)
                 Tile t;
-                t.a_row = (int)(row0 + (long long)rt * BM);
+                t.a_row = (int)(row0 + (long long)rr * BM);
                 t.b_row = r * d.D + ct * BN;
                 t.k0 = 0;
                 t.nkb = d.Kpad / BK;
                 t.c_row = t.a_row;
                 t.c_col = ct * BN;
-                t.rows = (int)min((long long)BM, rows - (long long)rt * BM);
+                t.rows = (rt < nrt) ? (int)min((long long)BM, rows - (long long)rt * BM) : 0;
                 t.cols = min(BN, d.D - ct * BN);
-                t1[ct * nrt + rt] = t;
+                t1[ct * nrt2 + rt] = t;
             }
-        Tile* t3 = tiles3 + (long long)g3off[r] * d.nkt * d.nct;
+        const int nkt2 = (d.nkt + 1) & ~1;
+        Tile* t3 = tiles3 + (long long)g3off[r] * nkt2 * d.nct;
         const int kpadrows = (int)(((rows + 31) / 32) * 32);
         for (int jt = 0; jt < d.nct; ++jt)
-            for (int kt = 0; kt < d.nkt; ++kt) {
+            for (int kt = 0; kt < nkt2; ++kt) {
+                const int kk = min(kt, d.nkt - 1);
                 Tile t;
-                t.a_row = kt * BM;
+                t.a_row = kk * BM;
                 t.b_row = jt * BN;
                 t.k0 = padoff[r];
                 t.nkb = kpadrows / BK;
-                t.c_row = r * d.D + kt * BM;
+                t.c_row = r * d.D + kk * BM;
                 t.c_col = jt * BN;
-                t.rows = min(BM, d.D - kt * BM);
+                t.rows = (kt < d.nkt) ? min(BM, d.D - kt * BM) : 0;
                 t.cols = min(BN, d.D - jt * BN);
-                t3[jt * d.nkt + kt] = t;
+                t3[jt * nkt2 + kt] = t;
             }
     }
 }
@@ -401,6 +407,7 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 const Tile t = a.tiles[tile];
+                if (t.rows == 0) continue;  // the filler of an odd pair (gemm3x_pair_kernel needs it)
                 for (int kb = 0; kb < t.nkb; ++kb, ++it) {
                     const int s = it % STAGES;
                     mbar_wait(empty(s), ((it / STAGES) & 1u) ^ 1u);
@@ -418,7 +425,8 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
         if (lane == 0) {
             // ===== MMA issuer =====
             uint32_t it = 0, tcount = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                if (a.tiles[tile].rows == 0) continue;
                 const int nkb = a.tiles[tile].nkb;
                 const int acc = tcount & 1u;
                 mbar_wait(tempty(acc), ((tcount >> 1) & 1u) ^ 1u);
@@ -440,6 +448,7 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
                     umma_commit(empty(s));
                 }
                 umma_commit(tfull(acc));
+                ++tcount;
             }
         }
     } else {
@@ -449,8 +458,9 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
         const bool vec = (a.pitch % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.C) & 15) == 0) &&
                          (a.cmask == nullptr || (reinterpret_cast<uintptr_t>(a.cmask) & 15) == 0);
         uint32_t tcount = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const Tile t = a.tiles[tile];
+            if (t.rows == 0) continue;
             const int acc = tcount & 1u;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
             const long long o0 = (long long)(t.c_row + row) * a.pitch + t.c_col;
@@ -495,6 +505,7 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty(acc));
+            ++tcount;
         }
     }
     __syncwarp();
@@ -504,6 +515,172 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
         __syncwarp();
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// The same GEMM on CTA PAIRS (cta_group::2): the two tiles of a pair (same B tile, two A tiles) are one 256 x 256 tile of the
+// pair.  Each CTA stages its own A tile and half of the B tile -- 64 KB per k-stage and SM instead of 96 KB, which is what
+// bounds the one-CTA kernel (ncu: 7.2 GB from L2 per GEMM at 10.7 TB/s, tensor pipe 52 % active) -- in a 3-stage ring.
+// Both producers signal the LEADER's `full` barrier (the leader issues every MMA); the leader's commits reach both CTAs'
+// `empty` / `tfull` barriers; both CTAs' epilogue warps release the accumulator on the leader's `tempty`.
+constexpr int STAGES2 = 3;
+constexpr uint32_t BH_BYTES = (BN / 2) * BK * 4;               // this CTA's half of the B tile (hi or lo): 16 KB
+constexpr uint32_t STAGE2_BYTES = 2 * A_BYTES + 2 * BH_BYTES;  // 64 KB
+constexpr uint32_t SMEM2_BYTES = 1024 + STAGES2 * STAGE2_BYTES + 128;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm3x_pair_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
+                   const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo, const GemmArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + STAGES2 * STAGE2_BYTES;
+    auto full = [&](int s) { return bars + 8u * s; };
+    auto empty = [&](int s) { return bars + 24u + 8u * s; };
+    auto tfull = [&](int s) { return bars + 48u + 8u * s; };
+    auto tempty = [&](int s) { return bars + 64u + 8u * s; };
+    const uint32_t tmem_slot = bars + 80u;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmAhi);
+        tma_prefetch_desc(&tmAlo);
+        tma_prefetch_desc(&tmBhi);
+        tma_prefetch_desc(&tmBlo);
+        for (int s = 0; s < STAGES2; ++s) {
+            mbar_init(full(s), 1);   // the leader's arrive.expect_tx (bytes of both CTAs)
+            mbar_init(empty(s), 1);  // the leader's commit, delivered to both CTAs
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(tfull(s), 1);   // the leader's commit, delivered to both CTAs
+            mbar_init(tempty(s), 8);  // one lane of each epilogue warp of both CTAs (used on the leader only)
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    cluster_sync_all();  // the peer's barriers and TMEM exist before anything is sent to them
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    const int ntiles = *a.ntiles;  // even: pairs
+    const int first = 2 * (int)cluster_id_x(), stride = 2 * (int)cluster_count_x();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer (both CTAs) =====
+            uint32_t it = 0;
+            for (int tile0 = first; tile0 < ntiles; tile0 += stride) {
+                const Tile t = a.tiles[tile0 + crank];
+                for (int kb = 0; kb < t.nkb; ++kb, ++it) {
+                    const int s = it % STAGES2;
+                    mbar_wait(empty(s), ((it / STAGES2) & 1u) ^ 1u);
+                    if (crank == 0) mbar_arrive_expect_tx(full(s), 2 * STAGE2_BYTES);
+                    const uint32_t lf = map_to_rank(full(s), 0);
+                    const uint32_t st = base + s * STAGE2_BYTES;
+                    const int kc = t.k0 + kb * BK;
+                    tma_load_2d_pair(st, &tmAhi, lf, kc, t.a_row);
+                    tma_load_2d_pair(st + A_BYTES, &tmAlo, lf, kc, t.a_row);
+                    tma_load_2d_pair(st + 2 * A_BYTES, &tmBhi, lf, kc, t.b_row + (int)crank * (BN / 2));
+                    tma_load_2d_pair(st + 2 * A_BYTES + BH_BYTES, &tmBlo, lf, kc, t.b_row + (int)crank * (BN / 2));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && crank == 0) {
+            // ===== MMA issuer (leader only) =====
+            uint32_t it = 0, tcount = 0;
+            for (int tile0 = first; tile0 < ntiles; tile0 += stride, ++tcount) {
+                const int nkb = a.tiles[tile0].nkb;
+                const int acc = tcount & 1u;
+                mbar_wait(tempty(acc), ((tcount >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d = tmem_base + acc * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % STAGES2;
+                    mbar_wait(full(s), (it / STAGES2) & 1u);
+                    tc_fence_after();
+                    const uint32_t st = base + s * STAGE2_BYTES;
+                    const uint64_t ahi = umma_desc_sw128(st), alo = umma_desc_sw128(st + A_BYTES);
+                    const uint64_t bhi = umma_desc_sw128(st + 2 * A_BYTES), blo = umma_desc_sw128(st + 2 * A_BYTES + BH_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, alo + 2 * k, bhi + 2 * k, (kb | k) != 0);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, ahi + 2 * k, blo + 2 * k, 1u);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, ahi + 2 * k, bhi + 2 * k, 1u);
+                    umma_commit_pair(empty(s));
+                }
+                umma_commit_pair(tfull(acc));
+            }
+        }
+    } else {
+        // ===== epilogue (both CTAs): this CTA's 128 accumulator rows = its own tile of the pair =====
+        const int wq = warp & 3;
+        const int row = wq * 32 + lane;
+        const bool vec = (a.pitch % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.C) & 15) == 0) &&
+                         (a.cmask == nullptr || (reinterpret_cast<uintptr_t>(a.cmask) & 15) == 0);
+        uint32_t tcount = 0;
+        for (int tile0 = first; tile0 < ntiles; tile0 += stride, ++tcount) {
+            const Tile t = a.tiles[tile0 + crank];
+            const int acc = tcount & 1u;
+            const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
+            const long long o0 = (long long)(t.c_row + row) * a.pitch + t.c_col;
+            const bool rok = row < t.rows;
+            mbar_wait(tfull(acc), (tcount >> 1) & 1u);
+            tc_fence_after();
+            if (t.rows > 0) {
+#pragma unroll 1
+                for (int c = 0; c * 32 < t.cols; ++c) {
+                    float v[32];
+                    __syncwarp();
+                    tmem_ld32(taddr + c * 32, v);
+                    if (!rok) continue;
+                    const int ncol = min(32, t.cols - c * 32);
+                    float* crow = a.C + o0 + c * 32;
+                    const float* mrow = a.cmask ? a.cmask + o0 + c * 32 : nullptr;
+                    if (vec && ncol == 32) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 x = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                            if (mrow != nullptr) {
+                                const float4 m = __ldg(reinterpret_cast<const float4*>(mrow + j));
+                                x.x *= m.x, x.y *= m.y, x.z *= m.z, x.w *= m.w;
+                            }
+                            if (a.beta) {
+                                const float4 y = *reinterpret_cast<const float4*>(crow + j);
+                                x.x += y.x, x.y += y.y, x.z += y.z, x.w += y.w;
+                            }
+                            *reinterpret_cast<float4*>(crow + j) = x;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (j < ncol) {
+                                float x = v[j];
+                                if (mrow != nullptr) x *= __ldg(mrow + j);
+                                if (a.beta) x += crow[j];
+                                crow[j] = x;
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(map_to_rank(tempty(acc), 0));
+        }
+    }
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();  // no CTA leaves (or frees its TMEM) while its peer may still use it
+    if (warp == 1) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, TMEM_COLS);
     }
 }
 
@@ -726,6 +903,15 @@ scatter_rows_kernel(const float* __restrict__ dX, int Kpad, const int* __restric
 }
 
 // ---- host side ---------------------------------------------------------------------------------------------------
+static int g_pair = -1;  // 1 (default): gemm3x_pair_kernel on CTA pairs; 0 (KGE_TS_PAIR=0): one CTA per tile
+static int gemm_pair() {
+    if (g_pair < 0) {
+        const char* v = getenv("KGE_TS_PAIR");
+        g_pair = (v != nullptr && v[0] == '0') ? 0 : 1;
+    }
+    return g_pair;
+}
+
 static cudaError_t run_gemm(const float* Ahi, const float* Alo, long long a_rows, long long a_inner, const float* Bhi,
                             const float* Blo, long long b_rows, long long b_inner, const Tile* tiles, const int* ntiles,
                             int max_tiles, float* C, long long pitch, const float* cmask, int beta, cudaStream_t st) {
@@ -733,15 +919,21 @@ static cudaError_t run_gemm(const float* Ahi, const float* Alo, long long a_rows
     cudaError_t e;
     if (!attr_set) {
         if ((e = cudaFuncSetAttribute(gemm3x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(gemm3x_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM2_BYTES)) != cudaSuccess) return e;
         attr_set = true;
     }
+    const bool pair = gemm_pair() != 0;
     CUtensorMap tAhi, tAlo, tBhi, tBlo;
+    const int bbox = pair ? BN / 2 : BN;  // a CTA of a pair stages half of the B tile
     if (!make_tmap(&tAhi, Ahi, a_rows, (int)a_inner, BM) || !make_tmap(&tAlo, Alo, a_rows, (int)a_inner, BM) ||
-        !make_tmap(&tBhi, Bhi, b_rows, (int)b_inner, BN) || !make_tmap(&tBlo, Blo, b_rows, (int)b_inner, BN))
+        !make_tmap(&tBhi, Bhi, b_rows, (int)b_inner, bbox) || !make_tmap(&tBlo, Blo, b_rows, (int)b_inner, bbox))
         return cudaErrorNotSupported;
     GemmArgs g{tiles, ntiles, C, pitch, cmask, beta};
-    const int grid = std::max(1, std::min(max_tiles, sm_count()));
-    gemm3x_kernel<<<grid, kGemmThreads, SMEM_BYTES, st>>>(tAhi, tAlo, tBhi, tBlo, g);
+    const int grid = std::max(2, std::min(max_tiles, sm_count()) & ~1);
+    if (pair)
+        gemm3x_pair_kernel<<<grid, kGemmThreads, SMEM2_BYTES, st>>>(tAhi, tAlo, tBhi, tBlo, g);
+    else
+        gemm3x_kernel<<<grid, kGemmThreads, SMEM_BYTES, st>>>(tAhi, tAlo, tBhi, tBlo, g);
     return cudaGetLastError();
 }
 
