@@ -23,6 +23,7 @@
 //   schedule    persistent CTAs (one per SM), tile = (entity tile, query tile) with the query tile fastest so
 //               that concurrently running CTAs share the B tile in L2.
 #include <climits>
+#include <cstdlib>
 
 #include "kge_umma.cuh"
 
@@ -98,90 +99,133 @@ struct TileArgs {
     unsigned long long* n_equal;
 };
 
-template <bool DIAG>
+// PAIR (count mode only): clusters of two CTAs work on two query tiles against the same entity tile as ONE 256 x 256 tile
+// (tcgen05.mma.cta_group::2): each CTA stages its own 128 queries and HALF of the entity tile -- 64 KB instead of 96 KB per
+// k-stage and SM, three stages instead of two.  The one-CTA kernel is bound by those L2 -> SM bytes, not by the tensor
+// pipe (kge_transparse.cu has the same pipeline with a store epilogue and the measurements).  Protocol: both producers
+// signal the LEADER's `full` barrier, the leader issues every MMA, its commits reach both CTAs' `empty` / `tfull` barriers,
+// both CTAs' epilogue warps release the accumulator on the leader's `tempty`.
+template <bool DIAG, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 eval_mma_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
                 const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo, const TileArgs a) {
+    static_assert(!(DIAG && PAIR), "the true-score pass has no shared B tile");
+    constexpr int NST = PAIR ? STAGES2 : STAGES;
+    constexpr uint32_t STB = PAIR ? STAGE2_BYTES : STAGE_BYTES;
+    constexpr uint32_t BHALF = PAIR ? BH_BYTES : B_BYTES;  // bytes of the B block (hi or lo) this CTA stages
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms are 1024-byte aligned
-    const uint32_t bars = base + STAGES * STAGE_BYTES;
-    // barriers: full[s] @ +0, empty[s] @ +16, tfull[a] @ +32, tempty[a] @ +48, TMEM base address @ +64
+    const uint32_t bars = base + NST * STB;
+    // barriers: full[s] @ +0, empty[s] @ +24, tfull[a] @ +48, tempty[a] @ +64, TMEM base address @ +80
     auto full = [&](int s) { return bars + 8u * s; };
-    auto empty = [&](int s) { return bars + 16u + 8u * s; };
-    auto tfull = [&](int s) { return bars + 32u + 8u * s; };
-    auto tempty = [&](int s) { return bars + 48u + 8u * s; };
-    const uint32_t tmem_slot = bars + 64u;
+    auto empty = [&](int s) { return bars + 24u + 8u * s; };
+    auto tfull = [&](int s) { return bars + 48u + 8u * s; };
+    auto tempty = [&](int s) { return bars + 64u + 8u * s; };
+    const uint32_t tmem_slot = bars + 80u;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t crank = 0;
+    if constexpr (PAIR) crank = cluster_ctarank();
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmAhi);
         tma_prefetch_desc(&tmAlo);
         tma_prefetch_desc(&tmBhi);
         tma_prefetch_desc(&tmBlo);
-        for (int s = 0; s < STAGES; ++s) {
-            mbar_init(full(s), 1);   // the producer's arrive.expect_tx
+        for (int s = 0; s < NST; ++s) {
+            mbar_init(full(s), 1);   // the (leader's) producer's arrive.expect_tx
             mbar_init(empty(s), 1);  // tcgen05.commit of the MMA thread
         }
         for (int s = 0; s < 2; ++s) {
-            mbar_init(tfull(s), 1);   // tcgen05.commit after the last k-block
-            mbar_init(tempty(s), 4);  // one lane of each epilogue warp
+            mbar_init(tfull(s), 1);              // tcgen05.commit after the last k-block
+            mbar_init(tempty(s), PAIR ? 8 : 4);  // one lane of each epilogue warp (of both CTAs of a pair)
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+    if (warp == 1) {
+        if constexpr (PAIR) tmem_alloc_pair(tmem_slot, TMEM_COLS);
+        else tmem_alloc(tmem_slot, TMEM_COLS);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if constexpr (PAIR) cluster_sync_all();  // the peer's barriers and TMEM exist before anything is sent to them
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-    const int ntiles = DIAG ? a.nqt : a.nqt * a.net;
+    // work items: DIAG one per query tile; count mode one per (entity tile, query tile), the query tile fastest; PAIR one
+    // per (entity tile, PAIR of query tiles) and cluster -- this CTA takes query tile 2 * pair + rank (a tile past the last
+    // query reads zeros and counts nothing)
+    const int hq = (a.nqt + 1) / 2;
+    const int nwork = DIAG ? a.nqt : (PAIR ? hq * a.net : a.nqt * a.net);
+    const int w0 = PAIR ? (int)cluster_id_x() : (int)blockIdx.x, wstride = PAIR ? (int)cluster_count_x() : (int)gridDim.x;
+    auto tile_qt = [&](int w) { return DIAG ? w : (PAIR ? 2 * (w % hq) + (int)crank : w % a.nqt); };
+    auto tile_et = [&](int w) { return PAIR ? w / hq : w / a.nqt; };
 
     if (warp == 0) {
         if (lane == 0) {
             // ===== TMA producer =====
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const int qt = DIAG ? tile : tile % a.nqt;
-                const int brow = DIAG ? qt * BM : (tile / a.nqt) * BN;
+            for (int w = w0; w < nwork; w += wstride) {
+                const int qt = tile_qt(w);
+                const int brow = DIAG ? qt * BM : tile_et(w) * BN + (PAIR ? (int)crank * (BN / 2) : 0);
                 for (int kb = 0; kb < a.nkb; ++kb, ++it) {
-                    const int s = it % STAGES;
-                    mbar_wait(empty(s), ((it / STAGES) & 1u) ^ 1u);
-                    mbar_arrive_expect_tx(full(s), STAGE_BYTES);
-                    const uint32_t st = base + s * STAGE_BYTES;
-                    tma_load_2d(st, &tmAhi, full(s), kb * BK, qt * BM);
-                    tma_load_2d(st + A_BYTES, &tmAlo, full(s), kb * BK, qt * BM);
-                    tma_load_2d(st + 2 * A_BYTES, &tmBhi, full(s), kb * BK, brow);
-                    tma_load_2d(st + 2 * A_BYTES + B_BYTES, &tmBlo, full(s), kb * BK, brow);
+                    const int s = it % NST;
+                    mbar_wait(empty(s), ((it / NST) & 1u) ^ 1u);
+                    const uint32_t st = base + s * STB;
+                    if constexpr (PAIR) {
+                        if (crank == 0) mbar_arrive_expect_tx(full(s), 2 * STB);  // the bytes of both CTAs
+                        const uint32_t lf = map_to_rank(full(s), 0);
+                        tma_load_2d_pair(st, &tmAhi, lf, kb * BK, qt * BM);
+                        tma_load_2d_pair(st + A_BYTES, &tmAlo, lf, kb * BK, qt * BM);
+                        tma_load_2d_pair(st + 2 * A_BYTES, &tmBhi, lf, kb * BK, brow);
+                        tma_load_2d_pair(st + 2 * A_BYTES + BHALF, &tmBlo, lf, kb * BK, brow);
+                    } else {
+                        mbar_arrive_expect_tx(full(s), STB);
+                        tma_load_2d(st, &tmAhi, full(s), kb * BK, qt * BM);
+                        tma_load_2d(st + A_BYTES, &tmAlo, full(s), kb * BK, qt * BM);
+                        tma_load_2d(st + 2 * A_BYTES, &tmBhi, full(s), kb * BK, brow);
+                        tma_load_2d(st + 2 * A_BYTES + BHALF, &tmBlo, full(s), kb * BK, brow);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
+        if (lane == 0 && crank == 0) {
+            // ===== MMA issuer (the leader's, in a pair) =====
             uint32_t it = 0, tcount = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+            for (int w = w0; w < nwork; w += wstride, ++tcount) {
                 const int acc = tcount & 1u;
                 mbar_wait(tempty(acc), ((tcount >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 const uint32_t d = tmem_base + acc * BN;
                 for (int kb = 0; kb < a.nkb; ++kb, ++it) {
-                    const int s = it % STAGES;
-                    mbar_wait(full(s), (it / STAGES) & 1u);
+                    const int s = it % NST;
+                    mbar_wait(full(s), (it / NST) & 1u);
                     tc_fence_after();
-                    const uint32_t st = base + s * STAGE_BYTES;
+                    const uint32_t st = base + s * STB;
                     const uint64_t ahi = umma_desc_sw128(st), alo = umma_desc_sw128(st + A_BYTES);
-                    const uint64_t bhi = umma_desc_sw128(st + 2 * A_BYTES), blo = umma_desc_sw128(st + 2 * A_BYTES + B_BYTES);
+                    const uint64_t bhi = umma_desc_sw128(st + 2 * A_BYTES), blo = umma_desc_sw128(st + 2 * A_BYTES + BHALF);
                     // small terms first: lo*hi, hi*lo, then hi*hi
+                    if constexpr (PAIR) {
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, alo + 2 * k, bhi + 2 * k, (kb | k) != 0);
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, alo + 2 * k, bhi + 2 * k, (kb | k) != 0);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, blo + 2 * k, 1u);
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, ahi + 2 * k, blo + 2 * k, 1u);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, bhi + 2 * k, 1u);
-                    umma_commit(empty(s));  // frees the stage once these MMAs have read it
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32_pair(d, ahi + 2 * k, bhi + 2 * k, 1u);
+                        umma_commit_pair(empty(s));
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, alo + 2 * k, bhi + 2 * k, (kb | k) != 0);
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, blo + 2 * k, 1u);
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d, ahi + 2 * k, bhi + 2 * k, 1u);
+                        umma_commit(empty(s));  // frees the stage once these MMAs have read it
+                    }
                 }
-                umma_commit(tfull(acc));  // accumulator complete
+                if constexpr (PAIR) umma_commit_pair(tfull(acc));
+                else umma_commit(tfull(acc));  // accumulator complete
             }
         }
     } else {
@@ -189,9 +233,9 @@ eval_mma_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
         const int wq = warp & 3;
         const int row = wq * 32 + lane;
         uint32_t tcount = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tcount) {
+        for (int w = w0; w < nwork; w += wstride, ++tcount) {
             const int acc = tcount & 1u;
-            const int qt = DIAG ? tile : tile % a.nqt;
+            const int qt = tile_qt(w);
             const long long q = (long long)qt * BM + row;
             const bool qok = q < a.Q;
             const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + acc * BN;
@@ -205,7 +249,7 @@ eval_mma_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
                 for (int j = 0; j < 32; ++j) s = (j == lane) ? v[j] : s;
                 if (qok) a.true_score[q] = s;
             } else {
-                const long long e0 = a.b_row_id0 + (long long)(tile / a.nqt) * BN;  // global id of column 0
+                const long long e0 = a.b_row_id0 + (long long)tile_et(w) * BN;  // global id of column 0
                 const long long e_end = a.b_row_id0 + a.b_rows;
                 float t = 0.f;
                 int te = -1, cur = 0, fe = 0, nextf = INT_MAX;
@@ -267,16 +311,21 @@ eval_mma_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty(acc));
+            if (lane == 0) {
+                if constexpr (PAIR) mbar_arrive_cluster(map_to_rank(tempty(acc), 0));
+                else mbar_arrive(tempty(acc));
+            }
         }
     }
     __syncwarp();
     tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) cluster_sync_all();  // no CTA leaves (or frees its TMEM) while its peer may still use it
     if (warp == 1) {
         __syncwarp();
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        if constexpr (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+        else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -308,6 +357,15 @@ static Layout layout(const Params& P, int64_t Q, int64_t nfilter) {
 }  // namespace mma
 
 static int g_tensor_path = 1;
+// CTA pairs in the counting pass (default); KGE_EVAL_PAIR=0 selects the one-CTA kernel
+static bool eval_pair() {
+    static int v = -1;
+    if (v < 0) {
+        const char* s = getenv("KGE_EVAL_PAIR");
+        v = (s != nullptr && s[0] == '0') ? 0 : 1;
+    }
+    return v != 0;
+}
 void eval_set_tensor_path(int on) { g_tensor_path = on ? 1 : 0; }
 bool eval_mma_applies(const Params& P) {
     return g_tensor_path && (P.model == KGE_DISTMULT || P.model == KGE_COMPLEX) && P.E < (1LL << 31);
@@ -341,8 +399,9 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
     }
     static bool attr_set = false;
     if (!attr_set) {
-        if ((e = cudaFuncSetAttribute(eval_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
-        if ((e = cudaFuncSetAttribute(eval_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(eval_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(eval_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES)) != cudaSuccess) return e;
+        if ((e = cudaFuncSetAttribute(eval_mma_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM2_BYTES)) != cudaSuccess) return e;
         attr_set = true;
     }
     const int nsm = sm_count();
@@ -379,18 +438,38 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
     a.n_equal = n_equal;
     // 4  true scores: the diagonal of Qs x T^T
     a.net = 1;
-    eval_mma_kernel<true><<<(unsigned)std::min(a.nqt, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmThi, tmTlo, a);
+    eval_mma_kernel<true, false><<<(unsigned)std::min(a.nqt, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmThi, tmTlo, a);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     // 5  candidates, one chunk of the split workspace at a time
     for (long long c0 = e_lo; c0 < e_hi; c0 += kEntityChunk) {
         const long long rows = std::min(kEntityChunk, e_hi - c0);
         split_rows_kernel<<<blocks_for(rows * (Kpad / 4)), 256, 0, st>>>(ent, P.De, c0, 1, nullptr, -1, rows, K, Kpad, Bhi, Blo);
-        if (!make_tmap(&tmBhi, Bhi, rows, Kpad, BN) || !make_tmap(&tmBlo, Blo, rows, Kpad, BN)) return cudaErrorNotSupported;
+        const bool pair = eval_pair();
+        const int bbox = pair ? BN / 2 : BN;  // a CTA of a pair stages half of the entity tile
+        if (!make_tmap(&tmBhi, Bhi, rows, Kpad, bbox) || !make_tmap(&tmBlo, Blo, rows, Kpad, bbox)) return cudaErrorNotSupported;
         a.b_row_id0 = c0;
         a.b_rows = rows;
         a.net = (int)((rows + BN - 1) / BN);
         const long long ntiles = (long long)a.nqt * a.net;
-        eval_mma_kernel<false><<<(unsigned)std::min<long long>(ntiles, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmBhi, tmBlo, a);
+        if (pair) {
+            // clusters of two CTAs, one work item per (entity tile, pair of query tiles)
+            const long long nwork = (long long)((a.nqt + 1) / 2) * a.net;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(2u * (unsigned)std::max<long long>(1, std::min<long long>(nwork, nsm / 2)));
+            cfg.blockDim = dim3(kThreads);
+            cfg.dynamicSmemBytes = SMEM2_BYTES;
+            cfg.stream = st;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            if ((e = cudaLaunchKernelEx(&cfg, eval_mma_kernel<false, true>, tmAhi, tmAlo, tmBhi, tmBlo, a)) != cudaSuccess) return e;
+        } else {
+            eval_mma_kernel<false, false><<<(unsigned)std::min<long long>(ntiles, nsm), kThreads, SMEM_BYTES, st>>>(tmAhi, tmAlo, tmBhi, tmBlo, a);
+        }
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     return cudaSuccess;

@@ -523,10 +523,6 @@ gemm3x_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__
 // bounds the one-CTA kernel (ncu: 7.2 GB from L2 per GEMM at 10.7 TB/s, tensor pipe 52 % active) -- in a 3-stage ring.
 // Both producers signal the LEADER's `full` barrier (the leader issues every MMA); the leader's commits reach both CTAs'
 // `empty` / `tfull` barriers; both CTAs' epilogue warps release the accumulator on the leader's `tempty`.
-constexpr int STAGES2 = 3;
-constexpr uint32_t BH_BYTES = (BN / 2) * BK * 4;               // this CTA's half of the B tile (hi or lo): 16 KB
-constexpr uint32_t STAGE2_BYTES = 2 * A_BYTES + 2 * BH_BYTES;  // 64 KB
-constexpr uint32_t SMEM2_BYTES = 1024 + STAGES2 * STAGE2_BYTES + 128;
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm3x_pair_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,

@@ -75,6 +75,10 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 // ---- CTA pair (cta_group::2): two SMs of a cluster work on ONE 256-row tile -----------------------------------------
 // Each CTA stages its 128 rows of A and HALF of the B tile; the leader's tcgen05.mma.cta_group::2 reads both CTAs' shared
 // memory and writes 128 accumulator rows into each CTA's TMEM.  Per SM and k-stage that is 64 KB instead of 96 KB.
+constexpr int STAGES2 = 3;
+constexpr uint32_t BH_BYTES = (BN / 2) * BK * 4;               // this CTA's half of the B tile (hi or lo): 16 KB
+constexpr uint32_t STAGE2_BYTES = 2 * A_BYTES + 2 * BH_BYTES;  // 64 KB
+constexpr uint32_t SMEM2_BYTES = 1024 + STAGES2 * STAGE2_BYTES + 128;
 constexpr uint32_t kIdescPair = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
