@@ -455,7 +455,9 @@ cudaError_t launch_eval_rank_mma(const Params& P, int mode, const float* ent, co
             // clusters of two CTAs, one work item per (entity tile, pair of query tiles)
             const long long nwork = (long long)((a.nqt + 1) / 2) * a.net;
             cudaLaunchConfig_t cfg{};
-            cfg.gridDim = dim3(2u * (unsigned)std::max<long long>(1, std::min<long long>(nwork, nsm / 2)));
+            static int pairs = 0;  // CTA pairs the device holds at once
+            if (pairs == 0) pairs = max_active_pairs(eval_mma_kernel<false, true>, kThreads, SMEM2_BYTES);
+            cfg.gridDim = dim3(2u * (unsigned)std::max<long long>(1, std::min<long long>(nwork, pairs)));
             cfg.blockDim = dim3(kThreads);
             cfg.dynamicSmemBytes = SMEM2_BYTES;
             cfg.stream = st;

@@ -886,10 +886,23 @@ relation_grad_kernel(const float* __restrict__ GR, const int* __restrict__ off, 
     }
 }
 
-// dX rows -> entity gradient rows (float atomics: the order of the uses of one entity is not fixed)
+// dX rows -> entity gradient rows (float atomics: the order of the uses of one entity is not fixed); four coordinates
+// per reduction (red.global.add.v4.f32) when the rows allow 16-byte accesses
 __global__ void __launch_bounds__(256)
 scatter_rows_kernel(const float* __restrict__ dX, int Kpad, const int* __restrict__ row_ent, long long rows, int D,
                     float* grad_ent) {
+    if ((D & 3) == 0 && (reinterpret_cast<uintptr_t>(grad_ent) & 15) == 0) {
+        const int d4 = D >> 2;
+        const long long total = rows * d4;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+            const long long row = i / d4;
+            const int j = (int)(i - row * d4) * 4;
+            const float4 v = *reinterpret_cast<const float4*>(dX + row * Kpad + j);
+            float* dst = grad_ent + (long long)row_ent[row] * D + j;
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+        }
+        return;
+    }
     const long long total = rows * D;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long row = i / D;
@@ -925,11 +938,15 @@ static cudaError_t run_gemm(const float* Ahi, const float* Alo, long long a_rows
         !make_tmap(&tBhi, Bhi, b_rows, (int)b_inner, bbox) || !make_tmap(&tBlo, Blo, b_rows, (int)b_inner, bbox))
         return cudaErrorNotSupported;
     GemmArgs g{tiles, ntiles, C, pitch, cmask, beta};
-    const int grid = std::max(2, std::min(max_tiles, sm_count()) & ~1);
-    if (pair)
+    if (pair) {
+        static int pairs = 0;  // CTA pairs the device holds at once
+        if (pairs == 0) pairs = max_active_pairs(gemm3x_pair_kernel, kGemmThreads, SMEM2_BYTES);
+        const int grid = 2 * std::max(1, std::min(max_tiles / 2, pairs));
         gemm3x_pair_kernel<<<grid, kGemmThreads, SMEM2_BYTES, st>>>(tAhi, tAlo, tBhi, tBlo, g);
-    else
+    } else {
+        const int grid = std::max(1, std::min(max_tiles, sm_count()));
         gemm3x_kernel<<<grid, kGemmThreads, SMEM_BYTES, st>>>(tAhi, tAlo, tBhi, tBlo, g);
+    }
     return cudaGetLastError();
 }
 

@@ -197,5 +197,29 @@ static inline bool make_tmap(CUtensorMap* tm, const float* ptr, long long rows, 
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// CTA pairs that can be resident at once for `kernel` (1 CTA per SM at `smem` bytes): the persistent pair kernels size
+// their grid with it -- a GPC with an odd number of free SMs leaves one idle, and a cluster that starts in a second wave
+// would stretch the tail of a persistent loop.
+template <typename K>
+static inline int max_active_pairs(K kernel, int threads, size_t smem) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2u * (unsigned)sm_count());
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = sm_count() / 2;
+    }
+    return n;
+}
+
 }  // namespace mma
 }  // namespace kge
