@@ -114,6 +114,8 @@ PROTOTYPES = {
                                          C.c_int, _P, _SZ, _P]),
     "kge_transparse_backward": (C.c_int, [C.POINTER(TranSparseDesc), C.c_int, _P, _P, _P, _I64, _I64, _P, _P, _P, _P, _P,
                                           _P, _SZ, _P]),
+    "kge_tf_call_terms": (C.c_int, [_P, _I64, _I64, C.c_int, _P, _P]),
+    "kge_tf_call_terms_backward": (C.c_int, [_P, _P, _I64, _I64, C.c_int, _P, _P]),
     "kge_check_ids": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _P, _P]),
     "kge_probe_l2_read": (C.c_int, [_P, _SZ, C.c_int, _P, C.POINTER(C.c_int64), _P]),
     "kge_profile_enable": (C.c_int, [C.c_int]),

@@ -681,26 +681,7 @@ gemm3x_pair_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_const
 }
 
 // ---- score / dscore: one CTA per (sorted) positive ---------------------------------------------------------------
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-// fixed-order block sum, result broadcast; red: 33 floats
-__device__ __forceinline__ float block_sum(float v, float* red) {
-    v = warp_sum(v);
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
-    __syncthreads();
-    if (l == 0) red[w] = v;
-    __syncthreads();
-    if (w == 0) {
-        float t = (l < nw) ? red[l] : 0.f;
-        t = warp_sum(t);
-        if (l == 0) red[32] = t;
-    }
-    __syncthreads();
-    return red[32];
-}
+// (warp_sum / block_sum: kge_common.cuh -- fixed combination order)
 __device__ __forceinline__ float sgn(float x) { return (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f); }
 
 struct ScoreArgs {

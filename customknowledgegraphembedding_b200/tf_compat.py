@@ -24,12 +24,39 @@ import time
 from collections import defaultdict
 
 import torch
-import torch.nn.functional as F
 
+from . import _lib, ops
 from .model import KGEModel
 from .transparse import TranSparseModel
 
 TF_MODE_HEAD_BATCH, TF_MODE_TAIL_BATCH, TF_MODE_SINGLE = 0, 1, 3
+
+
+class _CallTerms(torch.autograd.Function):
+    """The row reductions of ``TFKGEModel.call`` (model.py:145,168-171): kge_tf_call_terms and its backward."""
+
+    @staticmethod
+    def forward(ctx, score, single):
+        score = score.contiguous().float()
+        B, N = score.shape
+        out = torch.empty(B, 1, dtype=torch.float32, device=score.device)
+        with torch.cuda.device(score.device):
+            _lib.check(_lib.load().kge_tf_call_terms(ops._ptr(score), B, N, int(single), ops._ptr(out), ops._stream()),
+                       "kge_tf_call_terms")
+        ctx.save_for_backward(score)
+        ctx.single = single
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        (score,) = ctx.saved_tensors
+        B, N = score.shape
+        ds = torch.empty_like(score)
+        gout = gout.contiguous().float()
+        with torch.cuda.device(score.device):
+            _lib.check(_lib.load().kge_tf_call_terms_backward(ops._ptr(score), ops._ptr(gout), B, N, int(ctx.single),
+                                                              ops._ptr(ds), ops._stream()), "kge_tf_call_terms_backward")
+        return ds, None
 
 
 class TFKGEModel:
@@ -103,9 +130,9 @@ class TFKGEModel:
         positive_sample, negative_sample = sample
         name = self.mode_name(mode)
         if name == "single":
-            return F.logsigmoid(self.kge(positive_sample, "single"))          # model.py:144-145
-        s = self.kge((positive_sample, negative_sample), name)                # model.py:148-199
-        return (F.softmax(s * 1, dim=1) * F.logsigmoid(-s)).sum(dim=1, keepdim=True)
+            return _CallTerms.apply(self.kge(positive_sample, "single"), True)   # model.py:144-145
+        s = self.kge((positive_sample, negative_sample), name)                   # model.py:148-199
+        return _CallTerms.apply(s, False)                                        # model.py:168-171 / 195-198
 
     __call__ = call
 

@@ -470,6 +470,13 @@ KGE_API int kge_transparse_backward(const kge_transparse_desc *desc, int mode, c
                                     const float *dnegative, float *grad_entity, float *grad_relation, float *grad_W,
                                     void *ws, size_t ws_bytes, void *stream);
 
+/* The reductions of TFKGEModel.call on raw scores (tensorflow_codes/model.py:145 `log_sigmoid(single_score)`; :168-171,
+ * :195-198 `reduce_sum(softmax(s * 1, axis=1) * log_sigmoid(-s), axis=1)` -- temperature 1, NO stop-gradient on the
+ * softmax):  score [B, N] (N = 1 with single != 0) -> out [B];  backward: dscore [B, N] = gout[b] * d out[b] / d score. */
+KGE_API int kge_tf_call_terms(const float *score, int64_t B, int64_t N, int single, float *out, void *stream);
+KGE_API int kge_tf_call_terms_backward(const float *score, const float *gout, int64_t B, int64_t N, int single,
+                                       float *dscore, void *stream);
+
 /* Optional device-side range check of a batch (no reference counterpart as a call: tf.gather / index_select raise on an
  * out-of-range id, the row gathers here would read -- and the Adam bucket build write -- out of bounds).  positive
  * [B,3], negative [B,N] (may be NULL with N = 0) on the device; scratch32: 32 device bytes.  SYNCHRONOUS: waits for the
