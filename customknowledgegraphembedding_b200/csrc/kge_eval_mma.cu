@@ -22,6 +22,9 @@
 //               candidate with an identical row ties exactly (n_equal keeps its meaning).
 //   schedule    persistent CTAs (one per SM), tile = (entity tile, query tile) with the query tile fastest so
 //               that concurrently running CTAs share the B tile in L2.
+//   CTA pairs   (count mode, default) two CTAs of a cluster take two query tiles against one entity tile as ONE
+//               256 x 256 tile: tcgen05.mma.cta_group::2 issued by the leader, each CTA stages its queries and half
+//               of the entity tile (64 KB per stage and SM, 3 stages) -- see the PAIR comment at the kernel.
 #include <climits>
 #include <cstdlib>
 
