@@ -93,6 +93,48 @@ def test_readme_command_runs_the_tf_trainer(tmp_path, capsys):
         run.main(cmd.replace("--nentity %d" % E, "--nentity 50").split())
 
 
+@pytest.mark.gpu
+def test_tf_command_with_the_transparse_score_function(tmp_path, capsys):
+    """`-sf TranSparse` (tensorflow_codes/model.py:96-106,226-235) through the same command line: W and the mask are
+    built, the trainer steps all three variables, the first loss equals the oracle's on the same variables."""
+    from oracle import kge_oracle as ko
+    from customknowledgegraphembedding_b200 import wire
+    import customknowledgegraphembedding_b200.tf_compat as tfc
+    E, R, H, B, N = 90, 3, 24, 8, 10
+    batches = []
+    for s in range(3):
+        pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=s)
+        batches.append((pos.numpy(), neg.numpy(), w.numpy().reshape(-1, 1), 0 if mode == "head-batch" else 1))
+    shard = str(tmp_path / "toy.tfrec")
+    assert wire.write_tfrecords(batches, shard, B) == 3
+    cmd = "-ip %s -bz %d -sf TranSparse --nentity %d --nrelation %d --hidden_dim %d --gamma 12.0 --epochs 1 " \
+          "--steps_per_epoch 100" % (shard, B, E, R, H)
+    seen = {}
+    orig = tfc.Trainer.train_step
+
+    def spy(self, data_iter):
+        if "w0" not in seen:
+            seen["w0"] = {k: v.detach().cpu().clone() for k, v in self.model.state_dict().items()}
+        out = orig(self, data_iter)
+        seen.setdefault("losses", []).append(float(out["loss"]))
+        return out
+    tfc.Trainer.train_step = spy
+    try:
+        model, _ = run.main(cmd.split())
+    finally:
+        tfc.Trainer.train_step = orig
+    assert len(seen["losses"]) == 2 and "DONE" in capsys.readouterr().out   # step += 99 per call: two real steps
+    assert model.W.shape == (R, H, H) and not torch.equal(model.W.detach().cpu(), seen["w0"]["W"])
+    om = ko.OracleTranSparse(E, R, H, 12.0)
+    om.load_state_dict(seen["w0"])
+    opt = ko.KerasAdam([om.entity_embedding, om.relation_embedding, om.W], lr=1e-5)
+    pos, neg, w, mode = ko.synthetic_batch(E, R, B, N, seed=0)
+    want = ko.tf_train_step(om, opt, (pos, neg, w.view(-1, 1), torch.full((B,), 0 if mode == "head-batch" else 1)))
+    np.testing.assert_allclose(seen["losses"][0], float(want), rtol=1e-5, atol=1e-6)
+    with pytest.raises(ValueError):  # model.py:227 needs entity_dim == relation_dim
+        run.main((cmd + " -de").split())
+
+
 def test_argument_errors_match_upstream():
     with pytest.raises(ValueError, match="one of train/val/test mode must be choosed."):
         run.main([])
