@@ -81,3 +81,38 @@ def test_transparse_host_logic_without_gpu():
     rc = lib.kge_transparse_forward(ctypes.byref(as_written), 7, None, None, None, None, None, None, 8, 16, None, None, 0,
                                     None, 0, None)
     assert rc == _lib.KGE_ERR_INVALID_ARGUMENT and b"mode" in lib.kge_last_error()
+
+
+def test_struct_layouts_match_the_header(tmp_path):
+    """The header compiles as plain C (the boundary is a C ABI) and every struct of the ctypes binding has the size and
+    field offsets the C compiler gives it."""
+    import shutil
+    import subprocess
+    from customknowledgegraphembedding_b200 import _lib
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    structs = {"kge_model_desc": _lib.ModelDesc, "kge_loss_opts": _lib.LossOpts, "kge_adam_opts": _lib.AdamOpts,
+               "kge_step_buffers": _lib.StepBuffers, "kge_transparse_desc": _lib.TranSparseDesc}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "kge_b200.h"', 'int main(void) {']
+    for cname, ct in structs.items():
+        lines.append('printf("%s size %%zu\\n", sizeof(%s));' % (cname, cname))
+        for fname, _ in ct._fields_:
+            lines.append('printf("%s %s %%zu\\n", offsetof(%s, %s));' % (cname, fname, cname, fname))
+    lines += ['printf("abi %d\\n", KGE_B200_ABI_VERSION);', 'return 0; }']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(REPO, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split("\n")
+    seen = {}
+    for ln in out:
+        parts = ln.split()
+        if len(parts) == 3:
+            seen[(parts[0], parts[1])] = int(parts[2])
+        elif len(parts) == 2 and parts[0] == "abi":
+            assert int(parts[1]) == _lib.ABI_VERSION
+    for cname, ct in structs.items():
+        assert seen[(cname, "size")] == ctypes.sizeof(ct), cname
+        for fname, _ in ct._fields_:
+            assert seen[(cname, fname)] == getattr(ct, fname).offset, (cname, fname)
