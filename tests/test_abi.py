@@ -116,3 +116,17 @@ def test_struct_layouts_match_the_header(tmp_path):
         assert seen[(cname, "size")] == ctypes.sizeof(ct), cname
         for fname, _ in ct._fields_:
             assert seen[(cname, fname)] == getattr(ct, fname).offset, (cname, fname)
+
+
+def test_binding_argument_counts_match_the_header():
+    """Every prototype of the ctypes binding takes as many arguments as the declaration in include/kge_b200.h."""
+    from customknowledgegraphembedding_b200 import _lib
+    text = open(os.path.join(REPO, "include", "kge_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    found = {}
+    for m in re.finditer(r"KGE_API\s+[\w\s\*]+?\b(kge_\w+)\s*\(([^;]*?)\)\s*;", text, flags=re.S):
+        params = m.group(2).strip()
+        found[m.group(1)] = 0 if params in ("", "void") else params.count(",") + 1
+    assert set(found) == set(_lib.PROTOTYPES)
+    for name, (_, argtypes) in _lib.PROTOTYPES.items():
+        assert found[name] == len(argtypes), "%s: header has %d parameters, binding %d" % (name, found[name], len(argtypes))
