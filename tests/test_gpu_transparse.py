@@ -43,6 +43,7 @@ CASES = [
     (90, 3, 100, 7, 20, None),        # D across K stages, one column tile
     (150, 4, 300, 5, 130, [0, 2]),    # two column tiles, > 128 rows per relation, relations 1 and 3 absent
     (40, 37, 33, 9, 3, None),         # more relations than positives, odd D (scalar stores)
+    (50, 2500, 8, 40, 3, None),       # more relations than threads of the plan CTA (each thread scans several)
 ]
 
 
