@@ -130,3 +130,20 @@ def test_binding_argument_counts_match_the_header():
     assert set(found) == set(_lib.PROTOTYPES)
     for name, (_, argtypes) in _lib.PROTOTYPES.items():
         assert found[name] == len(argtypes), "%s: header has %d parameters, binding %d" % (name, found[name], len(argtypes))
+
+
+def test_transparse_has_no_cpu_path_either():
+    import torch
+    from customknowledgegraphembedding_b200.transparse import TranSparseModel
+    m = TranSparseModel(10, 2, 8, 12.0)
+    assert m.W.shape == (2, 8, 8) and m.mask.shape == (2, 8, 8) and set(m.mask.unique().tolist()) <= {0.0, 1.0}
+    assert [n for n, p in m.named_parameters() if p.requires_grad] == ["entity_embedding", "relation_embedding", "W"]
+    assert m.nout("head-batch", 7) == 7 and m.nout("tail-batch", 7) == 1 and m.nout("single", 7) == 0
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            m(torch.zeros(2, 3, dtype=torch.int64))
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            m((torch.zeros(2, 3, dtype=torch.int64), torch.zeros(2, 4, dtype=torch.int64)), "head-batch")
+    # the product never imports the oracle
+    src = open(os.path.join(REPO, "customknowledgegraphembedding_b200", "transparse.py")).read()
+    assert "oracle" not in src
